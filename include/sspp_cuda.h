@@ -1,0 +1,175 @@
+/* sspp_cuda.h — C ABI of the B200 candidate-scoring path (libsspp_cuda.so).
+ *
+ * Plain C: opaque handles, pointers and sizes only; no exceptions cross the boundary.  Every
+ * function returns 0 on success or a negative SSPPCU_E* code, with text in ssppcu_last_error()
+ * (or the caller's err buffer for the constructors).  There is NO CPU fallback behind this ABI:
+ * without a CUDA device ssppcu_create fails with SSPPCU_ECUDA.
+ *
+ * What each entry point replaces in the reference (paths under /root/reference):
+ *   ssppcu_model_load / _parse   mj_loadXML                       include/sspp.h:47, src/main_icra_benchmark.cpp:146
+ *   ssppcu_create                per-thread mjData pools          include/sspp.h:235-244, include/sspp/tsp_collision_world.h:21-27
+ *   ssppcu_set_queries           initializePath / initLinear      include/sspp.h:82-97, include/sspp/tsp_path_model.h:11-29
+ *   ssppcu_reset_distribution    Planner::reset, Distribution::reset   include/sspp/tsp_planner.h:54-69, tsp_distribution.h:16-29
+ *   ssppcu_set_distribution      sigma*limits of sampleWithNoise  include/sspp.h:116-125
+ *   ssppcu_iterate               the candidate loop: sample -> spline -> mj_forward -> contacts -> costs -> elites -> update
+ *                                include/sspp.h:203-224 and include/sspp/tsp_planner.h:78-142
+ *   ssppcu_get_results/_params   successes_/failures_/sampled_sets_, ret_success_paths   tsp_planner.h:114-118, sspp.h:223
+ *   ssppcu_get_elites            EliteSelector::select / weights  include/sspp/tsp_elites.h:13-32
+ *   ssppcu_get_distribution      Distribution::mean_vias / sigma_vias   include/sspp/tsp_distribution.h:7-8
+ *   ssppcu_eval_points           spline(u), qpos <- point, mj_forward, contact read-out
+ *                                include/sspp.h:137-144, include/Collision.h:84-103
+ */
+#ifndef SSPP_CUDA_H
+#define SSPP_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SSPPCU_OK 0
+#define SSPPCU_EINVAL (-1)   /* bad argument */
+#define SSPPCU_EMODEL (-2)   /* MJCF could not be loaded / specialised */
+#define SSPPCU_ECUDA (-3)    /* CUDA runtime error (including: no device) */
+#define SSPPCU_ELIMIT (-4)   /* a compiled-in limit is exceeded */
+
+#define SSPPCU_MAX_DOF 9
+
+#define SSPPCU_MODE_JOINT 0  /* planner A: sspp::SamplingPathPlanner<kDOF>, joint space, cubic */
+#define SSPPCU_MODE_TASK 1   /* planner B: tsp::Planner, (x,y,z,yaw) of a free body, quadratic */
+
+#define SSPPCU_ST_CONVERGED 0
+#define SSPPCU_ST_FAILED 1
+#define SSPPCU_ST_ABSENT 2   /* the forwarded-best slot of a cold iteration */
+
+typedef struct ssppcu_model ssppcu_model_t;
+typedef struct ssppcu_planner ssppcu_t;
+
+/* Read-only view of the flat FP64 model (an mjModel subset).  Pointers stay valid until
+ * ssppcu_model_free.  body_jtype uses MuJoCo's enum: -1 none, 0 free, 2 slide, 3 hinge. */
+typedef struct SsppFlatModelView {
+  int32_t nbody, ngeom, nq, nexclude;
+  const int32_t* body_parent; const int32_t* body_weld; const int32_t* body_jtype; const int32_t* body_qadr;
+  const double* body_pos;  /* 3 */  const double* body_quat; /* 4 */
+  const double* jnt_axis;  /* 3 */  const double* jnt_pos;   /* 3 */  const double* jnt_range; /* 2 */
+  const double* qpos0;
+  const int32_t* geom_body; const int32_t* geom_type; const int32_t* geom_contype; const int32_t* geom_conaffinity;
+  const double* geom_size; /* 3 */  const double* geom_pos;  /* 3 */  const double* geom_quat; /* 4 */
+  const double* geom_margin;
+  const int32_t* exclude;  /* 2 per entry */
+} SsppFlatModelView;
+
+typedef struct SsppPlannerConfig {
+  int32_t mode;            /* SSPPCU_MODE_* */
+  int32_t dof;             /* JOINT: 1..9 planned scalar joints (first qpos entries); TASK: 4 */
+  int32_t degree;          /* spline degree: 3 (sspp.h:25) or 2 (tsp_types.h:9) */
+  int32_t n_points;        /* init_points (sspp.h:196) / total_points (tsp_planner.h:16) */
+  int32_t check_points;    /* check_points / checks */
+  int32_t n_samples;       /* random candidates per iteration (this shard's share when sharded) */
+  int32_t include_mean;    /* TASK seeds: mean set first (tsp_planner.h:82-85) */
+  int32_t include_best;    /* TASK seeds: forwarded best second (tsp_planner.h:87) */
+  int32_t do_update;       /* CES update of the distribution each iteration */
+  int32_t n_queries;       /* independent planning queries held by this handle */
+  int32_t device;          /* CUDA device ordinal */
+  int32_t shard_offset;    /* population sharding: global index of this shard's first candidate */
+  int32_t shard_global;    /* population sharding: global candidate count, 0 = not sharded */
+  const char* body_name;   /* TASK: the free body that is planned */
+  double w_collision, elite_fraction, inc, dec;
+  double sigma_floor, var_beta, mean_lr, stddev_min, stddev_max;
+  double eval_zmin, floor_margin, floor_scale;   /* tsp_evaluator.h:8 */
+  double limit_scale;      /* JOINT: penalty scale*max(0,|q|-hi)^2 per coordinate and point, 0 = off */
+  double sample_zmin;      /* cfg_.z_min (tsp_sampler.h:47) */
+  double dist_zmin;        /* dist_.z_min (tsp_distribution.h:64) */
+  double lo[SSPPCU_MAX_DOF], hi[SSPPCU_MAX_DOF];   /* sampler limits / mean clamp */
+} SsppPlannerConfig;
+
+/* sizes derived from a config, for sizing caller buffers */
+typedef struct SsppDims {
+  int32_t n_queries, n_cand, n_free, dof, n_points, nfd /* n_free*dof */, n_pad;
+  int32_t rows_collision, rows_arc, first_free_row;
+  int32_t threads, cand_per_cta, ctas_per_query; int64_t smem_bytes;
+  int32_t n_mbody, n_mgeom, n_sgeom, n_pair, n_mmpair, chain;
+} SsppDims;
+
+/* raw device pointers of the handle-owned result buffers (device-buffer path; valid until the
+ * next ssppcu_iterate on the handle's stream, layouts as in ssppcu_get_results / _get_params) */
+typedef struct SsppDeviceView {
+  float* L; float* Cnf; float* Cwf; float* cost; uint8_t* status;
+  float* params; float* mean; float* sigma; float* best; int32_t* best_valid;
+  unsigned long long* keys; float* elite_w;
+  int32_t* n_success; int32_t* n_elite; int32_t* best_idx; float* best_cost; int32_t* any_success;
+  void* stream;
+} SsppDeviceView;
+
+/* ---- model ---- */
+int ssppcu_model_load(const char* mjcf_path, ssppcu_model_t** out, char* err, size_t errlen);
+int ssppcu_model_parse(const char* mjcf_text, ssppcu_model_t** out, char* err, size_t errlen);
+void ssppcu_model_free(ssppcu_model_t* m);
+int ssppcu_model_view(const ssppcu_model_t* m, SsppFlatModelView* out);
+int ssppcu_model_body_id(const ssppcu_model_t* m, const char* name);          /* -1 when absent */
+const char* ssppcu_model_body_name(const ssppcu_model_t* m, int body);
+const char* ssppcu_model_geom_name(const ssppcu_model_t* m, int geom);
+/* (x,y,z,yaw) of a free body at the model's initial pose (Utility::get_body_point, utility.h:228-259) */
+int ssppcu_model_body_point(const ssppcu_model_t* m, const char* body, double out4[4]);
+/* filtered pair count for a planner: moving-vs-static, moving-vs-moving, never-moving */
+int ssppcu_model_pair_counts(const ssppcu_model_t* m, int mode, int dof, const char* body,
+                             int32_t* n_moving_static, int32_t* n_moving_moving, int32_t* n_static_static,
+                             char* err, size_t errlen);
+
+/* ---- planner handle ---- */
+void ssppcu_default_config(int mode, SsppPlannerConfig* cfg);
+int ssppcu_create(const ssppcu_model_t* m, const SsppPlannerConfig* cfg, ssppcu_t** out, char* err, size_t errlen);
+void ssppcu_destroy(ssppcu_t* h);
+const char* ssppcu_last_error(const ssppcu_t* h);
+int ssppcu_dims(const ssppcu_t* h, SsppDims* out);
+int ssppcu_set_stream(ssppcu_t* h, void* cuda_stream);   /* NULL restores the handle's own stream */
+
+/* start/end: [n_queries][dof] host doubles.  Builds the point matrix of every query (JOINT: the
+ * interpolating control points of the straight line; TASK: the linear interpolation points). */
+int ssppcu_set_queries(ssppcu_t* h, const double* start, const double* end);
+/* TASK reset(): mean <- interior points with z floor and clamp, sigma <- clamp(sigma0), best cleared */
+int ssppcu_reset_distribution(ssppcu_t* h, double sigma0);
+/* explicit distribution, [n_queries][nfd] host doubles; NULL leaves that part unchanged */
+int ssppcu_set_distribution(ssppcu_t* h, const double* mean, const double* sigma);
+int ssppcu_get_distribution(ssppcu_t* h, double* mean, double* sigma);
+/* JOINT convenience: mean <- interior control points, sigma[r][d] <- sigma*limits[d] (sspp.h:116-125) */
+int ssppcu_set_joint_noise(ssppcu_t* h, double sigma, const double* limits);
+
+/* n_iters fused iterations, asynchronous on the handle's stream; Philox counters (seed, iter0+i) */
+int ssppcu_iterate(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters);
+int ssppcu_sync(ssppcu_t* h);
+
+/* host copies of the last iteration; any pointer may be NULL.  Per-candidate arrays are
+ * [n_queries][n_cand], per-query arrays [n_queries].  Synchronises the stream. */
+int ssppcu_get_results(ssppcu_t* h, float* L, float* Cnf, float* Cwf, float* cost, uint8_t* status,
+                       int32_t* n_success, int32_t* n_elite, int32_t* best_idx, float* best_cost,
+                       int32_t* any_success);
+int ssppcu_get_params(ssppcu_t* h, float* params /* [n_queries][n_cand][nfd] */);
+int ssppcu_get_best(ssppcu_t* h, float* best /* [n_queries][nfd] */, int32_t* valid /* [n_queries] */);
+/* sorted (cost,index) of one query: up to cap entries, elites first with their CES weights */
+int ssppcu_get_elites(ssppcu_t* h, int query, uint32_t* idx, float* cost, float* weight, int cap);
+int ssppcu_device_view(ssppcu_t* h, SsppDeviceView* out);
+
+/* Score explicit spline points: pts [n][dof] host floats -> collision cost per point (the
+ * contact rule of the handle's mode).  The unit check of FK + narrow phase. */
+int ssppcu_eval_points(ssppcu_t* h, const float* pts, int n, float* cost_out);
+
+/* collocation matrices the handle applies (host copies, row-major [rows][n_points]) */
+int ssppcu_get_collocation(ssppcu_t* h, float* psi_collision, float* psi_arc);
+/* point matrix of every query, [n_queries][n_points][dof] */
+int ssppcu_get_base(ssppcu_t* h, float* base);
+
+/* ---- population sharding: each rank scores its shard with ssppcu_iterate, gathers the sorted
+ * shard keys of all ranks (8 bytes per candidate) and applies the identical update ---- */
+int ssppcu_shard_keys(ssppcu_t* h, unsigned long long** dev_keys, int32_t* n_keys);
+int ssppcu_merge_update(ssppcu_t* h, const unsigned long long* dev_gathered_keys, int n_keys,
+                        uint64_t seed, uint32_t iter);
+
+int ssppcu_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SSPP_CUDA_H */

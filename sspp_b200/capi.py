@@ -1,0 +1,330 @@
+"""ctypes binding of the C ABI in include/sspp_cuda.h (libsspp_cuda.so).
+
+This is the thinnest possible host-side layer: it only marshals arguments.  The shared library
+is built in-tree by ``__graft_entry__.build()`` (nvcc, sm_100a).  If it is missing the import
+fails loudly — there is no Python or CPU fallback for the scoring path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+import numpy as np
+
+_HERE = Path(__file__).resolve().parent
+LIB_PATH = _HERE / "csrc" / "libsspp_cuda.so"
+
+MAX_DOF = 9
+MODE_JOINT, MODE_TASK = 0, 1
+ST_CONVERGED, ST_FAILED, ST_ABSENT = 0, 1, 2
+OK, EINVAL, EMODEL, ECUDA, ELIMIT = 0, -1, -2, -3, -4
+
+
+class SsppError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(msg)
+        self.code = code
+
+
+def _load() -> C.CDLL:
+    if not LIB_PATH.exists():
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). sspp_b200 has no CPU fallback.")
+    return C.CDLL(str(LIB_PATH), mode=os.RTLD_GLOBAL if hasattr(os, "RTLD_GLOBAL") else 0)
+
+
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int32)
+_fp = C.POINTER(C.c_float)
+
+
+class FlatModelView(C.Structure):
+    _fields_ = [("nbody", C.c_int32), ("ngeom", C.c_int32), ("nq", C.c_int32), ("nexclude", C.c_int32),
+                ("body_parent", _ip), ("body_weld", _ip), ("body_jtype", _ip), ("body_qadr", _ip),
+                ("body_pos", _dp), ("body_quat", _dp), ("jnt_axis", _dp), ("jnt_pos", _dp), ("jnt_range", _dp),
+                ("qpos0", _dp),
+                ("geom_body", _ip), ("geom_type", _ip), ("geom_contype", _ip), ("geom_conaffinity", _ip),
+                ("geom_size", _dp), ("geom_pos", _dp), ("geom_quat", _dp), ("geom_margin", _dp),
+                ("exclude", _ip)]
+
+
+class PlannerConfig(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("dof", C.c_int32), ("degree", C.c_int32), ("n_points", C.c_int32),
+                ("check_points", C.c_int32), ("n_samples", C.c_int32), ("include_mean", C.c_int32),
+                ("include_best", C.c_int32), ("do_update", C.c_int32), ("n_queries", C.c_int32),
+                ("device", C.c_int32), ("shard_offset", C.c_int32), ("shard_global", C.c_int32),
+                ("body_name", C.c_char_p),
+                ("w_collision", C.c_double), ("elite_fraction", C.c_double), ("inc", C.c_double), ("dec", C.c_double),
+                ("sigma_floor", C.c_double), ("var_beta", C.c_double), ("mean_lr", C.c_double),
+                ("stddev_min", C.c_double), ("stddev_max", C.c_double),
+                ("eval_zmin", C.c_double), ("floor_margin", C.c_double), ("floor_scale", C.c_double),
+                ("limit_scale", C.c_double), ("sample_zmin", C.c_double), ("dist_zmin", C.c_double),
+                ("lo", C.c_double * MAX_DOF), ("hi", C.c_double * MAX_DOF)]
+
+
+class Dims(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("n_queries", "n_cand", "n_free", "dof", "n_points", "nfd", "n_pad",
+                                          "rows_collision", "rows_arc", "first_free_row", "threads", "cand_per_cta",
+                                          "ctas_per_query")] + [("smem_bytes", C.c_int64)] + \
+               [(n, C.c_int32) for n in ("n_mbody", "n_mgeom", "n_sgeom", "n_pair", "n_mmpair", "chain")]
+
+
+class DeviceView(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("L", "Cnf", "Cwf", "cost", "status", "params", "mean", "sigma", "best",
+                                          "best_valid", "keys", "elite_w", "n_success", "n_elite", "best_idx",
+                                          "best_cost", "any_success", "stream")]
+
+
+# every symbol include/sspp_cuda.h declares (tests check the library exports all of them)
+SYMBOLS = [
+    "ssppcu_model_load", "ssppcu_model_parse", "ssppcu_model_free", "ssppcu_model_view", "ssppcu_model_body_id",
+    "ssppcu_model_body_name", "ssppcu_model_geom_name", "ssppcu_model_body_point", "ssppcu_model_pair_counts",
+    "ssppcu_default_config", "ssppcu_create", "ssppcu_destroy", "ssppcu_last_error", "ssppcu_dims",
+    "ssppcu_set_stream", "ssppcu_set_queries", "ssppcu_reset_distribution", "ssppcu_set_distribution",
+    "ssppcu_get_distribution", "ssppcu_set_joint_noise", "ssppcu_iterate", "ssppcu_sync", "ssppcu_get_results",
+    "ssppcu_get_params", "ssppcu_get_best", "ssppcu_get_elites", "ssppcu_device_view", "ssppcu_eval_points",
+    "ssppcu_get_collocation", "ssppcu_get_base", "ssppcu_shard_keys", "ssppcu_merge_update", "ssppcu_version",
+]
+
+lib = _load()
+lib.ssppcu_last_error.restype = C.c_char_p
+lib.ssppcu_model_body_name.restype = C.c_char_p
+lib.ssppcu_model_geom_name.restype = C.c_char_p
+lib.ssppcu_model_load.argtypes = [C.c_char_p, C.POINTER(C.c_void_p), C.c_char_p, C.c_size_t]
+lib.ssppcu_model_parse.argtypes = [C.c_char_p, C.POINTER(C.c_void_p), C.c_char_p, C.c_size_t]
+lib.ssppcu_model_free.argtypes = [C.c_void_p]
+lib.ssppcu_model_view.argtypes = [C.c_void_p, C.POINTER(FlatModelView)]
+lib.ssppcu_model_body_id.argtypes = [C.c_void_p, C.c_char_p]
+lib.ssppcu_model_body_name.argtypes = [C.c_void_p, C.c_int]
+lib.ssppcu_model_geom_name.argtypes = [C.c_void_p, C.c_int]
+lib.ssppcu_model_body_point.argtypes = [C.c_void_p, C.c_char_p, _dp]
+lib.ssppcu_model_pair_counts.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p, _ip, _ip, _ip, C.c_char_p, C.c_size_t]
+lib.ssppcu_default_config.argtypes = [C.c_int, C.POINTER(PlannerConfig)]
+lib.ssppcu_default_config.restype = None
+lib.ssppcu_create.argtypes = [C.c_void_p, C.POINTER(PlannerConfig), C.POINTER(C.c_void_p), C.c_char_p, C.c_size_t]
+lib.ssppcu_destroy.argtypes = [C.c_void_p]
+lib.ssppcu_destroy.restype = None
+lib.ssppcu_model_free.restype = None
+lib.ssppcu_last_error.argtypes = [C.c_void_p]
+lib.ssppcu_dims.argtypes = [C.c_void_p, C.POINTER(Dims)]
+lib.ssppcu_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+lib.ssppcu_set_queries.argtypes = [C.c_void_p, _dp, _dp]
+lib.ssppcu_reset_distribution.argtypes = [C.c_void_p, C.c_double]
+lib.ssppcu_set_distribution.argtypes = [C.c_void_p, _dp, _dp]
+lib.ssppcu_get_distribution.argtypes = [C.c_void_p, _dp, _dp]
+lib.ssppcu_set_joint_noise.argtypes = [C.c_void_p, C.c_double, _dp]
+lib.ssppcu_iterate.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_int]
+lib.ssppcu_sync.argtypes = [C.c_void_p]
+lib.ssppcu_get_results.argtypes = [C.c_void_p] + [C.c_void_p] * 10
+lib.ssppcu_get_params.argtypes = [C.c_void_p, C.c_void_p]
+lib.ssppcu_get_best.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+lib.ssppcu_get_elites.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+lib.ssppcu_device_view.argtypes = [C.c_void_p, C.POINTER(DeviceView)]
+lib.ssppcu_eval_points.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+lib.ssppcu_get_collocation.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+lib.ssppcu_get_base.argtypes = [C.c_void_p, C.c_void_p]
+lib.ssppcu_shard_keys.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), _ip]
+lib.ssppcu_merge_update.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_uint32]
+
+
+def _ptr(a: np.ndarray | None):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _dptr(a: np.ndarray):
+    return a.ctypes.data_as(_dp)
+
+
+def default_config(mode: int) -> PlannerConfig:
+    cfg = PlannerConfig()
+    lib.ssppcu_default_config(mode, C.byref(cfg))
+    return cfg
+
+
+class Model:
+    """Flat FP64 model parsed from an MJCF file or string (no MuJoCo involved)."""
+
+    def __init__(self, path: str | None = None, text: str | None = None):
+        self._h = C.c_void_p()
+        err = C.create_string_buffer(1024)
+        if path is not None:
+            rc = lib.ssppcu_model_load(os.fsencode(path), C.byref(self._h), err, len(err))
+        else:
+            rc = lib.ssppcu_model_parse((text or "").encode(), C.byref(self._h), err, len(err))
+        if rc != OK:
+            raise SsppError(rc, err.value.decode())
+        self.path = path
+        self.view = FlatModelView()
+        lib.ssppcu_model_view(self._h, C.byref(self.view))
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            lib.ssppcu_model_free(h)
+            self._h = None
+
+    def body_id(self, name: str) -> int:
+        return lib.ssppcu_model_body_id(self._h, name.encode())
+
+    def body_name(self, b: int) -> str:
+        return (lib.ssppcu_model_body_name(self._h, b) or b"").decode()
+
+    def geom_name(self, g: int) -> str:
+        return (lib.ssppcu_model_geom_name(self._h, g) or b"").decode()
+
+    def body_point(self, name: str) -> np.ndarray:
+        out = np.zeros(4)
+        rc = lib.ssppcu_model_body_point(self._h, name.encode(), _dptr(out))
+        if rc != OK:
+            raise SsppError(rc, f"body '{name}' is not a free body of the model")
+        return out
+
+    def pair_counts(self, mode: int, dof: int, body: str = "") -> tuple[int, int, int]:
+        a, b, c = C.c_int32(), C.c_int32(), C.c_int32()
+        err = C.create_string_buffer(1024)
+        rc = lib.ssppcu_model_pair_counts(self._h, mode, dof, body.encode(), C.byref(a), C.byref(b), C.byref(c), err, len(err))
+        if rc != OK:
+            raise SsppError(rc, err.value.decode())
+        return a.value, b.value, c.value
+
+    def arrays(self) -> dict:
+        """numpy copies of the flat arrays"""
+        v = self.view
+        nb, ng = v.nbody, v.ngeom
+
+        def ai(p, n): return np.ctypeslib.as_array(p, shape=(n,)).copy() if n else np.zeros(0, np.int32)
+        def ad(p, n, k): return np.ctypeslib.as_array(p, shape=(n * k,)).reshape(n, k).copy() if n else np.zeros((0, k))
+        return dict(nbody=nb, ngeom=ng, nq=v.nq,
+                    body_parent=ai(v.body_parent, nb), body_weld=ai(v.body_weld, nb), body_jtype=ai(v.body_jtype, nb),
+                    body_qadr=ai(v.body_qadr, nb), body_pos=ad(v.body_pos, nb, 3), body_quat=ad(v.body_quat, nb, 4),
+                    jnt_axis=ad(v.jnt_axis, nb, 3), jnt_pos=ad(v.jnt_pos, nb, 3), jnt_range=ad(v.jnt_range, nb, 2),
+                    qpos0=ad(v.qpos0, v.nq, 1).ravel(),
+                    geom_body=ai(v.geom_body, ng), geom_type=ai(v.geom_type, ng), geom_contype=ai(v.geom_contype, ng),
+                    geom_conaffinity=ai(v.geom_conaffinity, ng), geom_size=ad(v.geom_size, ng, 3),
+                    geom_pos=ad(v.geom_pos, ng, 3), geom_quat=ad(v.geom_quat, ng, 4),
+                    geom_margin=ad(v.geom_margin, ng, 1).ravel(),
+                    exclude=ai(v.exclude, 2 * v.nexclude).reshape(-1, 2))
+
+
+class Handle:
+    """One ssppcu_t: a scene specialised for one planner shape, resident on one GPU."""
+
+    def __init__(self, model: Model, cfg: PlannerConfig):
+        self._h = C.c_void_p()
+        self.model = model
+        self._body = cfg.body_name            # keep the bytes alive
+        err = C.create_string_buffer(1024)
+        rc = lib.ssppcu_create(model._h, C.byref(cfg), C.byref(self._h), err, len(err))
+        if rc != OK:
+            raise SsppError(rc, err.value.decode())
+        self.dims = Dims()
+        lib.ssppcu_dims(self._h, C.byref(self.dims))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib.ssppcu_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def _ck(self, rc: int):
+        if rc < 0:
+            raise SsppError(rc, lib.ssppcu_last_error(self._h).decode())
+        return rc
+
+    def set_stream(self, stream_ptr: int | None):
+        self._ck(lib.ssppcu_set_stream(self._h, stream_ptr))
+
+    def set_queries(self, start, end):
+        d = self.dims
+        s = np.ascontiguousarray(np.asarray(start, np.float64).reshape(d.n_queries, d.dof))
+        e = np.ascontiguousarray(np.asarray(end, np.float64).reshape(d.n_queries, d.dof))
+        self._ck(lib.ssppcu_set_queries(self._h, _dptr(s), _dptr(e)))
+
+    def reset_distribution(self, sigma0: float):
+        self._ck(lib.ssppcu_reset_distribution(self._h, float(sigma0)))
+
+    def set_distribution(self, mean=None, sigma=None):
+        d = self.dims
+        m = None if mean is None else np.ascontiguousarray(np.asarray(mean, np.float64).reshape(d.n_queries, d.nfd))
+        s = None if sigma is None else np.ascontiguousarray(np.asarray(sigma, np.float64).reshape(d.n_queries, d.nfd))
+        self._ck(lib.ssppcu_set_distribution(self._h, None if m is None else _dptr(m), None if s is None else _dptr(s)))
+
+    def get_distribution(self):
+        d = self.dims
+        m = np.zeros((d.n_queries, d.n_free, d.dof)); s = np.zeros_like(m)
+        self._ck(lib.ssppcu_get_distribution(self._h, _dptr(m), _dptr(s)))
+        return m, s
+
+    def set_joint_noise(self, sigma: float, limits):
+        lim = np.ascontiguousarray(np.asarray(limits, np.float64).reshape(self.dims.dof))
+        self._ck(lib.ssppcu_set_joint_noise(self._h, float(sigma), _dptr(lim)))
+
+    def iterate(self, seed: int, iter0: int = 0, n_iters: int = 1):
+        self._ck(lib.ssppcu_iterate(self._h, C.c_uint64(seed), C.c_uint32(iter0), int(n_iters)))
+
+    def sync(self):
+        self._ck(lib.ssppcu_sync(self._h))
+
+    def results(self) -> dict:
+        d = self.dims
+        Q, N = d.n_queries, d.n_cand
+        out = dict(L=np.zeros((Q, N), np.float32), Cnf=np.zeros((Q, N), np.float32), Cwf=np.zeros((Q, N), np.float32),
+                   cost=np.zeros((Q, N), np.float32), status=np.zeros((Q, N), np.uint8),
+                   n_success=np.zeros(Q, np.int32), n_elite=np.zeros(Q, np.int32), best_idx=np.zeros(Q, np.int32),
+                   best_cost=np.zeros(Q, np.float32), any_success=np.zeros(Q, np.int32))
+        self._ck(lib.ssppcu_get_results(self._h, *[_ptr(out[k]) for k in (
+            "L", "Cnf", "Cwf", "cost", "status", "n_success", "n_elite", "best_idx", "best_cost", "any_success")]))
+        return out
+
+    def params(self) -> np.ndarray:
+        d = self.dims
+        p = np.zeros((d.n_queries, d.n_cand, d.n_free, d.dof), np.float32)
+        self._ck(lib.ssppcu_get_params(self._h, _ptr(p)))
+        return p
+
+    def best(self):
+        d = self.dims
+        b = np.zeros((d.n_queries, d.n_free, d.dof), np.float32); v = np.zeros(d.n_queries, np.int32)
+        self._ck(lib.ssppcu_get_best(self._h, _ptr(b), _ptr(v)))
+        return b, v
+
+    def elites(self, query: int = 0, cap: int | None = None):
+        cap = self.dims.n_cand if cap is None else cap
+        idx = np.zeros(cap, np.uint32); cost = np.zeros(cap, np.float32); w = np.zeros(cap, np.float32)
+        n = self._ck(lib.ssppcu_get_elites(self._h, query, _ptr(idx), _ptr(cost), _ptr(w), cap))
+        return idx[:n], cost[:n], w[:n]
+
+    def device_view(self) -> DeviceView:
+        v = DeviceView()
+        self._ck(lib.ssppcu_device_view(self._h, C.byref(v)))
+        return v
+
+    def eval_points(self, pts) -> np.ndarray:
+        p = np.ascontiguousarray(np.asarray(pts, np.float32).reshape(-1, self.dims.dof))
+        out = np.zeros(len(p), np.float32)
+        self._ck(lib.ssppcu_eval_points(self._h, _ptr(p), len(p), _ptr(out)))
+        return out
+
+    def collocation(self):
+        d = self.dims
+        pc = np.zeros((d.rows_collision, d.n_points), np.float32)
+        pa = np.zeros((d.rows_arc, d.n_points), np.float32)
+        self._ck(lib.ssppcu_get_collocation(self._h, _ptr(pc), _ptr(pa)))
+        return pc, pa
+
+    def base(self) -> np.ndarray:
+        d = self.dims
+        b = np.zeros((d.n_queries, d.n_points, d.dof), np.float32)
+        self._ck(lib.ssppcu_get_base(self._h, _ptr(b)))
+        return b
+
+    def shard_keys(self) -> tuple[int, int]:
+        p = C.c_void_p(); n = C.c_int32()
+        self._ck(lib.ssppcu_shard_keys(self._h, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def merge_update(self, dev_keys_ptr: int, n_keys: int, seed: int, it: int):
+        self._ck(lib.ssppcu_merge_update(self._h, C.c_void_p(dev_keys_ptr), int(n_keys), C.c_uint64(seed), C.c_uint32(it)))

@@ -1,0 +1,570 @@
+// sspp_cabi.cu — implementation of include/sspp_cuda.h: handle bookkeeping, device buffers and
+// launches.  No arithmetic of the scoring path lives here (that is sspp_kernels.cu) and nothing
+// here can run the path on the CPU: every compute entry point ends in a kernel launch.
+#include "../../include/sspp_cuda.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "sspp_kernels.h"
+#include "sspp_model.h"
+#include "sspp_spline.h"
+
+using namespace sspp;
+using ssppm::DevModel;
+using ssppm::ScoreConfig;
+
+struct ssppcu_model {
+  FlatModel m;
+};
+
+struct ssppcu_planner {
+  SsppPlannerConfig cfg;
+  std::string body_name;
+  DevModel dev;
+  IterParams P;
+  int threads = 256;
+  size_t smem = 0;
+  int n_sm = 148;
+  cudaStream_t own_stream = nullptr, stream = nullptr;
+  std::string err;
+  SplineSetup spl;
+  std::vector<float> psi_col, psi_arc, base_host;
+  std::vector<void*> allocs;
+  float* d_eval_pts = nullptr; float* d_eval_out = nullptr; int eval_cap = 0;
+  unsigned long long* d_merge_keys = nullptr; int merge_cap = 0;
+};
+
+namespace {
+
+void set_err(char* err, size_t n, const std::string& s) {
+  if (err && n) { std::snprintf(err, n, "%s", s.c_str()); }
+}
+int fail(ssppcu_t* h, int code, const std::string& s) { if (h) h->err = s; return code; }
+int cuda_fail(ssppcu_t* h, cudaError_t e, const char* what) {
+  return fail(h, SSPPCU_ECUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CU(h, call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return cuda_fail((h), e__, #call); } while (0)
+
+template <class T>
+int dalloc(ssppcu_t* h, T** p, size_t n) {
+  void* q = nullptr;
+  cudaError_t e = cudaMalloc(&q, std::max<size_t>(n, 1) * sizeof(T));
+  if (e != cudaSuccess) return cuda_fail(h, e, "cudaMalloc");
+  e = cudaMemset(q, 0, std::max<size_t>(n, 1) * sizeof(T));
+  if (e != cudaSuccess) return cuda_fail(h, e, "cudaMemset");
+  h->allocs.push_back(q);
+  *p = static_cast<T*>(q);
+  return 0;
+}
+
+int next_pow2(int n) { int p = 1; while (p < n) p <<= 1; return p; }
+
+}  // namespace
+
+extern "C" {
+
+int ssppcu_version(void) { return 100; }
+
+int ssppcu_model_load(const char* path, ssppcu_model_t** out, char* err, size_t errlen) {
+  if (!path || !out) { set_err(err, errlen, "null argument"); return SSPPCU_EINVAL; }
+  try { auto* m = new ssppcu_model; m->m = load_mjcf(path); *out = m; return SSPPCU_OK; }
+  catch (const std::exception& e) { set_err(err, errlen, e.what()); return SSPPCU_EMODEL; }
+}
+int ssppcu_model_parse(const char* text, ssppcu_model_t** out, char* err, size_t errlen) {
+  if (!text || !out) { set_err(err, errlen, "null argument"); return SSPPCU_EINVAL; }
+  try { auto* m = new ssppcu_model; m->m = parse_mjcf(text); *out = m; return SSPPCU_OK; }
+  catch (const std::exception& e) { set_err(err, errlen, std::string("Failed to load MuJoCo model from XML: ") + e.what()); return SSPPCU_EMODEL; }
+}
+void ssppcu_model_free(ssppcu_model_t* m) { delete m; }
+
+int ssppcu_model_view(const ssppcu_model_t* mm, SsppFlatModelView* v) {
+  if (!mm || !v) return SSPPCU_EINVAL;
+  const FlatModel& m = mm->m;
+  v->nbody = m.nbody; v->ngeom = m.ngeom; v->nq = m.nq; v->nexclude = (int)m.exclude.size() / 2;
+  v->body_parent = m.body_parent.data(); v->body_weld = m.body_weld.data(); v->body_jtype = m.body_jtype.data();
+  v->body_qadr = m.body_qadr.data(); v->body_pos = m.body_pos.data(); v->body_quat = m.body_quat.data();
+  v->jnt_axis = m.jnt_axis.data(); v->jnt_pos = m.jnt_pos.data(); v->jnt_range = m.jnt_range.data();
+  v->qpos0 = m.qpos0.data();
+  v->geom_body = m.geom_body.data(); v->geom_type = m.geom_type.data(); v->geom_contype = m.geom_contype.data();
+  v->geom_conaffinity = m.geom_conaffinity.data(); v->geom_size = m.geom_size.data(); v->geom_pos = m.geom_pos.data();
+  v->geom_quat = m.geom_quat.data(); v->geom_margin = m.geom_margin.data(); v->exclude = m.exclude.data();
+  return SSPPCU_OK;
+}
+int ssppcu_model_body_id(const ssppcu_model_t* m, const char* name) { return (m && name) ? m->m.body_id(name) : -1; }
+const char* ssppcu_model_body_name(const ssppcu_model_t* m, int b) { return (m && b >= 0 && b < m->m.nbody) ? m->m.body_name[b].c_str() : nullptr; }
+const char* ssppcu_model_geom_name(const ssppcu_model_t* m, int g) { return (m && g >= 0 && g < m->m.ngeom) ? m->m.geom_name[g].c_str() : nullptr; }
+
+int ssppcu_model_body_point(const ssppcu_model_t* mm, const char* body, double out4[4]) {
+  if (!mm || !body || !out4) return SSPPCU_EINVAL;
+  const FlatModel& m = mm->m;
+  const int b = m.body_id(body);
+  if (b < 0 || m.body_jtype[b] != MJ_FREE) return SSPPCU_EMODEL;
+  const double* q = &m.qpos0[m.body_qadr[b]];
+  double R[9];
+  quat_to_mat(q + 3, R);
+  out4[0] = q[0]; out4[1] = q[1]; out4[2] = q[2];
+  out4[3] = std::atan2(R[3], R[0]);   // ZYX yaw
+  return SSPPCU_OK;
+}
+
+int ssppcu_model_pair_counts(const ssppcu_model_t* m, int mode, int dof, const char* body, int32_t* nms, int32_t* nmm,
+                             int32_t* nss, char* err, size_t errlen) {
+  if (!m) return SSPPCU_EINVAL;
+  try {
+    CompileInfo info;
+    DevModel D = compile_model(m->m, mode == SSPPCU_MODE_JOINT ? PLAN_JOINT : PLAN_TASK, dof, body ? body : "", &info);
+    if (nms) *nms = D.n_pair;
+    if (nmm) *nmm = D.n_mmpair;
+    if (nss) *nss = info.n_static_pairs;
+    return SSPPCU_OK;
+  } catch (const std::exception& e) { set_err(err, errlen, e.what()); return SSPPCU_EMODEL; }
+}
+
+void ssppcu_default_config(int mode, SsppPlannerConfig* c) {
+  if (!c) return;
+  std::memset(c, 0, sizeof(*c));
+  c->mode = mode;
+  c->n_queries = 1;
+  c->elite_fraction = 0.3;
+  if (mode == SSPPCU_MODE_JOINT) {        // sspp.h:195-196 defaults; classic planner A does no CES update
+    c->dof = 7; c->degree = 3; c->n_points = 10; c->check_points = 50; c->n_samples = 50;
+    c->w_collision = 0.0; c->inc = 1.5; c->dec = 0.95; c->var_beta = 0.2; c->mean_lr = 0.5;
+    c->stddev_min = 1e-3; c->stddev_max = 10.0;
+    for (int d = 0; d < SSPPCU_MAX_DOF; ++d) { c->lo[d] = -3.14159265358979323846; c->hi[d] = 3.14159265358979323846; }
+  } else {                                 // PlannerConfig defaults, tsp_planner.h:14-29
+    c->dof = 4; c->degree = 2; c->n_points = 3; c->check_points = 40; c->n_samples = 50;
+    c->include_mean = 1; c->include_best = 1; c->do_update = 1;
+    c->w_collision = 1.0; c->inc = 1.5; c->dec = 0.95; c->sigma_floor = 0.0; c->var_beta = 0.2; c->mean_lr = 0.5;
+    c->stddev_min = 1e-3; c->stddev_max = 0.5;
+    c->eval_zmin = 0.0; c->floor_margin = 0.01; c->floor_scale = 10.0;
+    for (int d = 0; d < SSPPCU_MAX_DOF; ++d) { c->lo[d] = -2.0; c->hi[d] = 2.0; }
+  }
+}
+
+void ssppcu_destroy(ssppcu_t* h) {
+  if (!h) return;
+  cudaSetDevice(h->cfg.device);
+  for (void* p : h->allocs) cudaFree(p);
+  if (h->d_eval_pts) cudaFree(h->d_eval_pts);
+  if (h->d_eval_out) cudaFree(h->d_eval_out);
+  if (h->d_merge_keys) cudaFree(h->d_merge_keys);
+  if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  delete h;
+}
+
+const char* ssppcu_last_error(const ssppcu_t* h) { return h ? h->err.c_str() : "null handle"; }
+
+int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu_t** out, char* err, size_t errlen) {
+  if (!mm || !cfg || !out) { set_err(err, errlen, "null argument"); return SSPPCU_EINVAL; }
+  const SsppPlannerConfig& c = *cfg;
+  const bool task = c.mode == SSPPCU_MODE_TASK;
+  if (c.mode != SSPPCU_MODE_JOINT && !task) { set_err(err, errlen, "unknown mode"); return SSPPCU_EINVAL; }
+  if (task && c.dof != 4) { set_err(err, errlen, "TASK mode plans (x,y,z,yaw): dof must be 4"); return SSPPCU_EINVAL; }
+  if (c.dof < 1 || c.dof > SSPPCU_MAX_DOF) { set_err(err, errlen, "dof out of range"); return SSPPCU_EINVAL; }
+  if (c.degree < 1 || c.degree > 5) { set_err(err, errlen, "degree out of range"); return SSPPCU_EINVAL; }
+  if (c.n_points < c.degree + 1 || c.n_points > ssppm::MAX_K) { set_err(err, errlen, "n_points must be in [degree+1, 16]"); return SSPPCU_EINVAL; }
+  if (c.check_points < 2 || c.check_points > 1024) { set_err(err, errlen, "check_points must be in [2, 1024]"); return SSPPCU_EINVAL; }
+  if (c.n_samples < 1 || c.n_queries < 1) { set_err(err, errlen, "n_samples and n_queries must be positive"); return SSPPCU_EINVAL; }
+  const int n_free = task ? c.n_points - 2 : c.n_points - 2 * c.degree;
+  const int free_begin = task ? 1 : c.degree;
+  if (n_free < 0) { set_err(err, errlen, "init_points leaves no room for the fixed boundary control points"); return SSPPCU_EINVAL; }
+  int ndev = 0;
+  cudaError_t ce = cudaGetDeviceCount(&ndev);
+  if (ce != cudaSuccess || ndev == 0) {
+    set_err(err, errlen, std::string("no CUDA device: ") + (ce != cudaSuccess ? cudaGetErrorString(ce) : "device count is 0") +
+                             " (this library has no CPU path)");
+    return SSPPCU_ECUDA;
+  }
+  if (c.device < 0 || c.device >= ndev) { set_err(err, errlen, "device ordinal out of range"); return SSPPCU_EINVAL; }
+  auto* h = new ssppcu_planner;
+  h->cfg = c;
+  h->body_name = c.body_name ? c.body_name : "";
+  h->cfg.body_name = nullptr;
+  try {
+    h->dev = compile_model(mm->m, task ? PLAN_TASK : PLAN_JOINT, c.dof, h->body_name, nullptr);
+    h->spl = make_setup(c.n_points, c.degree);
+  } catch (const std::exception& e) { set_err(err, errlen, e.what()); delete h; return SSPPCU_EMODEL; }
+  // ---- collocation grids (sspp.h:134-137,157-160; tsp_evaluator.h:19-24) ----
+  const int M = c.check_points;
+  std::vector<double> gcol, garc;
+  if (task) { for (int i = 0; i <= M; ++i) gcol.push_back((double)i * (1.0 / M)); }
+  else {
+    for (int i = 0; i <= M; ++i) gcol.push_back((double)i / M);
+    for (int i = 0; i < M; ++i) garc.push_back((double)i / (M - 1));
+  }
+  {
+    std::vector<double> pc = collocation_matrix(h->spl, gcol, task);
+    h->psi_col.assign(pc.begin(), pc.end());
+    if (!task) { std::vector<double> pa = collocation_matrix(h->spl, garc, false); h->psi_arc.assign(pa.begin(), pa.end()); }
+  }
+  IterParams& P = h->P;
+  std::memset(&P, 0, sizeof(P));
+  ScoreConfig& s = P.cfg;
+  s.mode = task ? ssppm::MODE_TASK : ssppm::MODE_JOINT;
+  s.D = c.dof; s.K = c.n_points; s.n_free = n_free; s.free_begin = free_begin;
+  s.Mc = M + 1; s.col_first = task ? 1 : 0; s.Ma = task ? M + 1 : M; s.arc_same = task ? 1 : 0;
+  s.include_mean = c.include_mean ? 1 : 0; s.include_best = c.include_best ? 1 : 0; s.do_update = c.do_update ? 1 : 0;
+  const int n_local = c.n_samples + ((c.shard_global > 0) ? 0 : s.include_mean + s.include_best);
+  s.n_cand = n_local;
+  s.w_collision = (float)c.w_collision;
+  s.eval_zmin = (float)c.eval_zmin; s.floor_margin = (float)c.floor_margin; s.floor_scale = (float)c.floor_scale;
+  s.limit_scale = (float)c.limit_scale; s.sample_zmin = (float)c.sample_zmin; s.dist_zmin = (float)c.dist_zmin;
+  s.inc = (float)c.inc; s.dec = (float)c.dec; s.sigma_min = (float)c.stddev_min; s.sigma_max = (float)c.stddev_max;
+  s.sigma_floor = (float)c.sigma_floor; s.var_beta = (float)c.var_beta; s.mean_lr = (float)c.mean_lr;
+  for (int d = 0; d < SSPPCU_MAX_DOF; ++d) { s.lo[d] = (float)c.lo[d]; s.hi[d] = (float)c.hi[d]; }
+  s.elite_frac = c.elite_fraction;
+  P.n_query = c.n_queries;
+  P.cand_offset = (c.shard_global > 0) ? c.shard_offset : 0;
+  P.sort_only = (c.shard_global > 0) ? 1 : 0;
+  if (c.shard_global > 0 && (c.shard_offset < 0 || c.shard_offset + n_local > c.shard_global)) {
+    set_err(err, errlen, "shard range exceeds the global population"); delete h; return SSPPCU_EINVAL;
+  }
+  if (c.shard_global > 0 && c.n_queries != 1) { set_err(err, errlen, "population sharding holds one query per handle"); delete h; return SSPPCU_EINVAL; }
+  P.k_pad = s.K | 1;
+  P.mq = std::max(s.Mc, s.Ma);
+  P.n_pad = next_pow2(std::max(2, s.n_cand));
+  if ((ce = cudaSetDevice(c.device)) != cudaSuccess) { set_err(err, errlen, std::string("cudaSetDevice: ") + cudaGetErrorString(ce)); delete h; return SSPPCU_ECUDA; }
+  cudaDeviceProp prop;
+  if ((ce = cudaGetDeviceProperties(&prop, c.device)) != cudaSuccess) { set_err(err, errlen, std::string("cudaGetDeviceProperties: ") + cudaGetErrorString(ce)); delete h; return SSPPCU_ECUDA; }
+  h->n_sm = prop.multiProcessorCount;
+  const size_t smem_cap = std::min<size_t>(prop.sharedMemPerBlockOptin, 200 * 1024);
+  // ---- tile shape: spread a query over ~2 CTAs per SM, or one CTA per query when there are many ----
+  h->threads = ((long)s.n_cand * s.Mc <= 1024) ? 128 : 256;
+  int ctas = std::max(1, std::min(s.n_cand, (2 * h->n_sm + c.n_queries - 1) / c.n_queries));
+  for (;;) {
+    P.cand_per_cta = (s.n_cand + ctas - 1) / ctas;
+    P.ctas_per_query = (s.n_cand + P.cand_per_cta - 1) / P.cand_per_cta;
+    h->smem = iterate_smem_bytes(h->dev, P, h->threads);
+    if (h->smem <= std::min<size_t>(smem_cap, 100 * 1024) || P.cand_per_cta == 1) break;
+    ctas = std::min(s.n_cand, ctas * 2);
+  }
+  if (h->smem > smem_cap) { set_err(err, errlen, "problem shape needs more shared memory than a CTA has"); delete h; return SSPPCU_ELIMIT; }
+  P.sort_in_smem = ((size_t)P.n_pad * 8 <= smem_cap) ? 1 : 0;
+  if (P.sort_in_smem) h->smem = std::max(h->smem, (size_t)P.n_pad * 8);
+  if ((ce = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking)) != cudaSuccess) { set_err(err, errlen, std::string("cudaStreamCreate: ") + cudaGetErrorString(ce)); delete h; return SSPPCU_ECUDA; }
+  h->stream = h->own_stream;
+  // ---- device buffers ----
+  const size_t Q = c.n_queries, N = s.n_cand, nfd = (size_t)n_free * s.D;
+  float *d_psi_col = nullptr, *d_psi_arc = nullptr, *d_base = nullptr;
+  int rc = 0;
+  rc |= dalloc(h, &d_psi_col, h->psi_col.size());
+  rc |= dalloc(h, &d_psi_arc, h->psi_arc.size());
+  rc |= dalloc(h, &d_base, Q * s.K * s.D);
+  rc |= dalloc(h, &P.mean, Q * nfd); rc |= dalloc(h, &P.sigma, Q * nfd); rc |= dalloc(h, &P.best, Q * nfd);
+  rc |= dalloc(h, &P.best_valid, Q);
+  rc |= dalloc(h, &P.params, Q * N * nfd);
+  rc |= dalloc(h, &P.L, Q * N); rc |= dalloc(h, &P.Cnf, Q * N); rc |= dalloc(h, &P.Cwf, Q * N); rc |= dalloc(h, &P.cost, Q * N);
+  rc |= dalloc(h, &P.status, Q * N);
+  rc |= dalloc(h, &P.keys, Q * P.n_pad); rc |= dalloc(h, &P.elite_w, Q * P.n_pad);
+  rc |= dalloc(h, &P.n_success, Q); rc |= dalloc(h, &P.n_elite, Q); rc |= dalloc(h, &P.best_idx, Q); rc |= dalloc(h, &P.any_success, Q);
+  rc |= dalloc(h, &P.best_cost, Q); rc |= dalloc(h, &P.ticket, Q);
+  if (rc) { set_err(err, errlen, h->err); ssppcu_destroy(h); return SSPPCU_ECUDA; }
+  P.psi_col = d_psi_col; P.psi_arc = d_psi_arc; P.base = d_base;
+  ce = cudaMemcpy(d_psi_col, h->psi_col.data(), h->psi_col.size() * sizeof(float), cudaMemcpyHostToDevice);
+  if (ce == cudaSuccess && !h->psi_arc.empty()) ce = cudaMemcpy(d_psi_arc, h->psi_arc.data(), h->psi_arc.size() * sizeof(float), cudaMemcpyHostToDevice);
+  if (ce != cudaSuccess) { set_err(err, errlen, std::string("cudaMemcpy: ") + cudaGetErrorString(ce)); ssppcu_destroy(h); return SSPPCU_ECUDA; }
+  h->base_host.assign(Q * s.K * s.D, 0.0f);
+  *out = h;
+  return SSPPCU_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// queries, distribution, iteration, read-back
+// ------------------------------------------------------------------------------------------
+namespace {
+
+int check(ssppcu_t* h) {
+  if (!h) return SSPPCU_EINVAL;
+  cudaError_t e = cudaSetDevice(h->cfg.device);
+  if (e != cudaSuccess) return cuda_fail(h, e, "cudaSetDevice");
+  return 0;
+}
+
+template <class T>
+int d2h(ssppcu_t* h, T* dst, const T* src, size_t n) {
+  if (!dst) return 0;
+  cudaError_t e = cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyDeviceToHost, h->stream);
+  if (e != cudaSuccess) return cuda_fail(h, e, "cudaMemcpyAsync D2H");
+  return 0;
+}
+template <class T>
+int h2d(ssppcu_t* h, T* dst, const T* src, size_t n) {
+  cudaError_t e = cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyHostToDevice, h->stream);
+  if (e != cudaSuccess) return cuda_fail(h, e, "cudaMemcpyAsync H2D");
+  e = cudaStreamSynchronize(h->stream);   // the source is a host temporary
+  if (e != cudaSuccess) return cuda_fail(h, e, "cudaStreamSynchronize");
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ssppcu_dims(const ssppcu_t* h, SsppDims* o) {
+  if (!h || !o) return SSPPCU_EINVAL;
+  const ScoreConfig& s = h->P.cfg;
+  o->n_queries = h->P.n_query; o->n_cand = s.n_cand; o->n_free = s.n_free; o->dof = s.D; o->n_points = s.K;
+  o->nfd = s.n_free * s.D; o->n_pad = h->P.n_pad; o->rows_collision = s.Mc; o->rows_arc = s.arc_same ? s.Mc : s.Ma;
+  o->first_free_row = s.free_begin; o->threads = h->threads; o->cand_per_cta = h->P.cand_per_cta;
+  o->ctas_per_query = h->P.ctas_per_query; o->smem_bytes = (int64_t)h->smem;
+  o->n_mbody = h->dev.n_mbody; o->n_mgeom = h->dev.n_mgeom; o->n_sgeom = h->dev.n_sgeom; o->n_pair = h->dev.n_pair;
+  o->n_mmpair = h->dev.n_mmpair; o->chain = h->dev.chain;
+  return SSPPCU_OK;
+}
+
+int ssppcu_set_stream(ssppcu_t* h, void* s) {
+  if (!h) return SSPPCU_EINVAL;
+  h->stream = s ? static_cast<cudaStream_t>(s) : h->own_stream;
+  return SSPPCU_OK;
+}
+
+int ssppcu_set_queries(ssppcu_t* h, const double* start, const double* end) {
+  if (int rc = check(h)) return rc;
+  if (!start || !end) return fail(h, SSPPCU_EINVAL, "null start/end");
+  const ScoreConfig& s = h->P.cfg;
+  const int Q = h->P.n_query, K = s.K, D = s.D;
+  std::vector<double> V((size_t)K * D);
+  for (int q = 0; q < Q; ++q) {
+    for (int i = 0; i < K; ++i) {
+      const double t = (double)i / (K - 1);
+      for (int d = 0; d < D; ++d) V[(size_t)i * D + d] = (1 - t) * start[(size_t)q * D + d] + t * end[(size_t)q * D + d];
+    }
+    float* dst = &h->base_host[(size_t)q * K * D];
+    if (s.mode == ssppm::MODE_TASK) {
+      for (size_t e = 0; e < V.size(); ++e) dst[e] = (float)V[e];
+    } else {   // control points of the interpolating spline: ctrl = Ainv * V (sspp.h:95)
+      for (int i = 0; i < K; ++i)
+        for (int d = 0; d < D; ++d) {
+          double acc = 0.0;
+          for (int k = 0; k < K; ++k) acc += h->spl.Ainv[(size_t)i * K + k] * V[(size_t)k * D + d];
+          dst[(size_t)i * D + d] = (float)acc;
+        }
+    }
+  }
+  return h2d(h, const_cast<float*>(h->P.base), h->base_host.data(), h->base_host.size());
+}
+
+int ssppcu_reset_distribution(ssppcu_t* h, double sigma0) {
+  if (int rc = check(h)) return rc;
+  const ScoreConfig& s = h->P.cfg;
+  const int Q = h->P.n_query, D = s.D, nfd = s.n_free * D;
+  std::vector<float> mean((size_t)Q * nfd), sigma((size_t)Q * nfd);
+  for (int q = 0; q < Q; ++q)
+    for (int r = 0; r < s.n_free; ++r)
+      for (int d = 0; d < D; ++d) {
+        double v = h->base_host[((size_t)q * s.K + s.free_begin + r) * D + d];
+        if (s.mode == ssppm::MODE_TASK && d == 2) { v = std::max(v, h->cfg.sample_zmin); v = std::max(v, h->cfg.dist_zmin); }
+        v = std::min(std::max(v, h->cfg.lo[d]), h->cfg.hi[d]);
+        mean[(size_t)q * nfd + r * D + d] = (float)v;
+        double sg = std::max(std::min(std::max(sigma0, h->cfg.stddev_min), h->cfg.stddev_max), h->cfg.sigma_floor);
+        sigma[(size_t)q * nfd + r * D + d] = (float)sg;
+      }
+  if (int rc = h2d(h, h->P.mean, mean.data(), mean.size())) return rc;
+  if (int rc = h2d(h, h->P.sigma, sigma.data(), sigma.size())) return rc;
+  CU(h, cudaMemsetAsync(h->P.best_valid, 0, Q * sizeof(int), h->stream));
+  CU(h, cudaMemsetAsync(h->P.any_success, 0, Q * sizeof(int), h->stream));
+  return SSPPCU_OK;
+}
+
+int ssppcu_set_distribution(ssppcu_t* h, const double* mean, const double* sigma) {
+  if (int rc = check(h)) return rc;
+  const size_t n = (size_t)h->P.n_query * h->P.cfg.n_free * h->P.cfg.D;
+  std::vector<float> tmp(n);
+  if (mean) { for (size_t i = 0; i < n; ++i) tmp[i] = (float)mean[i]; if (int rc = h2d(h, h->P.mean, tmp.data(), n)) return rc; }
+  if (sigma) { for (size_t i = 0; i < n; ++i) tmp[i] = (float)sigma[i]; if (int rc = h2d(h, h->P.sigma, tmp.data(), n)) return rc; }
+  return SSPPCU_OK;
+}
+
+int ssppcu_get_distribution(ssppcu_t* h, double* mean, double* sigma) {
+  if (int rc = check(h)) return rc;
+  const size_t n = (size_t)h->P.n_query * h->P.cfg.n_free * h->P.cfg.D;
+  std::vector<float> a(n), b(n);
+  if (int rc = d2h(h, a.data(), h->P.mean, n)) return rc;
+  if (int rc = d2h(h, b.data(), h->P.sigma, n)) return rc;
+  CU(h, cudaStreamSynchronize(h->stream));
+  if (mean) for (size_t i = 0; i < n; ++i) mean[i] = a[i];
+  if (sigma) for (size_t i = 0; i < n; ++i) sigma[i] = b[i];
+  return SSPPCU_OK;
+}
+
+int ssppcu_set_joint_noise(ssppcu_t* h, double sg, const double* limits) {
+  if (int rc = check(h)) return rc;
+  if (!limits) return fail(h, SSPPCU_EINVAL, "null limits");
+  const ScoreConfig& s = h->P.cfg;
+  const int Q = h->P.n_query, D = s.D, nfd = s.n_free * D;
+  std::vector<double> mean((size_t)Q * nfd), sigma((size_t)Q * nfd);
+  for (int q = 0; q < Q; ++q)
+    for (int r = 0; r < s.n_free; ++r)
+      for (int d = 0; d < D; ++d) {
+        mean[(size_t)q * nfd + r * D + d] = h->base_host[((size_t)q * s.K + s.free_begin + r) * D + d];
+        sigma[(size_t)q * nfd + r * D + d] = sg * limits[d];
+      }
+  CU(h, cudaMemsetAsync(h->P.best_valid, 0, Q * sizeof(int), h->stream));
+  CU(h, cudaMemsetAsync(h->P.any_success, 0, Q * sizeof(int), h->stream));
+  return ssppcu_set_distribution(h, mean.data(), sigma.data());
+}
+
+int ssppcu_iterate(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters) {
+  if (int rc = check(h)) return rc;
+  if (n_iters < 1) return fail(h, SSPPCU_EINVAL, "n_iters must be positive");
+  IterParams P = h->P;
+  P.seed = seed;
+  if (P.ctas_per_query == 1) {      // whole query in one CTA: iterate inside the kernel
+    P.iter0 = iter0; P.n_inner = n_iters;
+    CU(h, launch_iterate(h->dev, P, h->threads, h->smem, h->stream));
+  } else {
+    P.n_inner = 1;
+    for (int i = 0; i < n_iters; ++i) {
+      P.iter0 = iter0 + (uint32_t)i;
+      CU(h, launch_iterate(h->dev, P, h->threads, h->smem, h->stream));
+    }
+  }
+  return SSPPCU_OK;
+}
+
+int ssppcu_sync(ssppcu_t* h) {
+  if (int rc = check(h)) return rc;
+  CU(h, cudaStreamSynchronize(h->stream));
+  return SSPPCU_OK;
+}
+
+int ssppcu_get_results(ssppcu_t* h, float* L, float* Cnf, float* Cwf, float* cost, uint8_t* status, int32_t* n_success,
+                       int32_t* n_elite, int32_t* best_idx, float* best_cost, int32_t* any_success) {
+  if (int rc = check(h)) return rc;
+  const size_t Q = h->P.n_query, QN = Q * h->P.cfg.n_cand;
+  int rc = 0;
+  rc |= d2h(h, L, h->P.L, QN); rc |= d2h(h, Cnf, h->P.Cnf, QN); rc |= d2h(h, Cwf, h->P.Cwf, QN);
+  rc |= d2h(h, cost, h->P.cost, QN); rc |= d2h(h, status, h->P.status, QN);
+  rc |= d2h(h, n_success, h->P.n_success, Q); rc |= d2h(h, n_elite, h->P.n_elite, Q);
+  rc |= d2h(h, best_idx, h->P.best_idx, Q); rc |= d2h(h, best_cost, h->P.best_cost, Q);
+  rc |= d2h(h, any_success, h->P.any_success, Q);
+  if (rc) return SSPPCU_ECUDA;
+  CU(h, cudaStreamSynchronize(h->stream));
+  return SSPPCU_OK;
+}
+
+int ssppcu_get_params(ssppcu_t* h, float* params) {
+  if (int rc = check(h)) return rc;
+  if (!params) return fail(h, SSPPCU_EINVAL, "null params");
+  const size_t n = (size_t)h->P.n_query * h->P.cfg.n_cand * h->P.cfg.n_free * h->P.cfg.D;
+  if (int rc = d2h(h, params, h->P.params, n)) return rc;
+  CU(h, cudaStreamSynchronize(h->stream));
+  return SSPPCU_OK;
+}
+
+int ssppcu_get_best(ssppcu_t* h, float* best, int32_t* valid) {
+  if (int rc = check(h)) return rc;
+  const size_t Q = h->P.n_query, nfd = (size_t)h->P.cfg.n_free * h->P.cfg.D;
+  if (int rc = d2h(h, best, h->P.best, Q * nfd)) return rc;
+  if (int rc = d2h(h, valid, h->P.best_valid, Q)) return rc;
+  CU(h, cudaStreamSynchronize(h->stream));
+  return SSPPCU_OK;
+}
+
+int ssppcu_get_elites(ssppcu_t* h, int query, uint32_t* idx, float* cost, float* weight, int cap) {
+  if (int rc = check(h)) return rc;
+  if (query < 0 || query >= h->P.n_query || cap < 0) return fail(h, SSPPCU_EINVAL, "query out of range");
+  const int n = std::min(cap, h->P.cfg.n_cand);
+  std::vector<unsigned long long> keys(n);
+  std::vector<float> w(n);
+  if (int rc = d2h(h, keys.data(), h->P.keys + (size_t)query * h->P.n_pad, n)) return rc;
+  if (int rc = d2h(h, w.data(), h->P.elite_w + (size_t)query * h->P.n_pad, n)) return rc;
+  CU(h, cudaStreamSynchronize(h->stream));
+  for (int i = 0; i < n; ++i) {
+    if (idx) idx[i] = (uint32_t)(keys[i] & 0xFFFFFFFFull);
+    if (cost) {
+      uint32_t ob = (uint32_t)(keys[i] >> 32);
+      if (ob == 0xFFFFFFFFu) cost[i] = INFINITY;
+      else { ob = (ob & 0x80000000u) ? (ob & 0x7FFFFFFFu) : ~ob; std::memcpy(&cost[i], &ob, 4); }
+    }
+    if (weight) weight[i] = w[i];
+  }
+  return n;
+}
+
+int ssppcu_device_view(ssppcu_t* h, SsppDeviceView* o) {
+  if (!h || !o) return SSPPCU_EINVAL;
+  const IterParams& P = h->P;
+  o->L = P.L; o->Cnf = P.Cnf; o->Cwf = P.Cwf; o->cost = P.cost; o->status = P.status; o->params = P.params;
+  o->mean = P.mean; o->sigma = P.sigma; o->best = P.best; o->best_valid = P.best_valid; o->keys = P.keys;
+  o->elite_w = P.elite_w; o->n_success = P.n_success; o->n_elite = P.n_elite; o->best_idx = P.best_idx;
+  o->best_cost = P.best_cost; o->any_success = P.any_success; o->stream = h->stream;
+  return SSPPCU_OK;
+}
+
+int ssppcu_eval_points(ssppcu_t* h, const float* pts, int n, float* out) {
+  if (int rc = check(h)) return rc;
+  if (!pts || !out || n < 0) return fail(h, SSPPCU_EINVAL, "bad arguments");
+  if (n == 0) return SSPPCU_OK;
+  const int D = h->P.cfg.D;
+  if (n > h->eval_cap) {
+    if (h->d_eval_pts) cudaFree(h->d_eval_pts);
+    if (h->d_eval_out) cudaFree(h->d_eval_out);
+    h->d_eval_pts = h->d_eval_out = nullptr; h->eval_cap = 0;
+    CU(h, cudaMalloc(&h->d_eval_pts, (size_t)n * D * sizeof(float)));
+    CU(h, cudaMalloc(&h->d_eval_out, (size_t)n * sizeof(float)));
+    h->eval_cap = n;
+  }
+  CU(h, cudaMemcpyAsync(h->d_eval_pts, pts, (size_t)n * D * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+  CU(h, launch_eval_points(h->dev, D, h->d_eval_pts, n, h->d_eval_out, h->stream));
+  CU(h, cudaMemcpyAsync(out, h->d_eval_out, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));
+  return SSPPCU_OK;
+}
+
+int ssppcu_get_collocation(ssppcu_t* h, float* pc, float* pa) {
+  if (!h) return SSPPCU_EINVAL;
+  if (pc) std::memcpy(pc, h->psi_col.data(), h->psi_col.size() * sizeof(float));
+  if (pa && !h->psi_arc.empty()) std::memcpy(pa, h->psi_arc.data(), h->psi_arc.size() * sizeof(float));
+  return SSPPCU_OK;
+}
+
+int ssppcu_get_base(ssppcu_t* h, float* base) {
+  if (!h || !base) return SSPPCU_EINVAL;
+  std::memcpy(base, h->base_host.data(), h->base_host.size() * sizeof(float));
+  return SSPPCU_OK;
+}
+
+int ssppcu_shard_keys(ssppcu_t* h, unsigned long long** keys, int32_t* n) {
+  if (!h || !keys || !n) return SSPPCU_EINVAL;
+  *keys = h->P.keys; *n = h->P.cfg.n_cand;
+  return SSPPCU_OK;
+}
+
+int ssppcu_merge_update(ssppcu_t* h, const unsigned long long* gathered, int n_keys, uint64_t seed, uint32_t iter) {
+  if (int rc = check(h)) return rc;
+  if (!gathered || n_keys < 1) return fail(h, SSPPCU_EINVAL, "bad arguments");
+  if (h->cfg.shard_global <= 0) return fail(h, SSPPCU_EINVAL, "handle is not a population shard");
+  const int n_pad = next_pow2(std::max(2, n_keys));
+  if (n_pad > h->merge_cap) {
+    if (h->d_merge_keys) cudaFree(h->d_merge_keys);
+    h->d_merge_keys = nullptr; h->merge_cap = 0;
+    CU(h, cudaMalloc(&h->d_merge_keys, (size_t)n_pad * (sizeof(unsigned long long) + sizeof(float))));
+    h->merge_cap = n_pad;
+  }
+  CU(h, cudaMemcpyAsync(h->d_merge_keys, gathered, (size_t)n_keys * sizeof(unsigned long long), cudaMemcpyDeviceToDevice, h->stream));
+  MergeParams M;
+  std::memset(&M, 0, sizeof(M));
+  M.cfg = h->P.cfg;
+  M.cfg.n_cand = h->cfg.shard_global;
+  M.n_keys = n_keys; M.n_pad = n_pad; M.iter = iter; M.seed = seed;
+  M.keys = h->d_merge_keys;
+  M.elite_w = reinterpret_cast<float*>(h->d_merge_keys + n_pad);
+  M.mean = h->P.mean; M.sigma = h->P.sigma; M.best = h->P.best; M.best_valid = h->P.best_valid;
+  M.n_success = h->P.n_success; M.n_elite = h->P.n_elite; M.best_idx = h->P.best_idx; M.best_cost = h->P.best_cost;
+  M.any_success = h->P.any_success;
+  CU(h, launch_merge_update(M, h->stream));
+  return SSPPCU_OK;
+}
+
+}  // extern "C"

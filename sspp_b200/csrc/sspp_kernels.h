@@ -1,0 +1,64 @@
+// sspp_kernels.h — launch interface of the fused scoring iteration (sspp_kernels.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "sspp_math.h"
+
+namespace sspp {
+
+// Everything one launch needs besides the scene.  All pointers are device pointers owned by the
+// C-ABI handle; layouts are row-major with the query index outermost.
+struct IterParams {
+  ssppm::ScoreConfig cfg;
+  int n_query;
+  int cand_per_cta, ctas_per_query;
+  int n_inner;              // iterations run inside this launch (> 1 only when ctas_per_query == 1)
+  int sort_in_smem;         // keys of one query fit the dynamic shared memory
+  int cand_offset;          // global index of local candidate 0 (population sharding), else 0
+  int sort_only;            // population shard: sort the local keys, leave elites/update to the merge kernel
+  int n_pad;                // n_cand rounded up to a power of two (bitonic sort length)
+  int k_pad;                // row pitch of the basis matrices in shared memory (odd)
+  int mq;                   // pitch (rows) of the per-candidate point buffer: max(Mc, Ma)
+  uint32_t iter0;           // iteration counter of the first inner iteration (Philox counter word)
+  uint64_t seed;
+  const float* psi_col;     // [Mc][K]  collocation matrix of the collision grid
+  const float* psi_arc;     // [Ma][K]  collocation matrix of the arc-length grid (unused when arc_same)
+  const float* base;        // [Q][K][D] point matrix before the sampled rows are overwritten
+  float* mean;              // [Q][n_free*D]
+  float* sigma;             // [Q][n_free*D]
+  float* best;              // [Q][n_free*D]  forwarded best candidate (last_best_, tsp_planner.h:134)
+  int* best_valid;          // [Q]
+  float* params;            // [Q][N][n_free*D] sampled rows of every candidate
+  float* L; float* Cnf; float* Cwf; float* cost;   // [Q][N]
+  uint8_t* status;          // [Q][N]
+  unsigned long long* keys; // [Q][n_pad] (cost bits << 32 | index), sorted ascending after the launch
+  float* elite_w;           // [Q][n_pad] CES weights of the first n_elite sorted entries
+  int* n_success; int* n_elite; int* best_idx; int* any_success;   // [Q]
+  float* best_cost;         // [Q]
+  unsigned int* ticket;     // [Q]
+};
+
+// shared-memory bytes of the scoring phase for the given tile shape
+size_t iterate_smem_bytes(const ssppm::DevModel& M, const IterParams& P, int threads);
+
+cudaError_t launch_iterate(const ssppm::DevModel& M, const IterParams& P, int threads, size_t smem_bytes,
+                           cudaStream_t stream);
+
+// second kernel of the population-sharded path: every rank applies the same CES update from the
+// gathered (cost bits << 32 | global candidate index) keys of all shards; elites' sampled rows are
+// regenerated from the Philox counters, so only 8-byte keys cross NVLink.
+struct MergeParams {
+  ssppm::ScoreConfig cfg;      // n_cand = global population
+  int n_keys, n_pad;           // gathered keys, padded sort length
+  uint32_t iter; uint64_t seed;
+  unsigned long long* keys;    // [n_pad] gathered keys (sorted in place)
+  float* elite_w;              // [n_pad]
+  float* mean; float* sigma; float* best; int* best_valid;
+  int* n_success; int* n_elite; int* best_idx; float* best_cost; int* any_success;
+};
+cudaError_t launch_merge_update(const MergeParams& P, cudaStream_t stream);
+
+// collision cost of n explicit points pts[n][D] (unit check of kinematics + narrow phase)
+cudaError_t launch_eval_points(const ssppm::DevModel& M, int D, const float* pts, int n, float* out, cudaStream_t stream);
+
+}  // namespace sspp

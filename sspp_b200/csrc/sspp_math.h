@@ -1,0 +1,737 @@
+// sspp_math.h — single-source FP32 arithmetic of the candidate-scoring hot path.
+//
+// Compiled by nvcc this is the body of the sm_100a kernels (sspp_kernels.cu); compiled by g++
+// (-ffp-contract=off) it is the bit-replica checker oracle/o2_replica.cpp.  Every fused
+// multiply-add is an explicit fmaf(); the device build uses --fmad=false so nothing else is
+// contracted, sqrt and division are IEEE on both sides, and sin/cos/log are the polynomials
+// below (libm and the CUDA math library do not agree bit for bit).  No warp intrinsics in here:
+// reductions live in the kernel and are restated by the oracle.
+//
+// Reference semantics restated (file:line under /root/reference):
+//   sampleWithNoise          include/sspp.h:114-130        -> sample_joint_row()
+//   Sampler::sample          include/sspp/tsp_sampler.h:12-38 -> sample_task_dim()
+//   mj_set_point/yaw_to_quat include/utility.h:149-175,198-206 -> fk_body() JT_FREE4
+//   checkCollision (ncon>0)  include/sspp.h:132-150        -> contact rule CR_COUNT
+//   collision_point_cost     include/Collision.h:84-103    -> contact rule CR_CENTER
+//   floorPenalty             include/sspp/tsp_evaluator.h:10-14 -> floor_penalty()
+// MuJoCo's kinematics / narrow phase (third party, not in the reference tree) are restated
+// from its documented semantics; see DESIGN.md "Geometry semantics".
+#pragma once
+#include <stdint.h>
+#include <math.h>
+
+#if defined(__CUDACC__)
+#define SSPP_HD __host__ __device__ __forceinline__
+#else
+#define SSPP_HD inline
+#endif
+
+namespace ssppm {
+
+// ----------------------------------------------------------------------------------------
+// limits of the flattened model (kernel-parameter resident, < 32 KB)
+// ----------------------------------------------------------------------------------------
+enum { MAX_MBODY = 16, MAX_MGEOM = 32, MAX_SGEOM = 112, MAX_PAIR = 1024, MAX_MMPAIR = 64,
+       MAX_DOF = 9, MAX_K = 16 };
+
+enum GeomType { GT_PLANE = 0, GT_SPHERE = 2, GT_CAPSULE = 3, GT_CYLINDER = 5, GT_BOX = 6 };
+enum JointType { JT_NONE = 0, JT_HINGE = 1, JT_SLIDE = 2, JT_FREE4 = 3 };
+enum ContactRule { CR_COUNT = 0,   // planner A: every contact with dist < margin counts 1
+                   CR_CENTER = 1 };// planner B: dist < -1e-3 adds -1/(centre distance + 1e-4)
+
+struct DevBody {
+  float pos[3];     // frame origin in the parent frame (world frame when parent < 0)
+  float R0[9];      // frame orientation in the parent frame, row-major
+  float axis[3];    // joint axis in the body frame (unit)
+  float anchor[3];  // joint anchor in the body frame
+  int parent;       // index into the moving-body list, -1: static parent folded into pos/R0
+  int jtype;        // JointType
+  int qidx;         // first planned coordinate this joint reads
+  int geom_begin, geom_end;  // moving geoms attached to this body
+  int has_anchor;
+};
+struct DevMGeom {
+  float pos[3];     // in the body frame
+  float R[9];
+  float size[3];    // sphere r | capsule,cylinder r,half-length | box half extents
+  float rbound;     // bounding-sphere radius about pos
+  int type;
+  int pair_begin, pair_end;   // range in DevModel::pair
+  int body;
+};
+struct DevSGeom {
+  float pos[3];     // world frame
+  float R[9];
+  float size[3];
+  float rbound;     // < 0: unbounded (plane)
+  int type;
+};
+struct DevPair { int s; float margin; };
+struct DevMMPair { int a, b; float margin; };
+
+struct DevModel {
+  int n_mbody, n_mgeom, n_sgeom, n_pair, n_mmpair;
+  int rule;          // ContactRule
+  int chain;         // 1: parent[b] == b-1 for every b and no moving-moving pairs (no transform store)
+  float static_cost; // contribution of pairs that never move (added to every point)
+  DevBody body[MAX_MBODY];
+  DevMGeom mg[MAX_MGEOM];
+  DevSGeom sg[MAX_SGEOM];
+  DevPair pair[MAX_PAIR];
+  DevMMPair mm[MAX_MMPAIR];
+};
+
+// ----------------------------------------------------------------------------------------
+// small vector helpers (explicit fmaf everywhere)
+// ----------------------------------------------------------------------------------------
+struct v3 { float x, y, z; };
+struct m3 { float a[9]; };  // row-major
+
+SSPP_HD v3 mk(float x, float y, float z) { v3 r; r.x = x; r.y = y; r.z = z; return r; }
+SSPP_HD v3 ld3(const float* p) { return mk(p[0], p[1], p[2]); }
+SSPP_HD v3 add(v3 a, v3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+SSPP_HD v3 sub(v3 a, v3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+SSPP_HD v3 scale(v3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+SSPP_HD v3 madd(v3 a, float s, v3 b) { return mk(fmaf(a.x, s, b.x), fmaf(a.y, s, b.y), fmaf(a.z, s, b.z)); }
+SSPP_HD float dot(v3 a, v3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
+SSPP_HD v3 cross(v3 a, v3 b) {
+  return mk(fmaf(a.y, b.z, -(a.z * b.y)), fmaf(a.z, b.x, -(a.x * b.z)), fmaf(a.x, b.y, -(a.y * b.x)));
+}
+SSPP_HD v3 col(const m3& R, int j) { return mk(R.a[j], R.a[3 + j], R.a[6 + j]); }
+SSPP_HD v3 mulv(const m3& R, v3 v) {  // R v
+  return mk(fmaf(R.a[2], v.z, fmaf(R.a[1], v.y, R.a[0] * v.x)),
+            fmaf(R.a[5], v.z, fmaf(R.a[4], v.y, R.a[3] * v.x)),
+            fmaf(R.a[8], v.z, fmaf(R.a[7], v.y, R.a[6] * v.x)));
+}
+SSPP_HD v3 multv(const m3& R, v3 v) {  // R^T v
+  return mk(fmaf(R.a[6], v.z, fmaf(R.a[3], v.y, R.a[0] * v.x)),
+            fmaf(R.a[7], v.z, fmaf(R.a[4], v.y, R.a[1] * v.x)),
+            fmaf(R.a[8], v.z, fmaf(R.a[5], v.y, R.a[2] * v.x)));
+}
+SSPP_HD m3 mulm(const m3& A, const float* B) {  // A B, B row-major
+  m3 C;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+      C.a[3 * i + j] = fmaf(A.a[3 * i + 2], B[6 + j], fmaf(A.a[3 * i + 1], B[3 + j], A.a[3 * i] * B[j]));
+  return C;
+}
+SSPP_HD m3 ldm(const float* p) {
+  m3 R;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) R.a[i] = p[i];
+  return R;
+}
+SSPP_HD float clampf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
+
+// ----------------------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al., SC'11) — counter based, so samples are a pure function of
+// (seed, iteration, query, candidate, stream) on the GPU and in both oracles.
+// ----------------------------------------------------------------------------------------
+SSPP_HD void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint64_t p0 = (uint64_t)0xD2511F53u * c[0];
+    const uint64_t p1 = (uint64_t)0xCD9E8D57u * c[2];
+    const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c[1] ^ k0;
+    const uint32_t n1 = (uint32_t)p1;
+    const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c[3] ^ k1;
+    const uint32_t n3 = (uint32_t)p0;
+    c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+}
+
+// counter layout: {candidate, query, iteration, stream << 8 | block}
+SSPP_HD void philox_block(uint64_t seed, uint32_t iter, uint32_t query, uint32_t cand,
+                          uint32_t stream, uint32_t block, uint32_t out[4]) {
+  out[0] = cand; out[1] = query; out[2] = iter; out[3] = (stream << 8) | (block & 0xFFu);
+  philox4x32_10(out, (uint32_t)seed, (uint32_t)(seed >> 32));
+}
+
+// (0,1) uniform with 23 random bits, exactly representable
+SSPP_HD float u01(uint32_t x) { return ((float)(x >> 9) + 0.5f) * 1.1920928955078125e-7f; }
+
+// natural log for x in (0, 2), cephes logf polynomial with explicit fma
+SSPP_HD float log_poly(float x) {
+  union { float f; uint32_t u; } b; b.f = x;
+  int e = (int)(b.u >> 23) - 126;            // x = m * 2^e, m in [0.5,1)
+  b.u = (b.u & 0x007FFFFFu) | 0x3F000000u;
+  float m = b.f;
+  if (m < 0.70710678118654752440f) { e -= 1; m = m + m; }
+  const float f = m - 1.0f;
+  const float z = f * f;
+  float y = 7.0376836292e-2f;
+  y = fmaf(y, f, -1.1514610310e-1f);
+  y = fmaf(y, f, 1.1676998740e-1f);
+  y = fmaf(y, f, -1.2420140846e-1f);
+  y = fmaf(y, f, 1.4249322787e-1f);
+  y = fmaf(y, f, -1.6668057665e-1f);
+  y = fmaf(y, f, 2.0000714765e-1f);
+  y = fmaf(y, f, -2.4999993993e-1f);
+  y = fmaf(y, f, 3.3333331174e-1f);
+  y = y * f * z;
+  const float fe = (float)e;
+  y = fmaf(fe, -2.12194440e-4f, y);
+  y = fmaf(-0.5f, z, y);
+  return fmaf(fe, 0.693359375f, f + y);
+}
+
+// sin and cos for |x| < ~1e4: 3-term Cody-Waite reduction to [-pi/4, pi/4], cephes minimax kernels
+SSPP_HD void sincos_poly(float x, float* s, float* c) {
+  const float k = rintf(x * 0.63661977236758134308f);
+  float r = fmaf(k, -1.5703125f, x);
+  r = fmaf(k, -4.837512969970703125e-4f, r);
+  r = fmaf(k, -7.54978995489188216e-8f, r);
+  const float z = r * r;
+  float ps = -1.9515295891e-4f;
+  ps = fmaf(ps, z, 8.3321608736e-3f);
+  ps = fmaf(ps, z, -1.6666654611e-1f);
+  const float sr = fmaf(ps * z, r, r);
+  float pc = 2.443315711809948e-5f;
+  pc = fmaf(pc, z, -1.388731625493765e-3f);
+  pc = fmaf(pc, z, 4.166664568298827e-2f);
+  const float cr = fmaf(pc, z * z, fmaf(-0.5f, z, 1.0f));
+  const int q = (int)k & 3;
+  const float sv = (q & 1) ? cr : sr;
+  const float cv = (q & 1) ? sr : cr;
+  *s = (q & 2) ? -sv : sv;
+  *c = ((q + 1) & 2) ? -cv : cv;
+}
+
+// Box-Muller: two uniforms -> two standard normals
+SSPP_HD void box_muller(uint32_t a, uint32_t b, float* z0, float* z1) {
+  const float r = sqrtf(-2.0f * log_poly(u01(a)));
+  float s, c;
+  sincos_poly(6.28318530717958647692f * u01(b), &s, &c);
+  *z0 = r * c; *z1 = r * s;
+}
+
+// the j-th standard normal of (seed, iter, query, cand, stream): block j/4, lane j%4
+SSPP_HD float normal_at(uint64_t seed, uint32_t iter, uint32_t query, uint32_t cand,
+                        uint32_t stream, uint32_t j) {
+  uint32_t w[4];
+  philox_block(seed, iter, query, cand, stream, j >> 2, w);
+  float z0, z1;
+  if (j & 2) box_muller(w[2], w[3], &z0, &z1); else box_muller(w[0], w[1], &z0, &z1);
+  return (j & 1) ? z1 : z0;
+}
+
+// four normals of one Philox block
+SSPP_HD void normal4(uint64_t seed, uint32_t iter, uint32_t query, uint32_t cand,
+                     uint32_t stream, uint32_t block, float z[4]) {
+  uint32_t w[4];
+  philox_block(seed, iter, query, cand, stream, block, w);
+  box_muller(w[0], w[1], &z[0], &z[1]);
+  box_muller(w[2], w[3], &z[2], &z[3]);
+}
+
+// Planner B via sampler for one coordinate (include/sspp/tsp_sampler.h:16-36).
+//  dims 0..2: N(mean,sigma) rejected until inside [lo,hi]; after 100 tries U(lo,hi)
+//  dim 3 (yaw): N(mean,sigma) wrapped into [lo,hi] by +-range; mean if lo == hi
+// stream = free_row * 4 + dim; try t consumes normal t of that stream.
+SSPP_HD float sample_task_dim(uint64_t seed, uint32_t iter, uint32_t query, uint32_t cand,
+                              int row, int dim, float mean, float sigma, float lo, float hi) {
+  const uint32_t stream = (uint32_t)(row * 4 + dim);
+  if (dim < 3) {
+    float s = 0.0f;
+    int tries = 0;
+    bool inside = false;
+    for (int blk = 0; blk < 25 && !inside; ++blk) {
+      float z[4];
+      normal4(seed, iter, query, cand, stream, (uint32_t)blk, z);
+#pragma unroll
+      for (int l = 0; l < 4; ++l) {
+        if (!inside && tries < 99) {     // tries 1..99 may be accepted (reference breaks at try 100)
+          s = fmaf(z[l], sigma, mean);
+          ++tries;
+          inside = !(s < lo || s > hi);
+        }
+      }
+    }
+    if (!inside) {                        // 100th draw is discarded for a uniform
+      uint32_t w[4];
+      philox_block(seed, iter, query, cand, stream, 25u, w);
+      s = fmaf(u01(w[0]), hi - lo, lo);
+    }
+    return s;
+  }
+  if (lo == hi) return mean;
+  float yaw = fmaf(normal_at(seed, iter, query, cand, stream, 0u), sigma, mean);
+  const float range = hi - lo;
+  for (int it = 0; it < 64 && yaw < lo; ++it) yaw += range;
+  for (int it = 0; it < 64 && yaw > hi; ++it) yaw -= range;
+  return yaw;
+}
+
+// ----------------------------------------------------------------------------------------
+// forward kinematics of one moving body (MuJoCo mj_kinematics semantics for one joint per body)
+// ----------------------------------------------------------------------------------------
+SSPP_HD void rodrigues(v3 a, float th, float* Rj) {
+  float s, c;
+  sincos_poly(th, &s, &c);
+  const float t = 1.0f - c;
+  const float xy = a.x * a.y * t, xz = a.x * a.z * t, yz = a.y * a.z * t;
+  Rj[0] = fmaf(a.x * a.x, t, c); Rj[1] = fmaf(-a.z, s, xy);     Rj[2] = fmaf(a.y, s, xz);
+  Rj[3] = fmaf(a.z, s, xy);      Rj[4] = fmaf(a.y * a.y, t, c); Rj[5] = fmaf(-a.x, s, yz);
+  Rj[6] = fmaf(-a.y, s, xz);     Rj[7] = fmaf(a.x, s, yz);      Rj[8] = fmaf(a.z * a.z, t, c);
+}
+
+// parent frame (Rp,pp) -> this body's frame (R,p) given planned coordinates q
+template <class QA>
+SSPP_HD void fk_body(const DevBody& B, bool has_parent, const m3& Rp, v3 pp, QA& q, m3* R, v3* p) {
+  if (B.jtype == JT_FREE4) {  // (x,y,z,yaw) -> pose; quaternion (cos y/2,0,0,sin y/2) == Rz(yaw)
+    float s, c;
+    sincos_poly(q.get(B.qidx + 3), &s, &c);
+    R->a[0] = c; R->a[1] = -s; R->a[2] = 0.0f;
+    R->a[3] = s; R->a[4] = c;  R->a[5] = 0.0f;
+    R->a[6] = 0.0f; R->a[7] = 0.0f; R->a[8] = 1.0f;
+    *p = mk(q.get(B.qidx), q.get(B.qidx + 1), q.get(B.qidx + 2));
+    return;
+  }
+  m3 Rw; v3 pw;
+  if (has_parent) { Rw = mulm(Rp, B.R0); pw = add(pp, mulv(Rp, ld3(B.pos))); }
+  else { Rw = ldm(B.R0); pw = ld3(B.pos); }
+  if (B.jtype == JT_HINGE) {
+    float Rj[9];
+    rodrigues(ld3(B.axis), q.get(B.qidx), Rj);
+    const m3 Rn = mulm(Rw, Rj);
+    if (B.has_anchor) { const v3 an = ld3(B.anchor); pw = add(pw, sub(mulv(Rw, an), mulv(Rn, an))); }
+    Rw = Rn;
+  } else if (B.jtype == JT_SLIDE) {
+    pw = madd(mulv(Rw, ld3(B.axis)), q.get(B.qidx), pw);
+  }
+  *R = Rw; *p = pw;
+}
+
+// ----------------------------------------------------------------------------------------
+// primitives in the world frame and their signed distances (negative = penetration depth)
+// ----------------------------------------------------------------------------------------
+struct Prim { v3 p; m3 R; v3 s; int type; };
+
+SSPP_HD float seg_point_dist2(v3 a, v3 d, float dd, v3 x) {  // segment a + t d
+  const v3 w = sub(x, a);
+  float t = (dd > 0.0f) ? clampf(dot(w, d) / dd, 0.0f, 1.0f) : 0.0f;
+  const v3 r = sub(w, scale(d, t));
+  return dot(r, r);
+}
+
+// squared distance between segments p1+s d1 and p2+t d2 (Ericson 5.1.9 clamping scheme)
+SSPP_HD float seg_seg_dist2(v3 p1, v3 d1, v3 p2, v3 d2) {
+  const v3 r = sub(p1, p2);
+  const float a = dot(d1, d1), e = dot(d2, d2), f = dot(d2, r);
+  float s, t;
+  const float eps = 1e-12f;
+  if (a <= eps && e <= eps) { s = 0.0f; t = 0.0f; }
+  else if (a <= eps) { s = 0.0f; t = clampf(f / e, 0.0f, 1.0f); }
+  else {
+    const float c = dot(d1, r);
+    if (e <= eps) { t = 0.0f; s = clampf(-c / a, 0.0f, 1.0f); }
+    else {
+      const float b = dot(d1, d2);
+      const float den = fmaf(a, e, -(b * b));
+      s = (den > eps) ? clampf(fmaf(b, f, -(c * e)) / den, 0.0f, 1.0f) : 0.0f;
+      t = fmaf(b, s, f) / e;
+      if (t < 0.0f) { t = 0.0f; s = clampf(-c / a, 0.0f, 1.0f); }
+      else if (t > 1.0f) { t = 1.0f; s = clampf((b - c) / a, 0.0f, 1.0f); }
+    }
+  }
+  const v3 w = sub(madd(d1, s, r), scale(d2, t));
+  return dot(w, w);
+}
+
+// signed distance of a point (box frame) to a box of half extents h
+SSPP_HD float point_box_sd(v3 x, v3 h) {
+  const float qx = fabsf(x.x) - h.x, qy = fabsf(x.y) - h.y, qz = fabsf(x.z) - h.z;
+  const float ox = fmaxf(qx, 0.0f), oy = fmaxf(qy, 0.0f), oz = fmaxf(qz, 0.0f);
+  const float out2 = fmaf(oz, oz, fmaf(oy, oy, ox * ox));
+  const float in = fmaxf(qx, fmaxf(qy, qz));
+  return (out2 > 0.0f) ? sqrtf(out2) : in;
+}
+
+// distance (>= 0) from the segment p0 + t d (box frame, t in [0,1]) to a box.  The squared
+// distance g(t) is convex, C1 and piecewise quadratic, so g'(t) is monotone piecewise linear:
+// bracket its root on [0,1], then 6 Newton steps that fall back to bisection when they leave
+// the bracket (fixed trip count: identical work in every lane and in the oracles).
+SSPP_HD void seg_box_grad(float t, v3 p0, v3 d, v3 h, float* g, float* hs) {
+  const float x = fmaf(t, d.x, p0.x), y = fmaf(t, d.y, p0.y), z = fmaf(t, d.z, p0.z);
+  const float ex = x - clampf(x, -h.x, h.x), ey = y - clampf(y, -h.y, h.y), ez = z - clampf(z, -h.z, h.z);
+  *g = fmaf(ez, d.z, fmaf(ey, d.y, ex * d.x));
+  const float hx = (ex != 0.0f) ? d.x * d.x : 0.0f;
+  const float hy = (ey != 0.0f) ? d.y * d.y : 0.0f;
+  const float hz = (ez != 0.0f) ? d.z * d.z : 0.0f;
+  *hs = hx + hy + hz;
+}
+SSPP_HD float seg_box_dist(v3 p0, v3 d, v3 h) {
+  float g0, g1, hs;
+  seg_box_grad(0.0f, p0, d, h, &g0, &hs);
+  seg_box_grad(1.0f, p0, d, h, &g1, &hs);
+  float lo = 0.0f, hi = 1.0f, t = 0.5f;
+#pragma unroll 1
+  for (int it = 0; it < 6; ++it) {
+    float g;
+    seg_box_grad(t, p0, d, h, &g, &hs);
+    if (g > 0.0f) hi = t; else if (g < 0.0f) lo = t;
+    float tn = (hs > 0.0f && g != 0.0f) ? t - g / hs : t;
+    if (g != 0.0f && !(tn > lo && tn < hi)) tn = 0.5f * (lo + hi);
+    t = tn;
+  }
+  t = (g0 >= 0.0f) ? 0.0f : ((g1 <= 0.0f) ? 1.0f : t);
+  const float x = fmaf(t, d.x, p0.x), y = fmaf(t, d.y, p0.y), z = fmaf(t, d.z, p0.z);
+  const float ex = x - clampf(x, -h.x, h.x), ey = y - clampf(y, -h.y, h.y), ez = z - clampf(z, -h.z, h.z);
+  return sqrtf(fmaf(ez, ez, fmaf(ey, ey, ex * ex)));
+}
+
+// running maximum of s/sqrt(l2) kept without the square root: compare s|s|/l2 by cross products
+SSPP_HD void sat_max(float s, float l2, float* bs, float* bl2) {
+  if (s * fabsf(s) * (*bl2) > (*bs) * fabsf(*bs) * l2) { *bs = s; *bl2 = l2; }
+}
+
+// box-box: 15-axis separating-axis test; > 0 separation along the best axis (a lower bound of
+// the distance), < 0 the smallest penetration depth
+SSPP_HD float box_box_sd(const Prim& A, const Prim& B) {
+  float Rm[9], Ab[9];
+  const v3 dlt = sub(B.p, A.p);
+  const v3 t = multv(A.R, dlt);
+  const float tt[3] = {t.x, t.y, t.z};
+  const float ea[3] = {A.s.x, A.s.y, A.s.z}, eb[3] = {B.s.x, B.s.y, B.s.z};
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      Rm[3 * i + j] = dot(col(A.R, i), col(B.R, j));
+      Ab[3 * i + j] = fabsf(Rm[3 * i + j]);
+    }
+  float bs = -3.0e38f, bl2 = 1.0f;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const float ra = ea[i];
+    const float rb = fmaf(eb[2], Ab[3 * i + 2], fmaf(eb[1], Ab[3 * i + 1], eb[0] * Ab[3 * i]));
+    const float s = fabsf(tt[i]) - (ra + rb);
+    if (s > bs) bs = s;
+  }
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    const float ra = fmaf(ea[2], Ab[6 + j], fmaf(ea[1], Ab[3 + j], ea[0] * Ab[j]));
+    const float rb = eb[j];
+    const float pr = fmaf(tt[2], Rm[6 + j], fmaf(tt[1], Rm[3 + j], tt[0] * Rm[j]));
+    const float s = fabsf(pr) - (ra + rb);
+    if (s > bs) bs = s;
+  }
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const int i1 = (i + 1) % 3, i2 = (i + 2) % 3;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const int j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+      const float l2 = fmaf(-Rm[3 * i + j], Rm[3 * i + j], 1.0f);
+      const float ra = fmaf(ea[i1], Ab[3 * i2 + j], ea[i2] * Ab[3 * i1 + j]);
+      const float rb = fmaf(eb[j1], Ab[3 * i + j2], eb[j2] * Ab[3 * i + j1]);
+      const float pr = fmaf(tt[i2], Rm[3 * i1 + j], -(tt[i1] * Rm[3 * i2 + j]));
+      const float s = fabsf(pr) - (ra + rb);
+      if (l2 > 1e-6f) sat_max(s, l2, &bs, &bl2);
+    }
+  }
+  return bs / sqrtf(bl2);
+}
+
+// cylinder-box: support-function separating test over a fixed direction set
+//   box face normals, cylinder axis, axis x face normal, direction centre -> closest box point
+SSPP_HD float cyl_support(v3 a, float r, float h, v3 L, float l2) {  // support of the cylinder along L
+  const float la = dot(L, a);
+  return fmaf(h, fabsf(la), r * sqrtf(fmaxf(fmaf(-la, la, l2), 0.0f)));
+}
+SSPP_HD float cyl_box_sd(const Prim& C, const Prim& B) {
+  const v3 a = col(C.R, 2);
+  const float r = C.s.x, h = C.s.y;
+  const v3 dlt = sub(C.p, B.p);
+  const v3 bx[3] = {col(B.R, 0), col(B.R, 1), col(B.R, 2)};
+  const float eb[3] = {B.s.x, B.s.y, B.s.z};
+  float bs = -3.0e38f, bl2 = 1.0f;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {   // box normals (unit)
+    const float s = fabsf(dot(dlt, bx[i])) - eb[i] - cyl_support(a, r, h, bx[i], 1.0f);
+    if (s > bs) bs = s;
+  }
+  {                               // cylinder axis (unit)
+    const float rb = fmaf(eb[2], fabsf(dot(a, bx[2])), fmaf(eb[1], fabsf(dot(a, bx[1])), eb[0] * fabsf(dot(a, bx[0]))));
+    const float s = fabsf(dot(dlt, a)) - rb - h;
+    if (s > bs) bs = s;
+  }
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {   // axis x box normal
+    const v3 L = cross(a, bx[i]);
+    const float l2 = dot(L, L);
+    const float rb = fmaf(eb[2], fabsf(dot(L, bx[2])), fmaf(eb[1], fabsf(dot(L, bx[1])), eb[0] * fabsf(dot(L, bx[0]))));
+    const float s = fabsf(dot(dlt, L)) - rb - r * sqrtf(l2);
+    if (l2 > 1e-6f) sat_max(s, l2, &bs, &bl2);
+  }
+  {                               // centre -> closest point of the box
+    const v3 x = multv(B.R, dlt);
+    const v3 cp = mk(clampf(x.x, -eb[0], eb[0]), clampf(x.y, -eb[1], eb[1]), clampf(x.z, -eb[2], eb[2]));
+    const v3 Ll = sub(x, cp);     // box frame
+    const float l2 = dot(Ll, Ll);
+    if (l2 > 1e-12f) {
+      const v3 L = mulv(B.R, Ll);
+      const float rb = fmaf(eb[2], fabsf(Ll.z), fmaf(eb[1], fabsf(Ll.y), eb[0] * fabsf(Ll.x)));
+      const float s = fabsf(dot(dlt, L)) - rb - cyl_support(a, r, h, L, l2);
+      sat_max(s, l2, &bs, &bl2);
+    }
+  }
+  return bs / sqrtf(bl2);
+}
+
+SSPP_HD float point_cyl_sd(v3 x, const Prim& C) {  // signed distance of a world point to a cylinder
+  const v3 a = col(C.R, 2);
+  const v3 w = sub(x, C.p);
+  const float z = dot(w, a);
+  const v3 rad = sub(w, scale(a, z));
+  const float rho = sqrtf(dot(rad, rad));
+  const float dz = fabsf(z) - C.s.y, dr = rho - C.s.x;
+  const float oz = fmaxf(dz, 0.0f), orr = fmaxf(dr, 0.0f);
+  const float out2 = fmaf(oz, oz, orr * orr);
+  return (out2 > 0.0f) ? sqrtf(out2) : fmaxf(dz, dr);
+}
+
+// signed distance between two world primitives; *ok = false for an unsupported pairing
+SSPP_HD float prim_sd(const Prim& A, const Prim& B, bool* ok) {
+  *ok = true;
+  const bool sw = A.type > B.type;      // order by type; swap by value (keeps both in registers)
+  const Prim Pv = sw ? B : A, Qv = sw ? A : B;
+  const Prim* P = &Pv; const Prim* Q = &Qv;
+  const int tp = P->type, tq = Q->type;
+  if (tp == GT_PLANE) {
+    const v3 n = col(P->R, 2);
+    const float d0 = dot(n, sub(Q->p, P->p));
+    if (tq == GT_SPHERE) return d0 - Q->s.x;
+    if (tq == GT_CAPSULE) return d0 - Q->s.y * fabsf(dot(n, col(Q->R, 2))) - Q->s.x;
+    if (tq == GT_CYLINDER) {
+      const float na = dot(n, col(Q->R, 2));
+      return d0 - Q->s.y * fabsf(na) - Q->s.x * sqrtf(fmaxf(fmaf(-na, na, 1.0f), 0.0f));
+    }
+    if (tq == GT_BOX)
+      return d0 - fmaf(Q->s.z, fabsf(dot(n, col(Q->R, 2))),
+                       fmaf(Q->s.y, fabsf(dot(n, col(Q->R, 1))), Q->s.x * fabsf(dot(n, col(Q->R, 0)))));
+    *ok = false; return 3.0e38f;
+  }
+  if (tp == GT_SPHERE) {
+    if (tq == GT_SPHERE) { const v3 d = sub(Q->p, P->p); return sqrtf(dot(d, d)) - P->s.x - Q->s.x; }
+    if (tq == GT_CAPSULE) {
+      const v3 ax = col(Q->R, 2);
+      const v3 a0 = madd(ax, -Q->s.y, Q->p), dd = scale(ax, 2.0f * Q->s.y);
+      return sqrtf(seg_point_dist2(a0, dd, dot(dd, dd), P->p)) - P->s.x - Q->s.x;
+    }
+    if (tq == GT_CYLINDER) return point_cyl_sd(P->p, *Q) - P->s.x;
+    if (tq == GT_BOX) return point_box_sd(multv(Q->R, sub(P->p, Q->p)), Q->s) - P->s.x;
+  }
+  if (tp == GT_CAPSULE) {
+    const v3 ax = col(P->R, 2);
+    if (tq == GT_CAPSULE) {
+      const v3 bx = col(Q->R, 2);
+      const float d2 = seg_seg_dist2(madd(ax, -P->s.y, P->p), scale(ax, 2.0f * P->s.y),
+                                     madd(bx, -Q->s.y, Q->p), scale(bx, 2.0f * Q->s.y));
+      return sqrtf(d2) - P->s.x - Q->s.x;
+    }
+    if (tq == GT_BOX) {
+      const v3 c = multv(Q->R, sub(P->p, Q->p));
+      const v3 al = multv(Q->R, ax);
+      return seg_box_dist(madd(al, -P->s.y, c), scale(al, 2.0f * P->s.y), Q->s) - P->s.x;
+    }
+  }
+  if (tp == GT_CYLINDER && tq == GT_BOX) return cyl_box_sd(*P, *Q);
+  if (tp == GT_BOX && tq == GT_BOX) return box_box_sd(*P, *Q);
+  *ok = false; return 3.0e38f;
+}
+
+// contribution of one geom pair at signed distance d (centres ca, cb) under the model's rule
+SSPP_HD float contact_cost(int rule, float d, float margin, v3 ca, v3 cb) {
+  if (rule == CR_COUNT) return (d < margin) ? 1.0f : 0.0f;
+  if (d < margin && d < -1e-3f) {
+    const v3 w = sub(cb, ca);
+    return -1.0f / (sqrtf(dot(w, w)) + 1e-4f);
+  }
+  return 0.0f;
+}
+
+SSPP_HD Prim place(const DevMGeom& g, const m3& R, v3 p) {
+  Prim P;
+  P.p = add(p, mulv(R, ld3(g.pos)));
+  P.R = mulm(R, g.R);
+  P.s = ld3(g.size);
+  P.type = g.type;
+  return P;
+}
+SSPP_HD Prim static_prim(const DevSGeom& g) {
+  Prim P; P.p = ld3(g.pos); P.R = ldm(g.R); P.s = ld3(g.size); P.type = g.type; return P;
+}
+
+// Collision cost of one configuration q: FK of every moving body, placement of its geoms,
+// bounding-sphere cull, narrow phase, contact rule.  XF is a transform store with
+// put(body, k, value) / get(body, k), k in 0..11 (R row-major then p) — shared memory on the
+// GPU, a plain array in the replica; unused when model.chain is set.
+// QA exposes the planned coordinates as q.get(i).
+template <class XF, class QA>
+SSPP_HD float point_collision_cost(const DevModel& M, QA& q, XF& xf) {
+  float cost = M.static_cost;
+  m3 R; v3 p = mk(0.f, 0.f, 0.f);
+#pragma unroll
+  for (int k = 0; k < 9; ++k) R.a[k] = 0.0f;
+#pragma unroll 1
+  for (int b = 0; b < M.n_mbody; ++b) {
+    const DevBody& B = M.body[b];
+    m3 Rp; v3 pp;
+    const bool hp = B.parent >= 0;
+    if (hp) {
+      if (M.chain) { Rp = R; pp = p; }
+      else {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) Rp.a[k] = xf.get(B.parent, k);
+        pp = mk(xf.get(B.parent, 9), xf.get(B.parent, 10), xf.get(B.parent, 11));
+      }
+    } else { pp = mk(0.f, 0.f, 0.f); Rp = R; }
+    fk_body(B, hp, Rp, pp, q, &R, &p);
+    if (!M.chain) {
+#pragma unroll
+      for (int k = 0; k < 9; ++k) xf.put(b, k, R.a[k]);
+      xf.put(b, 9, p.x); xf.put(b, 10, p.y); xf.put(b, 11, p.z);
+    }
+#pragma unroll 1
+    for (int g = B.geom_begin; g < B.geom_end; ++g) {
+      const DevMGeom& G = M.mg[g];
+      const Prim P = place(G, R, p);
+#pragma unroll 1
+      for (int k = G.pair_begin; k < G.pair_end; ++k) {
+        const DevSGeom& S = M.sg[M.pair[k].s];
+        const float margin = M.pair[k].margin;
+        if (S.rbound >= 0.0f) {   // bounding-sphere cull (conservative: + margin + slack)
+          const v3 w = sub(P.p, ld3(S.pos));
+          const float rr = G.rbound + S.rbound + fmaxf(margin, 0.0f) + 1e-4f;
+          if (dot(w, w) > rr * rr) continue;
+        }
+        bool ok;
+        const Prim Q = static_prim(S);
+        const float d = prim_sd(P, Q, &ok);
+        cost += contact_cost(M.rule, d, margin, P.p, Q.p);
+      }
+    }
+  }
+#pragma unroll 1
+  for (int k = 0; k < M.n_mmpair; ++k) {   // pairs of geoms that move relative to each other
+    const DevMGeom& Ga = M.mg[M.mm[k].a];
+    const DevMGeom& Gb = M.mg[M.mm[k].b];
+    m3 Ra, Rb; v3 pa, pb;
+#pragma unroll
+    for (int e = 0; e < 9; ++e) { Ra.a[e] = xf.get(Ga.body, e); Rb.a[e] = xf.get(Gb.body, e); }
+    pa = mk(xf.get(Ga.body, 9), xf.get(Ga.body, 10), xf.get(Ga.body, 11));
+    pb = mk(xf.get(Gb.body, 9), xf.get(Gb.body, 10), xf.get(Gb.body, 11));
+    const Prim P = place(Ga, Ra, pa), Q = place(Gb, Rb, pb);
+    const v3 w = sub(P.p, Q.p);
+    const float rr = Ga.rbound + Gb.rbound + fmaxf(M.mm[k].margin, 0.0f) + 1e-4f;
+    if (dot(w, w) > rr * rr) continue;
+    bool ok;
+    const float d = prim_sd(P, Q, &ok);
+    cost += contact_cost(M.rule, d, M.mm[k].margin, P.p, Q.p);
+  }
+  return cost;
+}
+
+// floor penalty (include/sspp/tsp_evaluator.h:10-14) and its joint-space analogue
+SSPP_HD float floor_penalty(float z, float z_min, float margin, float scl) {
+  const float deficit = (z_min + margin) - z;
+  return (deficit > 0.0f) ? scl * deficit * deficit : 0.0f;
+}
+SSPP_HD float limit_penalty(float q, float lim, float scl) {
+  const float ex = fabsf(q) - lim;
+  return (ex > 0.0f) ? scl * ex * ex : 0.0f;
+}
+
+// order-preserving map float -> uint32 used for the (cost, index) sort keys
+SSPP_HD uint32_t float_order_bits(float f) {
+  union { float f; uint32_t u; } b; b.f = f;
+  return (b.u & 0x80000000u) ? ~b.u : (b.u | 0x80000000u);
+}
+
+// ----------------------------------------------------------------------------------------
+// planner configuration shared by the kernel, the C-ABI and the replica oracle
+// ----------------------------------------------------------------------------------------
+enum { MODE_JOINT = 0,    // planner A: Gaussian noise on interior control points (sspp.h:114-130)
+       MODE_TASK = 1 };   // planner B: truncated-normal via points (tsp_sampler.h:12-51)
+enum { ST_CONVERGED = 0, ST_FAILED = 1, ST_ABSENT = 2 };   // tsp_types.h:16 (+ empty slot)
+
+struct ScoreConfig {
+  int mode;
+  int D, K;               // coordinates per point, points per candidate (control points / interpolation points)
+  int n_free, free_begin; // sampled rows [free_begin, free_begin + n_free) of the K x D point matrix
+  int Mc, col_first;      // rows of the collision grid; rows < col_first are not collision checked
+  int Ma, arc_same;       // rows of the arc-length grid (ignored when arc_same: the collision grid is used)
+  int n_cand;             // candidates per query and iteration, special slots included
+  int include_mean;       // slot 0 is the distribution mean      (tsp_planner.h:82-85)
+  int include_best;       // next slot is the forwarded best path (tsp_planner.h:87)
+  int do_update;          // CES update of mean / sigma           (tsp_planner.h:122-141)
+  float w_collision;      // cost = L + w_collision * C_wf        (tsp_planner.h:123)
+  float eval_zmin, floor_margin, floor_scale;   // Evaluator members (tsp_evaluator.h:8)
+  float limit_scale;      // joint-space analogue of the floor penalty: scale*max(0,|q_d|-hi_d)^2, 0 = off
+  float sample_zmin;      // cfg_.z_min applied to sampled via z   (tsp_sampler.h:47)
+  float dist_zmin;        // dist_.z_min applied to the mean z     (tsp_distribution.h:64)
+  float inc, dec, sigma_min, sigma_max, sigma_floor, var_beta, mean_lr;
+  float lo[MAX_DOF], hi[MAX_DOF];   // sampler limits and mean clamp
+  double elite_frac;
+};
+
+// what candidate slot `cand` holds
+enum { CK_MEAN = 0, CK_BEST = 1, CK_SAMPLE = 2, CK_ABSENT = 3 };
+SSPP_HD int candidate_kind(const ScoreConfig& c, int cand, int best_valid) {
+  if (c.include_mean && cand == 0) return CK_MEAN;
+  if (c.include_best && cand == c.include_mean) return best_valid ? CK_BEST : CK_ABSENT;
+  return CK_SAMPLE;
+}
+
+// element t = row * D + dim of candidate `cand` (the sampled rows only)
+SSPP_HD float candidate_param(const ScoreConfig& c, uint64_t seed, uint32_t iter, uint32_t query, int cand,
+                              int kind, int t, const float* mean, const float* sigma, const float* best) {
+  const int r = t / c.D, d = t - r * c.D;
+  float v;
+  if (kind == CK_MEAN) v = mean[t];
+  else if (kind == CK_BEST) return best[t];
+  else if (kind == CK_ABSENT) return mean[t];
+  else if (c.mode == MODE_JOINT) {
+    // draw order of sspp.h:121-127: coordinate-major, then control point
+    v = fmaf(normal_at(seed, iter, query, (uint32_t)cand, 0u, (uint32_t)(d * c.n_free + r)), sigma[t], mean[t]);
+    return v;
+  } else v = sample_task_dim(seed, iter, query, (uint32_t)cand, r, d, mean[t], sigma[t], c.lo[d], c.hi[d]);
+  if (c.mode == MODE_TASK && d == 2) v = fmaxf(v, c.sample_zmin);
+  return v;
+}
+
+// per-point penalty added to C_wf
+template <class QA>
+SSPP_HD float point_penalty(const ScoreConfig& c, QA& q) {
+  if (c.mode == MODE_TASK) return floor_penalty(q.get(2), c.eval_zmin, c.floor_margin, c.floor_scale);
+  float pen = 0.0f;
+  if (c.limit_scale > 0.0f)
+    for (int d = 0; d < c.D; ++d) pen += limit_penalty(q.get(d), c.hi[d], c.limit_scale);
+  return pen;
+}
+
+SSPP_HD float clamp_sigma(const ScoreConfig& c, float s) {   // tsp_distribution.h:78-81 order
+  return fmaxf(fminf(fmaxf(s, c.sigma_min), c.sigma_max), c.sigma_floor);
+}
+SSPP_HD float wrap_angle_diff(float a, float b, float lo, float hi) {   // tsp_distribution.h:40-46
+  const float range = hi - lo;
+  float d = a - b;
+  for (int it = 0; it < 64 && d > 0.5f * range; ++it) d -= range;
+  for (int it = 0; it < 64 && d < -0.5f * range; ++it) d += range;
+  return d;
+}
+SSPP_HD uint64_t sort_key(float cost, int status, uint32_t idx) {
+  const uint32_t hi = (status == ST_CONVERGED) ? float_order_bits(cost) : 0xFFFFFFFFu;
+  return ((uint64_t)hi << 32) | idx;
+}
+SSPP_HD int elite_count(int n_success, double frac) {   // tsp_elites.h:15
+  if (n_success <= 0) return 0;
+  const int k = (int)((double)n_success * frac);
+  return k < 1 ? 1 : k;
+}
+
+}  // namespace ssppm
