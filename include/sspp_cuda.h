@@ -167,6 +167,15 @@ int ssppcu_shard_keys(ssppcu_t* h, unsigned long long** dev_keys, int32_t* n_key
 int ssppcu_merge_update(ssppcu_t* h, const unsigned long long* dev_gathered_keys, int n_keys,
                         uint64_t seed, uint32_t iter);
 
+/* ---- host-side spline algebra the handle applies (no device needed; FP64) ----
+ * Restates Eigen's KnotAveraging + SplineFitting::Interpolate + Spline::operator() as the
+ * reference calls them (include/sspp.h:95,137; include/sspp/tsp_path_model.h:25-28,39-42).
+ *   knots [n_points+degree+1], Ainv [n_points][n_points]: control points = Ainv * interpolation points
+ *   psi [n_grid][n_points]: via_form 0 -> Basis(grid) (acts on control points),
+ *                           via_form 1 -> Basis(grid) * Ainv (acts on interpolation points) */
+int ssppcu_spline_setup(int n_points, int degree, double* knots, double* Ainv);
+int ssppcu_collocation_matrix(int n_points, int degree, const double* grid, int n_grid, int via_form, double* psi);
+
 int ssppcu_version(void);
 
 #ifdef __cplusplus

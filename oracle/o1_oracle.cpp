@@ -426,6 +426,17 @@ void o1_spline_eval(const double* ctrl, int K, int D, int p, double u, double* o
   spline_point(std::vector<double>(ctrl, ctrl + K * D), K, D, p, t, u, out);
 }
 
+// spline evaluation on an explicit knot vector (pins the Cox-de Boor statement against the
+// reference's Python twin sspp/BSplines.py:44-51 through tests/golden/spline_golden.npz)
+void o1_spline_eval_knots(const double* ctrl, int K, int D, int p, const double* knots, double u, double* out) {
+  std::vector<double> t(knots, knots + K + p + 1);
+  spline_point(std::vector<double>(ctrl, ctrl + K * D), K, D, p, t, u, out);
+}
+void o1_basis_row(int K, int p, const double* knots, double u, double* out) {
+  std::vector<double> t(knots, knots + K + p + 1);
+  for (int j = 0; j < K; ++j) out[j] = bfun(u, p, j, t, true);
+}
+
 // Score candidates given their sampled rows (samples are an input).
 //   base [K][D] point matrix (control points for JOINT, interpolation points for TASK)
 //   params [n][n_free*D] -> L, Cnf, Cwf, cost, status per candidate; pts_out (optional) [n][M+1][D]

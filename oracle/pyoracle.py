@@ -86,6 +86,8 @@ class O1:
         L.o1_knots.argtypes = [C.c_int, C.c_int, _dp]
         L.o1_interpolate.argtypes = [_dp, C.c_int, C.c_int, C.c_int, _dp]
         L.o1_spline_eval.argtypes = [_dp, C.c_int, C.c_int, C.c_int, C.c_double, _dp]
+        L.o1_spline_eval_knots.argtypes = [_dp, C.c_int, C.c_int, C.c_int, _dp, C.c_double, _dp]
+        L.o1_basis_row.argtypes = [C.c_int, C.c_int, _dp, C.c_double, _dp]
         self.model = model
         self.mode, self.dof = mode, dof
         plan_body = model.body_id(body) if mode == 1 else -1
@@ -171,6 +173,20 @@ class O1:
         K, D = ctrl.shape
         out = np.zeros(D)
         self.lib.o1_spline_eval(_d(ctrl), K, D, p, float(u), _d(out))
+        return out
+
+    def spline_eval_knots(self, ctrl, p: int, knots, u: float) -> np.ndarray:
+        ctrl = np.ascontiguousarray(ctrl, np.float64); knots = np.ascontiguousarray(knots, np.float64)
+        K, D = ctrl.shape
+        assert len(knots) == K + p + 1
+        out = np.zeros(D)
+        self.lib.o1_spline_eval_knots(_d(ctrl), K, D, p, _d(knots), float(u), _d(out))
+        return out
+
+    def basis_row(self, K: int, p: int, knots, u: float) -> np.ndarray:
+        knots = np.ascontiguousarray(knots, np.float64)
+        out = np.zeros(K)
+        self.lib.o1_basis_row(K, p, _d(knots), float(u), _d(out))
         return out
 
     def philox(self, ctr, k0: int, k1: int) -> np.ndarray:

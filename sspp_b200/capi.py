@@ -86,6 +86,7 @@ SYMBOLS = [
     "ssppcu_get_distribution", "ssppcu_set_joint_noise", "ssppcu_iterate", "ssppcu_sync", "ssppcu_get_results",
     "ssppcu_get_params", "ssppcu_get_best", "ssppcu_get_elites", "ssppcu_device_view", "ssppcu_eval_points",
     "ssppcu_get_collocation", "ssppcu_get_base", "ssppcu_shard_keys", "ssppcu_merge_update", "ssppcu_version",
+    "ssppcu_spline_setup", "ssppcu_collocation_matrix",
 ]
 
 lib = _load()
@@ -127,6 +128,8 @@ lib.ssppcu_get_collocation.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
 lib.ssppcu_get_base.argtypes = [C.c_void_p, C.c_void_p]
 lib.ssppcu_shard_keys.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), _ip]
 lib.ssppcu_merge_update.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_uint32]
+lib.ssppcu_spline_setup.argtypes = [C.c_int, C.c_int, _dp, _dp]
+lib.ssppcu_collocation_matrix.argtypes = [C.c_int, C.c_int, _dp, C.c_int, C.c_int, _dp]
 
 
 def _ptr(a: np.ndarray | None):
@@ -141,6 +144,54 @@ def default_config(mode: int) -> PlannerConfig:
     cfg = PlannerConfig()
     lib.ssppcu_default_config(mode, C.byref(cfg))
     return cfg
+
+
+def spline_setup(n_points: int, degree: int):
+    """(knots, Ainv) of the interpolating spline through n_points uniform parameters (host FP64)."""
+    knots = np.zeros(n_points + degree + 1); ainv = np.zeros((n_points, n_points))
+    rc = lib.ssppcu_spline_setup(n_points, degree, _dptr(knots), _dptr(ainv))
+    if rc != OK:
+        raise SsppError(rc, "invalid spline shape")
+    return knots, ainv
+
+
+def collocation_matrix(n_points: int, degree: int, grid, via_form: bool) -> np.ndarray:
+    g = np.ascontiguousarray(grid, np.float64)
+    psi = np.zeros((len(g), n_points))
+    rc = lib.ssppcu_collocation_matrix(n_points, degree, _dptr(g), len(g), int(via_form), _dptr(psi))
+    if rc != OK:
+        raise SsppError(rc, "invalid spline shape")
+    return psi
+
+
+def planner_grids(cfg: "PlannerConfig"):
+    """host restatement of the grids ssppcu_create builds: (psi_col, psi_arc) as float32"""
+    M, task = cfg.check_points, cfg.mode == MODE_TASK
+    if task:
+        gcol = np.arange(M + 1) * (1.0 / M)
+        return collocation_matrix(cfg.n_points, cfg.degree, gcol, True).astype(np.float32), None
+    gcol = np.arange(M + 1) / M
+    garc = np.arange(M) / (M - 1)
+    return (collocation_matrix(cfg.n_points, cfg.degree, gcol, False).astype(np.float32),
+            collocation_matrix(cfg.n_points, cfg.degree, garc, False).astype(np.float32))
+
+
+def base_points(cfg: "PlannerConfig", start, end) -> np.ndarray:
+    """point matrix [K][D] of one query as ssppcu_set_queries builds it (float32)"""
+    K = cfg.n_points
+    t = (np.arange(K) / (K - 1))[:, None]
+    V = (1 - t) * np.asarray(start, np.float64)[None, :] + t * np.asarray(end, np.float64)[None, :]
+    if cfg.mode == MODE_TASK:
+        return V.astype(np.float32)
+    _, ainv = spline_setup(K, cfg.degree)
+    out = np.zeros_like(V)
+    for i in range(K):           # same accumulation order as the C side
+        for d in range(V.shape[1]):
+            acc = 0.0
+            for k in range(K):
+                acc += ainv[i, k] * V[k, d]
+            out[i, d] = acc
+    return out.astype(np.float32)
 
 
 class Model:

@@ -73,6 +73,25 @@ extern "C" {
 
 int ssppcu_version(void) { return 100; }
 
+int ssppcu_spline_setup(int n_points, int degree, double* knots, double* Ainv) {
+  if (degree < 1 || n_points < degree + 1) return SSPPCU_EINVAL;
+  try {
+    SplineSetup s = make_setup(n_points, degree);
+    if (knots) std::copy(s.knots.begin(), s.knots.end(), knots);
+    if (Ainv) std::copy(s.Ainv.begin(), s.Ainv.end(), Ainv);
+    return SSPPCU_OK;
+  } catch (const std::exception&) { return SSPPCU_EINVAL; }
+}
+int ssppcu_collocation_matrix(int n_points, int degree, const double* grid, int n_grid, int via_form, double* psi) {
+  if (degree < 1 || n_points < degree + 1 || !grid || !psi || n_grid < 0) return SSPPCU_EINVAL;
+  try {
+    SplineSetup s = make_setup(n_points, degree);
+    std::vector<double> P = collocation_matrix(s, std::vector<double>(grid, grid + n_grid), via_form != 0);
+    std::copy(P.begin(), P.end(), psi);
+    return SSPPCU_OK;
+  } catch (const std::exception&) { return SSPPCU_EINVAL; }
+}
+
 int ssppcu_model_load(const char* path, ssppcu_model_t** out, char* err, size_t errlen) {
   if (!path || !out) { set_err(err, errlen, "null argument"); return SSPPCU_EINVAL; }
   try { auto* m = new ssppcu_model; m->m = load_mjcf(path); *out = m; return SSPPCU_OK; }
