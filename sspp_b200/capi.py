@@ -212,7 +212,7 @@ class Model:
 
     def __del__(self):
         h = getattr(self, "_h", None)
-        if h:
+        if h and lib is not None:      # `lib` is already None during interpreter shutdown
             lib.ssppcu_model_free(h)
             self._h = None
 
@@ -274,7 +274,7 @@ class Handle:
         lib.ssppcu_dims(self._h, C.byref(self.dims))
 
     def close(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:
             lib.ssppcu_destroy(self._h)
             self._h = None
 

@@ -17,9 +17,9 @@ SEED = 0x53535050  # "SSPP"
 # the only concrete 7-DoF configurations the reference holds (scripts/bspline_params.npy)
 Q_START = np.array([1.1805, 0.7884, 1.6656, 1.4216, 0.8346, -1.6386, 1.3560])
 Q_END = np.array([0.4323, 0.7750, 1.6877, 1.4162, 0.7718, -1.6073, 0.6237])
-# the ICRA query (scripts/vpsto_benchmark/README.md:80-92)
-ICRA_START = np.array([0.5, 0.15, 0.116, 1.57])
-ICRA_END = np.array([0.5, -0.05, 0.116, 0.0])
+# the ICRA query: body points of block_green/ and block_orange/ lifted by 0.02 (src/main_icra_benchmark.cpp:176-178)
+ICRA_START = np.array([0.5, 0.15, 0.136, np.pi / 2])
+ICRA_END = np.array([0.5, -0.05, 0.136, np.pi / 2])
 ICRA_BODY = "gripper_collision_with_block/"
 
 
@@ -86,7 +86,7 @@ def task_case(scene="robocrane.xml", body=ICRA_BODY, n_samples=15, check_points=
     cfg.dist_zmin = 0.2 if faithful_quirks else 0.1
     cfg.eval_zmin = 0.0 if faithful_quirks else 0.1
     cfg.floor_margin, cfg.floor_scale = 0.01, 10.0
-    lo = [-0.7, -0.7, 0.1, -1.6]; hi = [0.7, 0.7, 0.6, 1.6]   # main_icra_benchmark.cpp:160
+    lo = [0.0, -0.7, 0.1, -1.6]; hi = [0.7, 0.7, 0.6, 1.6]   # main_icra_benchmark.cpp:160
     for d in range(4):
         cfg.lo[d], cfg.hi[d] = lo[d], hi[d]
     path = FIX / scene
