@@ -137,6 +137,12 @@ int ssppcu_get_distribution(ssppcu_t* h, double* mean, double* sigma);
 /* JOINT convenience: mean <- interior control points, sigma[r][d] <- sigma*limits[d] (sspp.h:116-125) */
 int ssppcu_set_joint_noise(ssppcu_t* h, double sigma, const double* limits);
 
+/* device-side snapshot / restore of the sampling state (mean, sigma, forwarded best): asynchronous
+ * device-to-device copies on the handle's stream.  restore re-arms a planner for a new plan() of the
+ * same query without touching the host (Planner::reset, tsp_planner.h:54-69). */
+int ssppcu_save_state(ssppcu_t* h);
+int ssppcu_restore_state(ssppcu_t* h);
+
 /* n_iters fused iterations, asynchronous on the handle's stream; Philox counters (seed, iter0+i) */
 int ssppcu_iterate(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters);
 int ssppcu_sync(ssppcu_t* h);
@@ -175,6 +181,10 @@ int ssppcu_merge_update(ssppcu_t* h, const unsigned long long* dev_gathered_keys
  *                           via_form 1 -> Basis(grid) * Ainv (acts on interpolation points) */
 int ssppcu_spline_setup(int n_points, int degree, double* knots, double* Ainv);
 int ssppcu_collocation_matrix(int n_points, int degree, const double* grid, int n_grid, int via_form, double* psi);
+
+/* Measured FP32 FMA throughput of the device (register-resident FMA chains, all SMs), the
+ * denominator of the roofline this path is bound by (it moves ~16 B per candidate). */
+int ssppcu_fp32_peak(int device, double* tflops, double* sm_clock_mhz);
 
 int ssppcu_version(void);
 

@@ -86,7 +86,8 @@ SYMBOLS = [
     "ssppcu_get_distribution", "ssppcu_set_joint_noise", "ssppcu_iterate", "ssppcu_sync", "ssppcu_get_results",
     "ssppcu_get_params", "ssppcu_get_best", "ssppcu_get_elites", "ssppcu_device_view", "ssppcu_eval_points",
     "ssppcu_get_collocation", "ssppcu_get_base", "ssppcu_shard_keys", "ssppcu_merge_update", "ssppcu_version",
-    "ssppcu_spline_setup", "ssppcu_collocation_matrix",
+    "ssppcu_spline_setup", "ssppcu_collocation_matrix", "ssppcu_save_state", "ssppcu_restore_state",
+    "ssppcu_fp32_peak",
 ]
 
 lib = _load()
@@ -128,6 +129,9 @@ lib.ssppcu_get_collocation.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
 lib.ssppcu_get_base.argtypes = [C.c_void_p, C.c_void_p]
 lib.ssppcu_shard_keys.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), _ip]
 lib.ssppcu_merge_update.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_uint32]
+lib.ssppcu_save_state.argtypes = [C.c_void_p]
+lib.ssppcu_restore_state.argtypes = [C.c_void_p]
+lib.ssppcu_fp32_peak.argtypes = [C.c_int, _dp, _dp]
 lib.ssppcu_spline_setup.argtypes = [C.c_int, C.c_int, _dp, _dp]
 lib.ssppcu_collocation_matrix.argtypes = [C.c_int, C.c_int, _dp, C.c_int, C.c_int, _dp]
 
@@ -144,6 +148,15 @@ def default_config(mode: int) -> PlannerConfig:
     cfg = PlannerConfig()
     lib.ssppcu_default_config(mode, C.byref(cfg))
     return cfg
+
+
+def fp32_peak(device: int = 0) -> tuple[float, float]:
+    """(measured FP32 FMA TFLOP/s, SM clock MHz from the device properties)"""
+    t, c = C.c_double(), C.c_double()
+    rc = lib.ssppcu_fp32_peak(device, C.byref(t), C.byref(c))
+    if rc != OK:
+        raise SsppError(rc, "FP32 probe failed (no CUDA device?)")
+    return t.value, c.value
 
 
 def spline_setup(n_points: int, degree: int):
@@ -318,6 +331,12 @@ class Handle:
 
     def sync(self):
         self._ck(lib.ssppcu_sync(self._h))
+
+    def save_state(self):
+        self._ck(lib.ssppcu_save_state(self._h))
+
+    def restore_state(self):
+        self._ck(lib.ssppcu_restore_state(self._h))
 
     def results(self) -> dict:
         d = self.dims

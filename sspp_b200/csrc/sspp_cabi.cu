@@ -40,6 +40,9 @@ struct ssppcu_planner {
   std::vector<void*> allocs;
   float* d_eval_pts = nullptr; float* d_eval_out = nullptr; int eval_cap = 0;
   unsigned long long* d_merge_keys = nullptr; int merge_cap = 0;
+  float* d_live = nullptr;       // mean | sigma | best | best_valid | any_success (ints), one block
+  float* d_state = nullptr;      // snapshot of d_live
+  size_t state_words = 0; bool state_saved = false;
 };
 
 namespace {
@@ -277,13 +280,19 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
   rc |= dalloc(h, &d_psi_col, h->psi_col.size());
   rc |= dalloc(h, &d_psi_arc, h->psi_arc.size());
   rc |= dalloc(h, &d_base, Q * s.K * s.D);
-  rc |= dalloc(h, &P.mean, Q * nfd); rc |= dalloc(h, &P.sigma, Q * nfd); rc |= dalloc(h, &P.best, Q * nfd);
-  rc |= dalloc(h, &P.best_valid, Q);
+  // sampling state in ONE block (mean | sigma | best | best_valid | any_success) + its snapshot, so that
+  // save / restore is a single device-to-device copy
+  h->state_words = 3 * Q * nfd + 2 * Q;
+  rc |= dalloc(h, &h->d_live, h->state_words); rc |= dalloc(h, &h->d_state, h->state_words);
+  if (!rc) {
+    P.mean = h->d_live; P.sigma = P.mean + Q * nfd; P.best = P.sigma + Q * nfd;
+    P.best_valid = reinterpret_cast<int*>(P.best + Q * nfd); P.any_success = P.best_valid + Q;
+  }
   rc |= dalloc(h, &P.params, Q * N * nfd);
   rc |= dalloc(h, &P.L, Q * N); rc |= dalloc(h, &P.Cnf, Q * N); rc |= dalloc(h, &P.Cwf, Q * N); rc |= dalloc(h, &P.cost, Q * N);
   rc |= dalloc(h, &P.status, Q * N);
   rc |= dalloc(h, &P.keys, Q * P.n_pad); rc |= dalloc(h, &P.elite_w, Q * P.n_pad);
-  rc |= dalloc(h, &P.n_success, Q); rc |= dalloc(h, &P.n_elite, Q); rc |= dalloc(h, &P.best_idx, Q); rc |= dalloc(h, &P.any_success, Q);
+  rc |= dalloc(h, &P.n_success, Q); rc |= dalloc(h, &P.n_elite, Q); rc |= dalloc(h, &P.best_idx, Q);
   rc |= dalloc(h, &P.best_cost, Q); rc |= dalloc(h, &P.ticket, Q);
   if (rc) { set_err(err, errlen, h->err); ssppcu_destroy(h); return SSPPCU_ECUDA; }
   P.psi_col = d_psi_col; P.psi_arc = d_psi_arc; P.base = d_base;
@@ -431,6 +440,46 @@ int ssppcu_set_joint_noise(ssppcu_t* h, double sg, const double* limits) {
   CU(h, cudaMemsetAsync(h->P.best_valid, 0, Q * sizeof(int), h->stream));
   CU(h, cudaMemsetAsync(h->P.any_success, 0, Q * sizeof(int), h->stream));
   return ssppcu_set_distribution(h, mean.data(), sigma.data());
+}
+
+int ssppcu_save_state(ssppcu_t* h) {
+  if (int rc = check(h)) return rc;
+  CU(h, cudaMemcpyAsync(h->d_state, h->d_live, h->state_words * 4, cudaMemcpyDeviceToDevice, h->stream));
+  h->state_saved = true;
+  return SSPPCU_OK;
+}
+int ssppcu_restore_state(ssppcu_t* h) {
+  if (int rc = check(h)) return rc;
+  if (!h->state_saved) return fail(h, SSPPCU_EINVAL, "no saved state");
+  CU(h, cudaMemcpyAsync(h->d_live, h->d_state, h->state_words * 4, cudaMemcpyDeviceToDevice, h->stream));
+  return SSPPCU_OK;
+}
+
+int ssppcu_fp32_peak(int device, double* tflops, double* sm_clock_mhz) {
+  if (!tflops) return SSPPCU_EINVAL;
+  if (cudaSetDevice(device) != cudaSuccess) return SSPPCU_ECUDA;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return SSPPCU_ECUDA;
+  float* sink = nullptr;
+  if (cudaMalloc(&sink, 4) != cudaSuccess) return SSPPCU_ECUDA;
+  cudaEvent_t a, b;
+  cudaEventCreate(&a); cudaEventCreate(&b);
+  const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 4096;
+  double best = 0.0;
+  for (int rep = 0; rep < 6; ++rep) {
+    cudaEventRecord(a, 0);
+    launch_fma_probe(sink, blocks, threads, iters, 0);
+    cudaEventRecord(b, 0);
+    if (cudaEventSynchronize(b) != cudaSuccess) { cudaFree(sink); return SSPPCU_ECUDA; }
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, a, b);
+    const double flop = 2.0 * 8 * 16 * (double)iters * threads * blocks;
+    if (rep > 0) best = std::max(best, flop / (ms * 1e-3) * 1e-12);
+  }
+  cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(sink);
+  *tflops = best;
+  if (sm_clock_mhz) *sm_clock_mhz = prop.clockRate * 1e-3;
+  return SSPPCU_OK;
 }
 
 int ssppcu_iterate(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters) {

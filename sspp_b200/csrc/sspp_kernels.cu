@@ -327,7 +327,30 @@ sspp_eval_points_kernel(const __grid_constant__ DevModel M, int D, const float* 
   out[i] = point_collision_cost(M, qa, xf);
 }
 
+__global__ void __launch_bounds__(256)
+sspp_fma_probe_kernel(float* sink, int iters) {
+  float a[8];
+  const float x = 1.0f + 1e-7f * (float)threadIdx.x, y = 1e-9f * (float)blockIdx.x;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) a[k] = (float)k;
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int r = 0; r < 16; ++r)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) a[k] = fmaf(a[k], x, y);
+  }
+  float s = 0.0f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s += a[k];
+  if (s == 123.456f) sink[0] = s;   // never true: keeps the chains alive
+}
+
 }  // namespace
+
+cudaError_t launch_fma_probe(float* sink, int blocks, int threads, int iters, cudaStream_t stream) {
+  sspp_fma_probe_kernel<<<blocks, threads, 0, stream>>>(sink, iters);
+  return cudaGetLastError();
+}
 
 size_t iterate_smem_bytes(const DevModel& M, const IterParams& P, int threads) {
   const ScoreConfig& c = P.cfg;

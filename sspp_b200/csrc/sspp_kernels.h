@@ -61,4 +61,7 @@ cudaError_t launch_merge_update(const MergeParams& P, cudaStream_t stream);
 // collision cost of n explicit points pts[n][D] (unit check of kinematics + narrow phase)
 cudaError_t launch_eval_points(const ssppm::DevModel& M, int D, const float* pts, int n, float* out, cudaStream_t stream);
 
+// FP32 FMA peak probe: every thread runs `iters` rounds of 8 independent FMA chains
+cudaError_t launch_fma_probe(float* sink, int blocks, int threads, int iters, cudaStream_t stream);
+
 }  // namespace sspp
