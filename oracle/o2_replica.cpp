@@ -112,6 +112,17 @@ int o2_iterate(void* h, const float* psi_col, const float* psi_arc, const float*
   const int Marc = c.arc_same ? Mc : Ma;
   const int best_ok = c.include_best ? *best_valid : 0;
   std::vector<float> X((size_t)K * D), qcol((size_t)Mc * D), qarc((size_t)Marc * D), cc(Mc), cw(Mc), seg(Marc);
+  // banded rows exactly as the C ABI packs them for the kernel
+  std::vector<int> first_col(Mc), first_arc(Ma > 0 ? Ma : 1);
+  const int w_col = compute_band(psi_col, Mc, K, first_col.data());
+  std::vector<float> band_col((size_t)Mc * w_col), band_arc;
+  pack_band(psi_col, Mc, K, w_col, first_col.data(), band_col.data());
+  int w_arc = 1;
+  if (!c.arc_same) {
+    w_arc = compute_band(psi_arc, Ma, K, first_arc.data());
+    band_arc.resize((size_t)Ma * w_arc);
+    pack_band(psi_arc, Ma, K, w_arc, first_arc.data(), band_arc.data());
+  }
   for (int i = 0; i < n_local; ++i) {
     const int gc = cand_offset + i;
     const int kind = candidate_kind(c, gc, best_ok);
@@ -123,8 +134,7 @@ int o2_iterate(void* h, const float* psi_col, const float* psi_arc, const float*
     }
     for (int m = 0; m < Mc; ++m) {
       for (int d = 0; d < D; ++d) {
-        float acc = 0.0f;
-        for (int k = 0; k < K; ++k) acc = fmaf(psi_col[m * K + k], X[k * D + d], acc);
+        const float acc = spline_coord(&band_col[(size_t)m * w_col], first_col[m], w_col, X.data(), D, d);
         qcol[m * D + d] = acc;
         if (pts) pts[((size_t)i * Mc + m) * D + d] = acc;
       }
@@ -140,9 +150,7 @@ int o2_iterate(void* h, const float* psi_col, const float* psi_arc, const float*
     if (!c.arc_same) {
       for (int m = 0; m < Ma; ++m)
         for (int d = 0; d < D; ++d) {
-          float acc = 0.0f;
-          for (int k = 0; k < K; ++k) acc = fmaf(psi_arc[m * K + k], X[k * D + d], acc);
-          qarc[m * D + d] = acc;
+          qarc[m * D + d] = spline_coord(&band_arc[(size_t)m * w_arc], first_arc[m], w_arc, X.data(), D, d);
         }
       qa_ = qarc.data();
     }

@@ -32,7 +32,7 @@ struct ssppcu_planner {
   IterParams P;
   int threads = 256;
   size_t smem = 0;
-  int n_sm = 148;
+  int n_sm = 148, grid = 1;
   cudaStream_t own_stream = nullptr, stream = nullptr;
   std::string err;
   SplineSetup spl;
@@ -250,35 +250,75 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
     set_err(err, errlen, "shard range exceeds the global population"); delete h; return SSPPCU_EINVAL;
   }
   if (c.shard_global > 0 && c.n_queries != 1) { set_err(err, errlen, "population sharding holds one query per handle"); delete h; return SSPPCU_EINVAL; }
-  P.k_pad = s.K | 1;
   P.mq = std::max(s.Mc, s.Ma);
   P.n_pad = next_pow2(std::max(2, s.n_cand));
+  // ---- banded collocation rows ----
+  std::vector<int> first_col(s.Mc), first_arc(std::max(1, s.Ma));
+  P.w_col = ssppm::compute_band(h->psi_col.data(), s.Mc, s.K, first_col.data());
+  std::vector<float> band_col((size_t)s.Mc * P.w_col), band_arc;
+  ssppm::pack_band(h->psi_col.data(), s.Mc, s.K, P.w_col, first_col.data(), band_col.data());
+  P.w_arc = 1;
+  if (!task) {
+    P.w_arc = ssppm::compute_band(h->psi_arc.data(), s.Ma, s.K, first_arc.data());
+    band_arc.resize((size_t)s.Ma * P.w_arc);
+    ssppm::pack_band(h->psi_arc.data(), s.Ma, s.K, P.w_arc, first_arc.data(), band_arc.data());
+  }
   if ((ce = cudaSetDevice(c.device)) != cudaSuccess) { set_err(err, errlen, std::string("cudaSetDevice: ") + cudaGetErrorString(ce)); delete h; return SSPPCU_ECUDA; }
   cudaDeviceProp prop;
   if ((ce = cudaGetDeviceProperties(&prop, c.device)) != cudaSuccess) { set_err(err, errlen, std::string("cudaGetDeviceProperties: ") + cudaGetErrorString(ce)); delete h; return SSPPCU_ECUDA; }
   h->n_sm = prop.multiProcessorCount;
   const size_t smem_cap = std::min<size_t>(prop.sharedMemPerBlockOptin, 200 * 1024);
-  // ---- tile shape: spread a query over ~2 CTAs per SM, or one CTA per query when there are many ----
+  // ---- tile shape ----
+  // many small queries: one CTA per query, whole plans inside one launch (coop = 0);
+  // otherwise a persistent cooperative grid over candidate tiles (coop = 1).
   h->threads = ((long)s.n_cand * s.Mc <= 1024) ? 128 : 256;
-  int ctas = std::max(1, std::min(s.n_cand, (2 * h->n_sm + c.n_queries - 1) / c.n_queries));
-  for (;;) {
-    P.cand_per_cta = (s.n_cand + ctas - 1) / ctas;
-    P.ctas_per_query = (s.n_cand + P.cand_per_cta - 1) / P.cand_per_cta;
-    h->smem = iterate_smem_bytes(h->dev, P, h->threads);
-    if (h->smem <= std::min<size_t>(smem_cap, 100 * 1024) || P.cand_per_cta == 1) break;
-    ctas = std::min(s.n_cand, ctas * 2);
+  P.coop = 0; P.cand_per_cta = s.n_cand; P.ctas_per_query = 1;
+  h->smem = iterate_smem_bytes(h->dev, P, h->threads);
+  const bool one_cta_ok = h->smem <= std::min<size_t>(smem_cap, 64 * 1024) && (long)s.n_cand * s.Mc <= 4096 && c.n_queries >= h->n_sm;
+  if (!one_cta_ok) {
+    P.coop = 1;
+    h->threads = 256;
+    int ctas = std::max(1, std::min(s.n_cand, (2 * h->n_sm + c.n_queries - 1) / c.n_queries));
+    for (;;) {
+      P.cand_per_cta = (s.n_cand + ctas - 1) / ctas;
+      P.ctas_per_query = (s.n_cand + P.cand_per_cta - 1) / P.cand_per_cta;
+      h->smem = iterate_smem_bytes(h->dev, P, h->threads);
+      if (h->smem <= std::min<size_t>(smem_cap, 100 * 1024) || P.cand_per_cta == 1) break;
+      ctas = std::min(s.n_cand, ctas * 2);
+    }
   }
   if (h->smem > smem_cap) { set_err(err, errlen, "problem shape needs more shared memory than a CTA has"); delete h; return SSPPCU_ELIMIT; }
-  P.sort_in_smem = ((size_t)P.n_pad * 8 <= smem_cap) ? 1 : 0;
-  if (P.sort_in_smem) h->smem = std::max(h->smem, (size_t)P.n_pad * 8);
+  P.n_tiles = P.ctas_per_query * c.n_queries;
+  h->grid = P.n_tiles;
+  if (P.coop) {
+    // ranking scratch: a chunk of keys + this CTA's own keys and counters; grid = co-resident CTAs
+    int per_sm = 0;
+    for (int pass = 0; pass < 2; ++pass) {
+      if ((ce = iterate_occupancy(h->threads, h->smem, &per_sm)) != cudaSuccess || per_sm < 1) {
+        set_err(err, errlen, std::string("occupancy query failed: ") + cudaGetErrorString(ce)); delete h; return SSPPCU_ECUDA;
+      }
+      h->grid = std::min(P.n_tiles, per_sm * h->n_sm);
+      const long long total = (long long)c.n_queries * s.n_cand;
+      const long long per = (total + h->grid - 1) / h->grid;
+      const size_t fixed = (size_t)per * 12 + 64;
+      const size_t want = std::min<size_t>((size_t)s.n_cand, 4096) * 8 + fixed;
+      if (fixed + 256 * 8 > smem_cap) { set_err(err, errlen, "population too large for the ranking scratch"); delete h; return SSPPCU_ELIMIT; }
+      if (want > h->smem && pass == 0) { h->smem = std::min(want, smem_cap); continue; }   // re-query occupancy with the larger footprint
+      P.rank_chunk = (int)std::min<size_t>((size_t)s.n_cand, (h->smem - fixed) / 8);
+      break;
+    }
+  }
   if ((ce = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking)) != cudaSuccess) { set_err(err, errlen, std::string("cudaStreamCreate: ") + cudaGetErrorString(ce)); delete h; return SSPPCU_ECUDA; }
   h->stream = h->own_stream;
   // ---- device buffers ----
   const size_t Q = c.n_queries, N = s.n_cand, nfd = (size_t)n_free * s.D;
   float *d_psi_col = nullptr, *d_psi_arc = nullptr, *d_base = nullptr;
+  int *d_first_col = nullptr, *d_first_arc = nullptr;
   int rc = 0;
-  rc |= dalloc(h, &d_psi_col, h->psi_col.size());
-  rc |= dalloc(h, &d_psi_arc, h->psi_arc.size());
+  rc |= dalloc(h, &d_psi_col, band_col.size());
+  rc |= dalloc(h, &d_psi_arc, band_arc.size());
+  rc |= dalloc(h, &d_first_col, first_col.size());
+  rc |= dalloc(h, &d_first_arc, first_arc.size());
   rc |= dalloc(h, &d_base, Q * s.K * s.D);
   // sampling state in ONE block (mean | sigma | best | best_valid | any_success) + its snapshot, so that
   // save / restore is a single device-to-device copy
@@ -291,13 +331,16 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
   rc |= dalloc(h, &P.params, Q * N * nfd);
   rc |= dalloc(h, &P.L, Q * N); rc |= dalloc(h, &P.Cnf, Q * N); rc |= dalloc(h, &P.Cwf, Q * N); rc |= dalloc(h, &P.cost, Q * N);
   rc |= dalloc(h, &P.status, Q * N);
-  rc |= dalloc(h, &P.keys, Q * P.n_pad); rc |= dalloc(h, &P.elite_w, Q * P.n_pad);
+  rc |= dalloc(h, &P.keys, Q * P.n_pad); rc |= dalloc(h, &P.keys_raw, Q * P.n_pad); rc |= dalloc(h, &P.elite_w, Q * P.n_pad);
+  rc |= dalloc(h, &P.succ_acc, Q);
   rc |= dalloc(h, &P.n_success, Q); rc |= dalloc(h, &P.n_elite, Q); rc |= dalloc(h, &P.best_idx, Q);
-  rc |= dalloc(h, &P.best_cost, Q); rc |= dalloc(h, &P.ticket, Q);
+  rc |= dalloc(h, &P.best_cost, Q);
   if (rc) { set_err(err, errlen, h->err); ssppcu_destroy(h); return SSPPCU_ECUDA; }
-  P.psi_col = d_psi_col; P.psi_arc = d_psi_arc; P.base = d_base;
-  ce = cudaMemcpy(d_psi_col, h->psi_col.data(), h->psi_col.size() * sizeof(float), cudaMemcpyHostToDevice);
-  if (ce == cudaSuccess && !h->psi_arc.empty()) ce = cudaMemcpy(d_psi_arc, h->psi_arc.data(), h->psi_arc.size() * sizeof(float), cudaMemcpyHostToDevice);
+  P.psi_col = d_psi_col; P.psi_arc = d_psi_arc; P.base = d_base; P.first_col = d_first_col; P.first_arc = d_first_arc;
+  ce = cudaMemcpy(d_psi_col, band_col.data(), band_col.size() * sizeof(float), cudaMemcpyHostToDevice);
+  if (ce == cudaSuccess) ce = cudaMemcpy(d_first_col, first_col.data(), first_col.size() * sizeof(int), cudaMemcpyHostToDevice);
+  if (ce == cudaSuccess && !band_arc.empty()) ce = cudaMemcpy(d_psi_arc, band_arc.data(), band_arc.size() * sizeof(float), cudaMemcpyHostToDevice);
+  if (ce == cudaSuccess && !band_arc.empty()) ce = cudaMemcpy(d_first_arc, first_arc.data(), first_arc.size() * sizeof(int), cudaMemcpyHostToDevice);
   if (ce != cudaSuccess) { set_err(err, errlen, std::string("cudaMemcpy: ") + cudaGetErrorString(ce)); ssppcu_destroy(h); return SSPPCU_ECUDA; }
   h->base_host.assign(Q * s.K * s.D, 0.0f);
   *out = h;
@@ -486,17 +529,8 @@ int ssppcu_iterate(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters) {
   if (int rc = check(h)) return rc;
   if (n_iters < 1) return fail(h, SSPPCU_EINVAL, "n_iters must be positive");
   IterParams P = h->P;
-  P.seed = seed;
-  if (P.ctas_per_query == 1) {      // whole query in one CTA: iterate inside the kernel
-    P.iter0 = iter0; P.n_inner = n_iters;
-    CU(h, launch_iterate(h->dev, P, h->threads, h->smem, h->stream));
-  } else {
-    P.n_inner = 1;
-    for (int i = 0; i < n_iters; ++i) {
-      P.iter0 = iter0 + (uint32_t)i;
-      CU(h, launch_iterate(h->dev, P, h->threads, h->smem, h->stream));
-    }
-  }
+  P.seed = seed; P.iter0 = iter0; P.n_inner = n_iters;
+  CU(h, launch_iterate(h->dev, P, h->threads, h->smem, h->grid, h->stream));
   return SSPPCU_OK;
 }
 

@@ -1,23 +1,33 @@
-// sspp_kernels.cu — the fused scoring iteration for sm_100a: one launch per planner iteration.
+// sspp_kernels.cu — the fused scoring iteration for sm_100a: one launch per planner iteration
+// (or per batch of iterations).
 //
 //   K1 perturb     Philox4x32-10 + Box-Muller noise on the sampled rows      (sspp.h:114-130, tsp_sampler.h:12-51)
-//   K2 spline      q_m = Psi[m,:] . X   (X: K x D point matrix in shared memory)  (Eigen::Spline::operator(), sspp.h:137)
+//   K2 spline      q_m = Psi[m,:] . X   (banded rows, X: K x D point matrix in shared memory)  (Eigen::Spline::operator(), sspp.h:137)
 //   K3 kinematics  link frames from q, per thread                            (mj_kinematics via sspp.h:139-143, utility.h:149-175)
 //   K4 collision   moving geoms against the scene primitives                 (mj_collision via sspp.h:144, Collision.h:84-103)
 //   K5 reduce      arc length, collision and penalty sums per candidate      (sspp.h:152-169, tsp_evaluator.h:17-32)
-//   K6 elites      bitonic sort of (cost,index) keys in the last CTA, CES weights (sspp.h:171-192, tsp_elites.h:13-32)
+//   K6 elites      order the (cost,index) keys, CES weights                  (sspp.h:171-192, tsp_elites.h:13-32)
 //   K7 update      weighted mean / EMA variance / sigma adaptation           (tsp_distribution.h:31-83)
 //
-// Work decomposition: a CTA owns `cand_per_cta` consecutive candidates of one query; its threads
-// stride over the flattened (candidate, collocation point) items, so every lane carries one
-// full FK + collision evaluation at a time whatever M is.  Per-point results go to shared
-// memory, one warp per candidate then reduces them in a fixed order (lane-strided partial sums,
-// xor butterfly) that the oracles restate.  The last CTA of a query to finish (atomic ticket)
-// sorts the keys and updates the sampling distribution, so an iteration is a single launch;
-// queries small enough for one CTA can run many iterations inside one launch.
+// Two shapes of the same kernel:
+//   coop = 1  persistent cooperative grid (as many CTAs as are co-resident, looping over candidate
+//             tiles).  Phase A scores the tiles; after a grid barrier phase B ranks every key against
+//             all keys of its query (grid-wide counting rank: each CTA stages the query's keys in
+//             shared memory chunk by chunk and counts, for the keys it owns, how many are smaller),
+//             which yields the sorted order without a serial sort; after a second barrier phase C
+//             updates the distribution with one WARP per (query, distribution element).
+//   coop = 0  one CTA per query (the ICRA shape: 17 candidates x 40 points): bitonic sort in shared
+//             memory and the update by the same CTA; all iterations of a plan run inside one launch.
+// A CTA tile owns `cand_per_cta` consecutive candidates of one query; its threads stride over the
+// flattened (candidate, collocation point) items, so a lane carries one full FK + collision
+// evaluation whatever M is.  Per-point results go to shared memory; one warp per candidate reduces
+// them in a fixed order (lane-strided partial sums, xor butterfly) that the oracles restate.
 #include "sspp_kernels.h"
 
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
+
+namespace cg = cooperative_groups;
 
 namespace sspp {
 using namespace ssppm;
@@ -34,17 +44,196 @@ struct SmemQ {      // planned coordinates of the point a thread is scoring, [d]
   __device__ __forceinline__ float get(int d) const { return base[d * T + tid]; }
 };
 
-__device__ __forceinline__ float warp_strided_sum(const float* v, int n, int lane) {
-  float acc = 0.0f;
-  for (int i = lane; i < n; i += 32) acc += v[i];
-#pragma unroll
-  for (int m = 16; m > 0; m >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, m);
-  return acc;
-}
 __device__ __forceinline__ float warp_butterfly(float acc) {
 #pragma unroll
   for (int m = 16; m > 0; m >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, m);
   return acc;
+}
+__device__ __forceinline__ float warp_strided_sum(const float* v, int n, int lane) {
+  float acc = 0.0f;
+  for (int i = lane; i < n; i += 32) acc += v[i];
+  return warp_butterfly(acc);
+}
+
+__device__ __forceinline__ float key_cost(unsigned long long key) {
+  unsigned ob = (unsigned)(key >> 32);
+  ob = (ob & 0x80000000u) ? (ob & 0x7FFFFFFFu) : ~ob;
+  return __uint_as_float(ob);
+}
+__device__ __forceinline__ bool key_success(unsigned long long key) { return (unsigned)(key >> 32) != 0xFFFFFFFFu; }
+
+// shared memory carve-up of the scoring phase (all 4-byte words)
+struct Smem {
+  unsigned long long* keys;   // coop == 0 only: n_pad sort keys
+  float *psi_col, *psi_arc, *X, *q, *cc, *cw, *seg, *qs, *xf;
+  int *first_col, *first_arc;
+};
+__device__ __forceinline__ Smem carve(unsigned char* raw, const ScoreConfig& c, const IterParams& P, int T) {
+  Smem s;
+  s.keys = reinterpret_cast<unsigned long long*>(raw);
+  float* sm = reinterpret_cast<float*>(raw) + (P.coop ? 0 : 2 * P.n_pad);
+  const int CT = P.cand_per_cta, wc = P.w_col | 1, wa = P.w_arc | 1;
+  s.psi_col = sm;   sm += c.Mc * wc;
+  s.psi_arc = sm;   sm += c.arc_same ? 0 : c.Ma * wa;
+  s.first_col = reinterpret_cast<int*>(sm); sm += c.Mc;
+  s.first_arc = reinterpret_cast<int*>(sm); sm += c.arc_same ? 0 : c.Ma;
+  s.X = sm;         sm += CT * c.K * c.D;
+  s.q = sm;         sm += CT * P.mq * c.D;
+  s.cc = sm;        sm += CT * c.Mc;     // collision cost per point
+  s.cw = sm;        sm += CT * c.Mc;     // collision cost + penalty per point
+  s.seg = sm;       sm += CT * P.mq;     // segment lengths
+  s.qs = sm;        sm += c.D * T;       // coordinates of the point in flight
+  s.xf = sm;                              // link frames (only when !chain)
+  return s;
+}
+__device__ __forceinline__ void load_basis(const Smem& s, const ScoreConfig& c, const IterParams& P, int tid, int T) {
+  const int wc = P.w_col | 1, wa = P.w_arc | 1;
+  for (int e = tid; e < c.Mc * P.w_col; e += T) s.psi_col[(e / P.w_col) * wc + (e % P.w_col)] = P.psi_col[e];
+  for (int e = tid; e < c.Mc; e += T) s.first_col[e] = P.first_col[e];
+  if (!c.arc_same) {
+    for (int e = tid; e < c.Ma * P.w_arc; e += T) s.psi_arc[(e / P.w_arc) * wa + (e % P.w_arc)] = P.psi_arc[e];
+    for (int e = tid; e < c.Ma; e += T) s.first_arc[e] = P.first_arc[e];
+  }
+}
+
+// Phase A for one tile: candidates [c0, c0 + nc) of `query`.  Ends with the per-candidate outputs
+// and raw keys in global memory; no trailing barrier.
+__device__ __forceinline__ void score_tile(const DevModel& M, const IterParams& P, const Smem& s, int query, int c0, int nc,
+                                           uint32_t iter) {
+  const ScoreConfig& c = P.cfg;
+  const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarp = T >> 5;
+  const int D = c.D, K = c.K, Mc = c.Mc, Ma = c.Ma, Mq = P.mq;
+  const int nfd = c.n_free * D;
+  const int Marc = c.arc_same ? Mc : Ma;
+  const int wc = P.w_col | 1, wa = P.w_arc | 1;
+  const float* mean = P.mean + (size_t)query * nfd;
+  const float* sigma = P.sigma + (size_t)query * nfd;
+  const float* best = P.best + (size_t)query * nfd;
+  const float* base = P.base + (size_t)query * K * D;
+  const size_t qn = (size_t)query * c.n_cand;
+  SmemXF xf{s.xf, T, tid};
+  SmemQ qa{s.qs, T, tid};
+  const int best_ok = c.include_best ? P.best_valid[query] : 0;
+  // ---- K1: candidate point matrices ----
+  for (int e = tid; e < nc * K * D; e += T) s.X[e] = base[e % (K * D)];
+  __syncthreads();
+  for (int e = tid; e < nc * nfd; e += T) {
+    const int cl = e / nfd, t = e - cl * nfd;
+    const int cand = c0 + cl, gcand = P.cand_offset + cand;
+    const int kind = candidate_kind(c, gcand, best_ok);
+    const float v = candidate_param(c, P.seed, iter, (uint32_t)query, gcand, kind, t, mean, sigma, best);
+    s.X[(cl * K + c.free_begin) * D + t] = v;
+    P.params[(qn + cand) * nfd + t] = v;
+  }
+  __syncthreads();
+  // ---- K2-K4: spline point, kinematics, collision per (candidate, point) item ----
+  for (int w = tid; w < nc * Mc; w += T) {
+    const int cl = w / Mc, m = w - cl * Mc;
+    const float* row = s.psi_col + m * wc;
+    const int first = s.first_col[m];
+    const float* X = s.X + cl * K * D;
+    for (int d = 0; d < D; ++d) {
+      const float acc = spline_coord(row, first, P.w_col, X, D, d);
+      s.qs[d * T + tid] = acc;
+      if (c.arc_same) s.q[(cl * Mq + m) * D + d] = acc;
+    }
+    float cc = 0.0f, cw = 0.0f;
+    if (m >= c.col_first) {
+      cc = point_collision_cost(M, qa, xf);
+      cw = cc + point_penalty(c, qa);
+    }
+    s.cc[cl * Mc + m] = cc;
+    s.cw[cl * Mc + m] = cw;
+  }
+  if (!c.arc_same) {
+    for (int w = tid; w < nc * Ma; w += T) {
+      const int cl = w / Ma, m = w - cl * Ma;
+      const float* row = s.psi_arc + m * wa;
+      const int first = s.first_arc[m];
+      const float* X = s.X + cl * K * D;
+      for (int d = 0; d < D; ++d) s.q[(cl * Mq + m) * D + d] = spline_coord(row, first, P.w_arc, X, D, d);
+    }
+  }
+  __syncthreads();
+  // ---- K5: segment lengths, then one warp per candidate reduces ----
+  for (int w = tid; w < nc * (Marc - 1); w += T) {
+    const int cl = w / (Marc - 1), m = 1 + (w - cl * (Marc - 1));
+    const float* a = s.q + (cl * Mq + m) * D;
+    float s2 = 0.0f;
+    for (int d = 0; d < D; ++d) { const float df = a[d] - a[d - D]; s2 = fmaf(df, df, s2); }
+    s.seg[cl * Mq + m - 1] = sqrtf(s2);
+  }
+  __syncthreads();
+  for (int cl = warp; cl < nc; cl += nwarp) {
+    const float L = warp_strided_sum(s.seg + cl * Mq, Marc - 1, lane);
+    const float Cnf = warp_strided_sum(s.cc + cl * Mc + c.col_first, Mc - c.col_first, lane);
+    const float Cwf = warp_strided_sum(s.cw + cl * Mc + c.col_first, Mc - c.col_first, lane);
+    if (lane == 0) {
+      const int cand = c0 + cl;
+      const int kind = candidate_kind(c, P.cand_offset + cand, best_ok);
+      const int st = (kind == CK_ABSENT) ? ST_ABSENT : ((Cnf == 0.0f) ? ST_CONVERGED : ST_FAILED);
+      const float cost = fmaf(c.w_collision, Cwf, L);
+      P.L[qn + cand] = L; P.Cnf[qn + cand] = Cnf; P.Cwf[qn + cand] = Cwf; P.cost[qn + cand] = cost;
+      P.status[qn + cand] = (uint8_t)st;
+      P.keys_raw[(size_t)query * P.n_pad + cand] = sort_key(cost, st, (uint32_t)(P.cand_offset + cand));
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// K6/K7 arithmetic for one distribution element t of one query, executed by ONE WARP.
+//   keys: sorted keys of the query; get_param(candidate index, t) -> sampled value.
+// CES log-weights w_j = (ln(k + 1/2) - ln(j + 1)) / sum (tsp_elites.h:24-32) are recomputed on the
+// fly: lane l owns j = l, l + 32, ... in every pass, partial sums meet in an xor butterfly.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ float ces_weight_sum(int k, float lk, int lane) {
+  float acc = 0.0f;
+  for (int j = lane; j < k; j += 32) acc += lk - log_poly((float)j + 1.0f);
+  return warp_butterfly(acc);
+}
+
+template <class ParamGetter>
+__device__ __forceinline__ void update_element(const ScoreConfig& c, const unsigned long long* keys, int k, float lk, float sumw,
+                                               int t, float* mean, float* sigma, ParamGetter get_param, int lane) {
+  const int d = t % c.D;
+  float acc = 0.0f;
+  for (int j = lane; j < k; j += 32) {
+    const float w = (lk - log_poly((float)j + 1.0f)) / sumw;
+    acc = fmaf(w, get_param((unsigned)(keys[j] & 0xFFFFFFFFu), t), acc);
+  }
+  const float em = warp_butterfly(acc);
+  const float m0 = mean[t];
+  float nm = fmaf(c.mean_lr, em - m0, m0);
+  if (c.mode == MODE_TASK && d == 2) nm = fmaxf(nm, c.dist_zmin);
+  nm = fminf(fmaxf(nm, c.lo[d]), c.hi[d]);
+  const bool wrap = (c.mode == MODE_TASK && d == 3 && c.lo[3] != c.hi[3]);
+  float vacc = 0.0f;
+  for (int j = lane; j < k; j += 32) {
+    const float w = (lk - log_poly((float)j + 1.0f)) / sumw;
+    const float v = get_param((unsigned)(keys[j] & 0xFFFFFFFFu), t);
+    const float df = wrap ? wrap_angle_diff(v, nm, c.lo[3], c.hi[3]) : v - nm;
+    vacc = fmaf(w, df * df, vacc);
+  }
+  const float var = warp_butterfly(vacc);
+  const float s0 = sigma[t];
+  const float blend = fmaf(c.var_beta, var, (1.0f - c.var_beta) * (s0 * s0));
+  float sg = clamp_sigma(c, sqrtf(blend));
+  sg = clamp_sigma(c, sg * c.dec);               // adapt(true)
+  if (lane == 0) { mean[t] = nm; sigma[t] = sg; }
+}
+
+struct StoredParams {
+  const float* params; int nfd; unsigned offset;
+  __device__ __forceinline__ float operator()(unsigned idx, int t) const { return params[(size_t)(idx - offset) * nfd + t]; }
+};
+
+// per-query scalars written once the order is known (thread-level; caller picks the thread)
+__device__ __forceinline__ void write_best(const IterParams& P, int query, unsigned long long k0) {
+  if (key_success(k0)) {
+    P.best_idx[query] = (int)(unsigned)(k0 & 0xFFFFFFFFu);
+    P.best_cost[query] = key_cost(k0);
+    P.any_success[query] = 1;
+  } else { P.best_idx[query] = -1; P.best_cost[query] = __int_as_float(0x7F800000); }
 }
 
 // ascending bitonic sort of n_pad (power of two) 64-bit keys by the whole CTA
@@ -65,20 +254,19 @@ __device__ void block_bitonic_sort(unsigned long long* keys, int n_pad) {
   }
 }
 
-// Elite selection + distribution update for one query, executed by one CTA.
-//   keys       sorted in place (shared or global memory), n_pad entries, unused tail = ~0
-//   get_param  (global candidate index, element t) -> sampled value
+// K6 + K7 of one query by one CTA (coop == 0, and the merge kernel): sorts `keys` in place
+// (shared or global memory), then updates; get_param as in update_element.
 template <class ParamGetter>
-__device__ void elites_and_update(const ScoreConfig& c, unsigned long long* keys, int n_pad, float* elite_w,
-                                  float* mean, float* sigma, float* best, int* best_valid,
-                                  int* n_success_out, int* n_elite_out, int* best_idx_out, float* best_cost_out,
-                                  int* any_success, ParamGetter get_param, int* s_int, float* s_flt) {
+__device__ void cta_elites_and_update(const ScoreConfig& c, unsigned long long* keys, int n_pad, float* elite_w, float* mean,
+                                      float* sigma, float* best, int* best_valid, int* n_success_out, int* n_elite_out,
+                                      int* best_idx_out, float* best_cost_out, int* any_success, ParamGetter get_param,
+                                      int* s_int) {
   const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarp = T >> 5;
   block_bitonic_sort(keys, n_pad);
   if (tid == 0) s_int[0] = 0;
   __syncthreads();
   int cnt = 0;
-  for (int i = tid; i < n_pad; i += T) cnt += ((unsigned)(keys[i] >> 32) != 0xFFFFFFFFu) ? 1 : 0;
+  for (int i = tid; i < n_pad; i += T) cnt += key_success(keys[i]) ? 1 : 0;
   cnt = __reduce_add_sync(0xFFFFFFFFu, cnt);
   if (lane == 0 && cnt) atomicAdd(&s_int[0], cnt);
   __syncthreads();
@@ -87,203 +275,187 @@ __device__ void elites_and_update(const ScoreConfig& c, unsigned long long* keys
   const int nfd = c.n_free * c.D;
   if (tid == 0) {
     *n_success_out = n_succ; *n_elite_out = k;
-    if (n_succ > 0) {
-      const unsigned long long k0 = keys[0];
-      *best_idx_out = (int)(unsigned)(k0 & 0xFFFFFFFFu);
-      unsigned ob = (unsigned)(k0 >> 32);
-      ob = (ob & 0x80000000u) ? (ob & 0x7FFFFFFFu) : ~ob;
-      *best_cost_out = __uint_as_float(ob);
-      *any_success = 1;
-    } else { *best_idx_out = -1; *best_cost_out = __int_as_float(0x7F800000); }
+    const unsigned long long k0 = keys[0];
+    if (n_succ > 0) { *best_idx_out = (int)(unsigned)(k0 & 0xFFFFFFFFu); *best_cost_out = key_cost(k0); *any_success = 1; }
+    else { *best_idx_out = -1; *best_cost_out = __int_as_float(0x7F800000); }
   }
   if (n_succ == 0) {
     if (c.do_update) for (int t = tid; t < nfd; t += T) sigma[t] = clamp_sigma(c, sigma[t] * c.inc);   // adapt(false)
     __syncthreads();
     return;
   }
-  // CES log-weights (tsp_elites.h:24-32)
   const float lk = log_poly((float)k + 0.5f);
-  for (int j = tid; j < k; j += T) elite_w[j] = lk - log_poly((float)j + 1.0f);
-  __syncthreads();
-  if (warp == 0) { const float s = warp_strided_sum(elite_w, k, lane); if (lane == 0) s_flt[0] = s; }
-  __syncthreads();
-  const float sumw = s_flt[0];
-  for (int j = tid; j < k; j += T) elite_w[j] = elite_w[j] / sumw;
-  __syncthreads();
-  if (c.do_update) {
-    for (int t = warp; t < nfd; t += nwarp) {       // one warp per distribution element
-      const int d = t % c.D;
-      float acc = 0.0f;
-      for (int j = lane; j < k; j += 32) acc = fmaf(elite_w[j], get_param((unsigned)(keys[j] & 0xFFFFFFFFu), t), acc);
-      const float em = warp_butterfly(acc);
-      const float m0 = mean[t];
-      float nm = fmaf(c.mean_lr, em - m0, m0);
-      if (c.mode == MODE_TASK && d == 2) nm = fmaxf(nm, c.dist_zmin);
-      nm = fminf(fmaxf(nm, c.lo[d]), c.hi[d]);
-      const bool wrap = (c.mode == MODE_TASK && d == 3 && c.lo[3] != c.hi[3]);
-      float vacc = 0.0f;
-      for (int j = lane; j < k; j += 32) {
-        const float v = get_param((unsigned)(keys[j] & 0xFFFFFFFFu), t);
-        const float df = wrap ? wrap_angle_diff(v, nm, c.lo[3], c.hi[3]) : v - nm;
-        vacc = fmaf(elite_w[j], df * df, vacc);
-      }
-      const float var = warp_butterfly(vacc);
-      const float s0 = sigma[t];
-      const float blend = fmaf(c.var_beta, var, (1.0f - c.var_beta) * (s0 * s0));
-      float sg = clamp_sigma(c, sqrtf(blend));
-      sg = clamp_sigma(c, sg * c.dec);               // adapt(true)
-      if (lane == 0) { mean[t] = nm; sigma[t] = sg; }
-    }
-  }
-  // forward the best candidate (last_best_)
+  const float sumw = ces_weight_sum(k, lk, lane);          // every warp computes the same number
+  for (int j = tid; j < k; j += T) elite_w[j] = (lk - log_poly((float)j + 1.0f)) / sumw;
+  // the best candidate is read before any element is updated (its rows are not state, but keep the order of v1)
   const unsigned bi = (unsigned)(keys[0] & 0xFFFFFFFFu);
+  if (c.do_update)
+    for (int t = warp; t < nfd; t += nwarp) update_element(c, keys, k, lk, sumw, t, mean, sigma, get_param, lane);
   for (int t = tid; t < nfd; t += T) best[t] = get_param(bi, t);
   if (tid == 0) *best_valid = 1;
   __syncthreads();
 }
 
-struct StoredParams {
-  const float* params; int nfd;
-  __device__ __forceinline__ float operator()(unsigned idx, int t) const { return params[(size_t)idx * nfd + t]; }
-};
-
-__global__ void __launch_bounds__(256, 2)
-sspp_iterate_kernel(const __grid_constant__ DevModel M, const __grid_constant__ IterParams P) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ int s_int[4];
-  __shared__ float s_flt[4];
+// ---- coop phase B: grid-wide counting rank -------------------------------------------------
+// Items are the (query, candidate) keys, split evenly over the CTAs.  For its keys of one query a CTA
+// stages the query's raw keys in shared memory, `chunk` at a time, and counts the smaller ones:
+// 4 owned keys per warp pass, lanes stride over the chunk.  rank = position in the sorted order
+// (keys are unique: they embed the candidate index).
+__device__ void rank_phase(const IterParams& P, unsigned char* smem_raw) {
   const ScoreConfig& c = P.cfg;
   const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarp = T >> 5;
-  const int query = blockIdx.y;
-  const int c0 = blockIdx.x * P.cand_per_cta;
-  const int nc = min(P.cand_per_cta, c.n_cand - c0);
-  const int D = c.D, K = c.K, Mc = c.Mc, Ma = c.Ma, Kp = P.k_pad, Mq = P.mq, CT = P.cand_per_cta;
-  const int nfd = c.n_free * D;
-  const int Marc = c.arc_same ? Mc : Ma;
-
-  // ---- shared memory carve-up (all float) ----
-  float* sm = reinterpret_cast<float*>(smem_raw);
-  float* s_psi_col = sm;              sm += Mc * Kp;
-  float* s_psi_arc = sm;              sm += c.arc_same ? 0 : Ma * Kp;
-  float* s_X = sm;                    sm += CT * K * D;
-  float* s_q = sm;                    sm += CT * Mq * D;
-  float* s_cc = sm;                   sm += CT * Mc;     // collision cost per point
-  float* s_cw = sm;                   sm += CT * Mc;     // collision cost + penalty per point
-  float* s_seg = sm;                  sm += CT * Mq;     // segment lengths
-  float* s_qs = sm;                   sm += D * T;       // coordinates of the point in flight
-  float* s_xf = sm;                                       // link frames (only when !chain)
-
-  for (int e = tid; e < Mc * K; e += T) s_psi_col[(e / K) * Kp + (e % K)] = P.psi_col[e];
-  if (!c.arc_same) for (int e = tid; e < Ma * K; e += T) s_psi_arc[(e / K) * Kp + (e % K)] = P.psi_arc[e];
-
-  float* mean = P.mean + (size_t)query * nfd;
-  float* sigma = P.sigma + (size_t)query * nfd;
-  float* best = P.best + (size_t)query * nfd;
-  const float* base = P.base + (size_t)query * K * D;
-  const size_t qn = (size_t)query * c.n_cand;
-  SmemXF xf{s_xf, T, tid};
-  SmemQ qa{s_qs, T, tid};
-
-  for (int it = 0; it < P.n_inner; ++it) {
-    const uint32_t iter = P.iter0 + (uint32_t)it;
-    const int best_ok = c.include_best ? P.best_valid[query] : 0;
-    // ---- K1: candidate point matrices ----
-    for (int e = tid; e < nc * K * D; e += T) s_X[e] = base[e % (K * D)];
-    __syncthreads();
-    for (int e = tid; e < nc * nfd; e += T) {
-      const int cl = e / nfd, t = e - cl * nfd;
-      const int cand = c0 + cl, gcand = P.cand_offset + cand;
-      const int kind = candidate_kind(c, gcand, best_ok);
-      const float v = candidate_param(c, P.seed, iter, (uint32_t)query, gcand, kind, t, mean, sigma, best);
-      s_X[(cl * K + c.free_begin) * D + t] = v;
-      P.params[(qn + cand) * nfd + t] = v;
-    }
-    __syncthreads();
-    // ---- K2-K4: spline point, kinematics, collision per (candidate, point) item ----
-    for (int w = tid; w < nc * Mc; w += T) {
-      const int cl = w / Mc, m = w - cl * Mc;
-      const float* psi = s_psi_col + m * Kp;
-      const float* X = s_X + cl * K * D;
-      for (int d = 0; d < D; ++d) {
-        float acc = 0.0f;
-        for (int k = 0; k < K; ++k) acc = fmaf(psi[k], X[k * D + d], acc);
-        s_qs[d * T + tid] = acc;
-        if (c.arc_same) s_q[(cl * Mq + m) * D + d] = acc;
-      }
-      float cc = 0.0f, cw = 0.0f;
-      if (m >= c.col_first) {
-        cc = point_collision_cost(M, qa, xf);
-        cw = cc + point_penalty(c, qa);
-      }
-      s_cc[cl * Mc + m] = cc;
-      s_cw[cl * Mc + m] = cw;
-    }
-    if (!c.arc_same) {
-      for (int w = tid; w < nc * Ma; w += T) {
-        const int cl = w / Ma, m = w - cl * Ma;
-        const float* psi = s_psi_arc + m * Kp;
-        const float* X = s_X + cl * K * D;
-        for (int d = 0; d < D; ++d) {
-          float acc = 0.0f;
-          for (int k = 0; k < K; ++k) acc = fmaf(psi[k], X[k * D + d], acc);
-          s_q[(cl * Mq + m) * D + d] = acc;
+  const int N = c.n_cand, nfd = c.n_free * c.D;
+  const long long total = (long long)P.n_query * N;
+  const long long per = (total + gridDim.x - 1) / gridDim.x;
+  const long long lo_item = per * blockIdx.x, hi_item = min(total, lo_item + per);
+  unsigned long long* s_chunk = reinterpret_cast<unsigned long long*>(smem_raw);
+  unsigned long long* s_mine = s_chunk + P.rank_chunk;
+  int* s_cnt = reinterpret_cast<int*>(s_mine + per);
+  __shared__ int s_succ;
+  for (long long item = lo_item; item < hi_item;) {
+    const int query = (int)(item / N);
+    const int i0 = (int)(item - (long long)query * N);
+    const int nmine = (int)min((long long)(N - i0), hi_item - item);
+    const unsigned long long* raw = P.keys_raw + (size_t)query * P.n_pad;
+    unsigned long long* sorted = P.keys + (size_t)query * P.n_pad;
+    for (int a = tid; a < nmine; a += T) { s_mine[a] = raw[i0 + a]; s_cnt[a] = 0; }
+    if (tid == 0) s_succ = 0;
+    for (int cs = 0; cs < N; cs += P.rank_chunk) {
+      const int cn = min(P.rank_chunk, N - cs);
+      __syncthreads();
+      for (int j = tid; j < cn; j += T) s_chunk[j] = __ldcg(raw + cs + j);
+      __syncthreads();
+      for (int a0 = warp * 4; a0 < nmine; a0 += nwarp * 4) {
+        const unsigned long long k0 = s_mine[a0], k1 = (a0 + 1 < nmine) ? s_mine[a0 + 1] : 0ull,
+                                 k2 = (a0 + 2 < nmine) ? s_mine[a0 + 2] : 0ull, k3 = (a0 + 3 < nmine) ? s_mine[a0 + 3] : 0ull;
+        int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+        for (int j = lane; j < cn; j += 32) {
+          const unsigned long long x = s_chunk[j];
+          c0 += (x < k0); c1 += (x < k1); c2 += (x < k2); c3 += (x < k3);
+        }
+        c0 = __reduce_add_sync(0xFFFFFFFFu, c0); c1 = __reduce_add_sync(0xFFFFFFFFu, c1);
+        c2 = __reduce_add_sync(0xFFFFFFFFu, c2); c3 = __reduce_add_sync(0xFFFFFFFFu, c3);
+        if (lane == 0) {
+          s_cnt[a0] += c0;
+          if (a0 + 1 < nmine) s_cnt[a0 + 1] += c1;
+          if (a0 + 2 < nmine) s_cnt[a0 + 2] += c2;
+          if (a0 + 3 < nmine) s_cnt[a0 + 3] += c3;
         }
       }
     }
     __syncthreads();
-    // ---- K5: segment lengths, then one warp per candidate reduces ----
-    for (int w = tid; w < nc * (Marc - 1); w += T) {
-      const int cl = w / (Marc - 1), m = 1 + (w - cl * (Marc - 1));
-      const float* a = s_q + (cl * Mq + m) * D;
-      float s2 = 0.0f;
-      for (int d = 0; d < D; ++d) { const float df = a[d] - a[d - D]; s2 = fmaf(df, df, s2); }
-      s_seg[cl * Mq + m - 1] = sqrtf(s2);
-    }
-    __syncthreads();
-    for (int cl = warp; cl < nc; cl += nwarp) {
-      const float L = warp_strided_sum(s_seg + cl * Mq, Marc - 1, lane);
-      const float Cnf = warp_strided_sum(s_cc + cl * Mc + c.col_first, Mc - c.col_first, lane);
-      const float Cwf = warp_strided_sum(s_cw + cl * Mc + c.col_first, Mc - c.col_first, lane);
-      if (lane == 0) {
-        const int cand = c0 + cl;
-        const int kind = candidate_kind(c, P.cand_offset + cand, best_ok);
-        const int st = (kind == CK_ABSENT) ? ST_ABSENT : ((Cnf == 0.0f) ? ST_CONVERGED : ST_FAILED);
-        const float cost = fmaf(c.w_collision, Cwf, L);
-        P.L[qn + cand] = L; P.Cnf[qn + cand] = Cnf; P.Cwf[qn + cand] = Cwf; P.cost[qn + cand] = cost;
-        P.status[qn + cand] = (uint8_t)st;
-        P.keys[(size_t)query * P.n_pad + cand] = sort_key(cost, st, (uint32_t)(P.cand_offset + cand));
+    int succ_hi = 0;
+    for (int a = tid; a < nmine; a += T) {
+      const unsigned long long key = s_mine[a];
+      const int r = s_cnt[a];
+      sorted[r] = key;
+      if (key_success(key)) succ_hi = max(succ_hi, r + 1);
+      if (r == 0 && !P.sort_only) {                       // best candidate of the query (last_best_, tsp_planner.h:131-138)
+        write_best(P, query, key);
+        if (key_success(key)) {
+          const float* src = P.params + ((size_t)query * N + (i0 + a)) * nfd;
+          float* dst = P.best + (size_t)query * nfd;
+          for (int t = 0; t < nfd; ++t) dst[t] = src[t];
+          P.best_valid[query] = 1;
+        }
       }
     }
-    // ---- K6/K7 in the last CTA of this query ----
-    __threadfence();
+    if (i0 == 0) for (int i = N + tid; i < P.n_pad; i += T) sorted[i] = ~0ull;
+    succ_hi = __reduce_max_sync(0xFFFFFFFFu, succ_hi);
+    if (lane == 0 && succ_hi) atomicMax(&s_succ, succ_hi);
     __syncthreads();
-    if (tid == 0) s_int[1] = (atomicAdd(&P.ticket[query], 1u) == (unsigned)(P.ctas_per_query - 1)) ? 1 : 0;
-    __syncthreads();
-    if (s_int[1]) {
-      __threadfence();
-      unsigned long long* gkeys = P.keys + (size_t)query * P.n_pad;
-      unsigned long long* keys = gkeys;
-      if (P.sort_in_smem) {
-        keys = reinterpret_cast<unsigned long long*>(smem_raw);
-        for (int i = tid; i < P.n_pad; i += T) keys[i] = (i < c.n_cand) ? __ldcg(gkeys + i) : ~0ull;
-      } else {
-        for (int i = c.n_cand + tid; i < P.n_pad; i += T) gkeys[i] = ~0ull;
+    if (tid == 0 && s_succ) atomicMax(&P.succ_acc[query], s_succ);   // n_success = rank of the last success + 1
+    item += nmine;
+  }
+}
+
+// ---- coop phase C: one warp per (query, distribution element); element nfd = the query's scalars ----
+__device__ void update_phase(const IterParams& P) {
+  const ScoreConfig& c = P.cfg;
+  const int lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+  const int nfd = c.n_free * c.D, N = c.n_cand;
+  const int gw = blockIdx.x * nwarp + (threadIdx.x >> 5), gstride = gridDim.x * nwarp;
+  const int n_items = P.n_query * (nfd + 1);
+  for (int item = gw; item < n_items; item += gstride) {
+    const int query = item / (nfd + 1), t = item - query * (nfd + 1);
+    const int n_succ = __ldcg(P.succ_acc + query);
+    const int k = elite_count(n_succ, c.elite_frac);
+    const unsigned long long* keys = P.keys + (size_t)query * P.n_pad;
+    float* mean = P.mean + (size_t)query * nfd;
+    float* sigma = P.sigma + (size_t)query * nfd;
+    if (t == nfd) {                     // scalars + elite weights of the query
+      if (lane == 0) { P.n_success[query] = n_succ; P.n_elite[query] = k; }
+      if (n_succ > 0) {
+        const float lk = log_poly((float)k + 0.5f);
+        const float sumw = ces_weight_sum(k, lk, lane);
+        float* ew = P.elite_w + (size_t)query * P.n_pad;
+        for (int j = lane; j < k; j += 32) ew[j] = (lk - log_poly((float)j + 1.0f)) / sumw;
       }
+      continue;
+    }
+    if (!c.do_update) continue;
+    if (n_succ == 0) { if (lane == 0) sigma[t] = clamp_sigma(c, sigma[t] * c.inc); continue; }   // adapt(false)
+    const float lk = log_poly((float)k + 0.5f);
+    const float sumw = ces_weight_sum(k, lk, lane);
+    StoredParams gp{P.params + (size_t)query * N * nfd, nfd, (unsigned)P.cand_offset};
+    update_element(c, keys, k, lk, sumw, t, mean, sigma, gp, lane);
+  }
+}
+
+template <bool COOP>
+__global__ void __launch_bounds__(256, 2)
+sspp_iterate_kernel(const __grid_constant__ DevModel M, const __grid_constant__ IterParams P) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ int s_int[4];
+  const ScoreConfig& c = P.cfg;
+  const int tid = threadIdx.x, T = blockDim.x;
+  const int nfd = c.n_free * c.D;
+  const Smem s = carve(smem_raw, c, P, T);
+  if (!COOP) {
+    // one CTA per query: every iteration of the launch stays inside this CTA
+    const int query = blockIdx.x;
+    load_basis(s, c, P, tid, T);
+    for (int it = 0; it < P.n_inner; ++it) {
+      score_tile(M, P, s, query, 0, c.n_cand, P.iter0 + (uint32_t)it);
+      __syncthreads();                                   // raw keys were written by this CTA: visible after the barrier
+      unsigned long long* keys = s.keys;
+      const unsigned long long* raw = P.keys_raw + (size_t)query * P.n_pad;
+      unsigned long long* sorted = P.keys + (size_t)query * P.n_pad;
+      for (int i = tid; i < P.n_pad; i += T) keys[i] = (i < c.n_cand) ? raw[i] : ~0ull;
       __syncthreads();
-      StoredParams gp{P.params + qn * nfd, nfd};
       if (P.sort_only) block_bitonic_sort(keys, P.n_pad);
-      else elites_and_update(c, keys, P.n_pad, P.elite_w + (size_t)query * P.n_pad, mean, sigma, best, P.best_valid + query,
-                        P.n_success + query, P.n_elite + query, P.best_idx + query, P.best_cost + query,
-                        P.any_success + query, gp, s_int, s_flt);
-      if (P.sort_in_smem) for (int i = tid; i < P.n_pad; i += T) gkeys[i] = keys[i];
-      if (tid == 0) P.ticket[query] = 0u;
-      __syncthreads();
-      if (P.sort_in_smem && P.n_inner > 1) {   // the key buffer aliases the basis matrices: reload them
-        for (int e = tid; e < Mc * K; e += T) s_psi_col[(e / K) * Kp + (e % K)] = P.psi_col[e];
-        if (!c.arc_same) for (int e = tid; e < Ma * K; e += T) s_psi_arc[(e / K) * Kp + (e % K)] = P.psi_arc[e];
+      else {
+        StoredParams gp{P.params + (size_t)query * c.n_cand * nfd, nfd, (unsigned)P.cand_offset};
+        cta_elites_and_update(c, keys, P.n_pad, P.elite_w + (size_t)query * P.n_pad, P.mean + (size_t)query * nfd,
+                              P.sigma + (size_t)query * nfd, P.best + (size_t)query * nfd, P.best_valid + query,
+                              P.n_success + query, P.n_elite + query, P.best_idx + query, P.best_cost + query,
+                              P.any_success + query, gp, s_int);
       }
+      for (int i = tid; i < P.n_pad; i += T) sorted[i] = keys[i];
+      __syncthreads();
     }
-    __syncthreads();
+    return;
+  }
+  cg::grid_group grid = cg::this_grid();
+  for (int it = 0; it < P.n_inner; ++it) {
+    // ---- phase A: score the tiles ----
+    load_basis(s, c, P, tid, T);                         // phase B reuses this shared memory
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+      const int query = tile / P.ctas_per_query;
+      const int c0 = (tile - query * P.ctas_per_query) * P.cand_per_cta;
+      const int nc = min(P.cand_per_cta, c.n_cand - c0);
+      if (c0 == 0 && tid == 0) P.succ_acc[query] = 0;
+      score_tile(M, P, s, query, c0, nc, P.iter0 + (uint32_t)it);
+      __syncthreads();
+    }
+    grid.sync();
+    // ---- phase B: order the keys ----
+    rank_phase(P, smem_raw);
+    if (P.sort_only) { if (it + 1 < P.n_inner) grid.sync(); continue; }
+    grid.sync();
+    // ---- phase C: distribution update ----
+    update_phase(P);
+    if (it + 1 < P.n_inner) grid.sync();
   }
 }
 
@@ -298,9 +470,7 @@ struct RegenParams {
 
 __global__ void __launch_bounds__(1024, 1)
 sspp_merge_update_kernel(const __grid_constant__ MergeParams P) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_int[4];
-  __shared__ float s_flt[4];
   __shared__ float s_mean0[MAX_K * MAX_DOF], s_sigma0[MAX_K * MAX_DOF], s_best0[MAX_K * MAX_DOF];
   const ScoreConfig& c = P.cfg;
   const int tid = threadIdx.x, T = blockDim.x;
@@ -309,8 +479,8 @@ sspp_merge_update_kernel(const __grid_constant__ MergeParams P) {
   for (int i = P.n_keys + tid; i < P.n_pad; i += T) P.keys[i] = ~0ull;
   __syncthreads();
   RegenParams gp{&c, P.seed, P.iter, s_mean0, s_sigma0, s_best0, c.include_best ? *P.best_valid : 0};
-  elites_and_update(c, P.keys, P.n_pad, P.elite_w, P.mean, P.sigma, P.best, P.best_valid, P.n_success, P.n_elite,
-                    P.best_idx, P.best_cost, P.any_success, gp, s_int, s_flt);
+  cta_elites_and_update(c, P.keys, P.n_pad, P.elite_w, P.mean, P.sigma, P.best, P.best_valid, P.n_success, P.n_elite,
+                        P.best_idx, P.best_cost, P.any_success, gp, s_int);
 }
 
 __global__ void __launch_bounds__(128)
@@ -354,26 +524,44 @@ cudaError_t launch_fma_probe(float* sink, int blocks, int threads, int iters, cu
 
 size_t iterate_smem_bytes(const DevModel& M, const IterParams& P, int threads) {
   const ScoreConfig& c = P.cfg;
-  size_t f = (size_t)c.Mc * P.k_pad + (c.arc_same ? 0 : (size_t)c.Ma * P.k_pad);
+  const int wc = P.w_col | 1, wa = P.w_arc | 1;
+  size_t f = (size_t)c.Mc * (wc + 1) + (c.arc_same ? 0 : (size_t)c.Ma * (wa + 1));
   f += (size_t)P.cand_per_cta * c.K * c.D;
   f += (size_t)P.cand_per_cta * P.mq * c.D;
   f += (size_t)P.cand_per_cta * c.Mc * 2;
   f += (size_t)P.cand_per_cta * P.mq;
   f += (size_t)c.D * threads;
   if (!M.chain) f += (size_t)M.n_mbody * 12 * threads;
+  if (!P.coop) f += 2 * (size_t)P.n_pad;
   return f * sizeof(float);
 }
 
-cudaError_t launch_iterate(const DevModel& M, const IterParams& P, int threads, size_t smem_bytes, cudaStream_t stream) {
-  static size_t configured = 0;
-  if (smem_bytes > configured) {
-    cudaError_t e = cudaFuncSetAttribute(sspp_iterate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+namespace {
+template <bool COOP>
+cudaError_t set_smem(size_t smem_bytes) {   // per device / context, so no caching across calls
+  if (smem_bytes <= 48 * 1024) return cudaSuccess;
+  return cudaFuncSetAttribute(sspp_iterate_kernel<COOP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+}
+}  // namespace
+
+cudaError_t iterate_occupancy(int threads, size_t smem_bytes, int* ctas_per_sm) {
+  cudaError_t e = set_smem<true>(smem_bytes);
+  if (e != cudaSuccess) return e;
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, sspp_iterate_kernel<true>, threads, smem_bytes);
+}
+
+cudaError_t launch_iterate(const DevModel& M, const IterParams& P, int threads, size_t smem_bytes, int grid, cudaStream_t stream) {
+  if (!P.coop) {
+    cudaError_t e = set_smem<false>(smem_bytes);
     if (e != cudaSuccess) return e;
-    configured = smem_bytes;
+    sspp_iterate_kernel<false><<<(unsigned)P.n_tiles, threads, smem_bytes, stream>>>(M, P);
+    return cudaGetLastError();
   }
-  dim3 grid((unsigned)P.ctas_per_query, (unsigned)P.n_query, 1);
-  sspp_iterate_kernel<<<grid, threads, smem_bytes, stream>>>(M, P);
-  return cudaGetLastError();
+  cudaError_t e = set_smem<true>(smem_bytes);
+  if (e != cudaSuccess) return e;
+  void* args[] = {const_cast<DevModel*>(&M), const_cast<IterParams*>(&P)};
+  return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(sspp_iterate_kernel<true>), dim3((unsigned)grid), dim3((unsigned)threads),
+                                     args, smem_bytes, stream);
 }
 
 cudaError_t launch_eval_points(const DevModel& M, int D, const float* pts, int n, float* out, cudaStream_t stream) {

@@ -12,17 +12,21 @@ struct IterParams {
   ssppm::ScoreConfig cfg;
   int n_query;
   int cand_per_cta, ctas_per_query;
-  int n_inner;              // iterations run inside this launch (> 1 only when ctas_per_query == 1)
-  int sort_in_smem;         // keys of one query fit the dynamic shared memory
+  int n_tiles;              // n_query * ctas_per_query
+  int coop;                 // 1: persistent cooperative grid (grid barriers, grid-wide ranking); 0: one CTA per query
+  int n_inner;              // iterations run inside this launch
   int cand_offset;          // global index of local candidate 0 (population sharding), else 0
   int sort_only;            // population shard: sort the local keys, leave elites/update to the merge kernel
-  int n_pad;                // n_cand rounded up to a power of two (bitonic sort length)
-  int k_pad;                // row pitch of the basis matrices in shared memory (odd)
+  int n_pad;                // n_cand rounded up to a power of two (pitch of the key arrays)
+  int rank_chunk;           // keys staged in shared memory per ranking pass (coop)
+  int w_col, w_arc;         // band widths of the collocation matrices
   int mq;                   // pitch (rows) of the per-candidate point buffer: max(Mc, Ma)
   uint32_t iter0;           // iteration counter of the first inner iteration (Philox counter word)
   uint64_t seed;
-  const float* psi_col;     // [Mc][K]  collocation matrix of the collision grid
-  const float* psi_arc;     // [Ma][K]  collocation matrix of the arc-length grid (unused when arc_same)
+  const float* psi_col;     // [Mc][w_col]  banded collocation matrix of the collision grid
+  const int* first_col;     // [Mc]         first column of every row
+  const float* psi_arc;     // [Ma][w_arc]  arc-length grid (unused when arc_same)
+  const int* first_arc;     // [Ma]
   const float* base;        // [Q][K][D] point matrix before the sampled rows are overwritten
   float* mean;              // [Q][n_free*D]
   float* sigma;             // [Q][n_free*D]
@@ -31,18 +35,22 @@ struct IterParams {
   float* params;            // [Q][N][n_free*D] sampled rows of every candidate
   float* L; float* Cnf; float* Cwf; float* cost;   // [Q][N]
   uint8_t* status;          // [Q][N]
-  unsigned long long* keys; // [Q][n_pad] (cost bits << 32 | index), sorted ascending after the launch
+  unsigned long long* keys_raw; // [Q][n_pad] (cost bits << 32 | index) by local candidate index
+  unsigned long long* keys; // [Q][n_pad] the same keys sorted ascending (tail = ~0)
   float* elite_w;           // [Q][n_pad] CES weights of the first n_elite sorted entries
   int* n_success; int* n_elite; int* best_idx; int* any_success;   // [Q]
   float* best_cost;         // [Q]
-  unsigned int* ticket;     // [Q]
+  int* succ_acc;            // [Q] scratch: success count accumulated by the ranking phase
 };
 
 // shared-memory bytes of the scoring phase for the given tile shape
 size_t iterate_smem_bytes(const ssppm::DevModel& M, const IterParams& P, int threads);
 
-cudaError_t launch_iterate(const ssppm::DevModel& M, const IterParams& P, int threads, size_t smem_bytes,
+// grid size: n_tiles CTAs (coop == 0) or `grid` co-resident CTAs looping over the tiles (coop == 1)
+cudaError_t launch_iterate(const ssppm::DevModel& M, const IterParams& P, int threads, size_t smem_bytes, int grid,
                            cudaStream_t stream);
+// co-resident CTAs per SM of the cooperative variant for this launch shape
+cudaError_t iterate_occupancy(int threads, size_t smem_bytes, int* ctas_per_sm);
 
 // second kernel of the population-sharded path: every rank applies the same CES update from the
 // gathered (cost bits << 32 | global candidate index) keys of all shards; elites' sampled rows are

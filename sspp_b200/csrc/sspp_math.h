@@ -646,6 +646,35 @@ SSPP_HD float limit_penalty(float q, float lim, float scl) {
   return (ex > 0.0f) ? scl * ex * ex : 0.0f;
 }
 
+// ----------------------------------------------------------------------------------------
+// banded collocation rows: a degree-p B-spline row has p+1 consecutive non-zeros, so the
+// kernel stores [rows][W] coefficients plus the first column of every row.  Skipping exact
+// zeros leaves the fmaf chain's result unchanged bit for bit (acc starts at +0 and can never
+// become -0), so the banded and the dense sums are the same number.
+// ----------------------------------------------------------------------------------------
+SSPP_HD float spline_coord(const float* row, int first, int W, const float* X, int D, int d) {
+  float acc = 0.0f;
+  for (int k = 0; k < W; ++k) acc = fmaf(row[k], X[(first + k) * D + d], acc);
+  return acc;
+}
+// host helper: band of a dense [rows][K] matrix -> width, first column per row (first + W <= K)
+inline int compute_band(const float* psi, int rows, int K, int* first) {
+  int W = 1;
+  for (int m = 0; m < rows; ++m) {
+    int lo = K, hi = -1;
+    for (int k = 0; k < K; ++k) if (psi[m * K + k] != 0.0f) { if (k < lo) lo = k; hi = k; }
+    if (hi < 0) { lo = 0; hi = 0; }
+    first[m] = lo;
+    if (hi - lo + 1 > W) W = hi - lo + 1;
+  }
+  for (int m = 0; m < rows; ++m) if (first[m] + W > K) first[m] = K - W;
+  return W;
+}
+inline void pack_band(const float* psi, int rows, int K, int W, const int* first, float* out /* [rows][W] */) {
+  for (int m = 0; m < rows; ++m)
+    for (int k = 0; k < W; ++k) out[m * W + k] = psi[m * K + first[m] + k];
+}
+
 // order-preserving map float -> uint32 used for the (cost, index) sort keys
 SSPP_HD uint32_t float_order_bits(float f) {
   union { float f; uint32_t u; } b; b.f = f;
