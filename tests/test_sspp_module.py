@@ -1,0 +1,121 @@
+"""The drop-in Python surface `_sspp` (reference: src/sspp_bindings.cpp:14-68): names, signatures,
+error behaviour on the CPU; plan() semantics against the oracles on the GPU."""
+import numpy as np
+import pytest
+
+from tests.helpers import FIX, Q_START, Q_END, SEED, joint_case, o1_for
+
+XML = str(FIX / "robocrane7.xml")
+
+
+@pytest.fixture(scope="module")
+def sp():
+    from sspp_b200 import _sspp
+    return _sspp
+
+
+def test_surface_matches_reference_names(sp):
+    for d in (3, 6, 7, 9):
+        assert hasattr(sp, f"SamplingPathPlanner{d}") and hasattr(sp, f"Spline{d}")
+    P = sp.SamplingPathPlanner7
+    for name in ("initializePath", "evaluate", "sampleWithNoise", "checkCollision", "computeArcLength", "findBestPath",
+                 "get_ctrl_pts", "plan"):
+        assert hasattr(P, name), name
+    assert hasattr(sp.Spline7, "ctrls")
+    assert sp.create_model_capsule(1234) is not None and sp.create_data_capsule(99) is not None
+    doc = P.plan.__doc__
+    import re
+    order = [doc.index(k) for k in ("start:", "end:", "sigma:", "limits:", "sample_count:", "check_points:", "init_points:")]
+    assert order == sorted(order)                                     # positional order of src/sspp_bindings.cpp:50
+    for kw, dflt in (("sample_count", 50), ("check_points", 50), ("init_points", 10)):
+        assert re.search(rf"{kw}: [^,)]*= {dflt}\b", doc), (kw, doc)
+
+
+def test_errors_like_the_reference(sp):
+    with pytest.raises(RuntimeError, match="Failed to load MuJoCo model from XML"):
+        sp.SamplingPathPlanner7("/nonexistent/scene.xml")
+    p = sp.SamplingPathPlanner7(XML)
+    s = sp.Spline7()
+    with pytest.raises(TypeError):
+        p.sampleWithNoise(s, 0.1, np.ones(7), object())
+    with pytest.raises(TypeError):
+        p.checkCollision(s, 10, object())
+    with pytest.raises(TypeError):
+        p.initializePath(np.zeros(6), np.zeros(7), s)
+
+
+def test_initialize_evaluate_arclength_host_side(sp):
+    from oracle import bsplines_np  # noqa: F401  (oracle only as the checker)
+    case = joint_case()
+    o1 = o1_for(case)
+    p = sp.SamplingPathPlanner7(XML)
+    s = sp.Spline7()
+    assert p.initializePath(Q_START, Q_END, s, 10) is True
+    c = s.ctrls()
+    assert c.shape == (7, 10) and c.dtype == np.float64
+    V = np.linspace(0, 1, 10)[:, None] * (Q_END - Q_START)[None, :] + Q_START[None, :]
+    np.testing.assert_allclose(c.T, o1.interpolate(V, 3), atol=1e-12)
+    np.testing.assert_allclose(s.knots(), o1.knots(10, 3), atol=1e-15)
+    for u in (0.0, 0.123, 0.5, 0.999, 1.0):
+        np.testing.assert_allclose(p.evaluate(s, u), o1.spline_eval(c.T.copy(), 3, u), atol=1e-12)
+        np.testing.assert_allclose(s(u), (1 - u) * Q_START + u * Q_END, atol=1e-12)     # a straight line stays straight
+    assert abs(p.computeArcLength(s, 50) - np.linalg.norm(Q_END - Q_START)) < 1e-12
+    best = sp.Spline7()
+    assert p.findBestPath([s], best, 10) is True
+    np.testing.assert_array_equal(best.ctrls(), c)
+    assert p.findBestPath([], best) is False
+    for K in (4, 7, 16):
+        assert p.initializePath(Q_START, Q_END, s, K) and s.ctrls().shape == (7, K)
+
+
+@pytest.mark.gpu
+def test_plan_semantics_on_gpu(sp, capsys):
+    case = joint_case(n_samples=100, check_points=100, n_points=7)
+    o1 = o1_for(case)
+    p = sp.SamplingPathPlanner7(XML)
+    p.set_seed(SEED)
+    lim = np.full(7, np.pi)
+    ok, paths = p.plan(Q_START, Q_END, 0.08, lim, 100, 100, 7)          # scripts/main.py:168-173 parameters
+    out = capsys.readouterr().out
+    assert f"Sampled 100 splines. Successful paths found: {len(paths)}" in out
+    assert ok and 0 < len(paths) < 100
+    # every returned spline is collision free at the reference's check grid, per the FP64 oracle
+    lengths = []
+    for s in paths:
+        c = s.ctrls()
+        assert c.shape == (7, 7)
+        np.testing.assert_allclose(c[:, :3].T, paths[0].ctrls()[:, :3].T, atol=0)      # boundary control points fixed (sspp.h:121-127)
+        for i in range(0, 101, 5):
+            cost, ncon, md = o1.point_cost(p.evaluate(s, i / 100))
+            assert ncon == 0 or abs(md) < 1e-4
+        lengths.append(p.computeArcLength(s, 100))
+    # the stored best path is the shortest success (findBestPath, sspp.h:171-192)
+    best = p.get_ctrl_pts()
+    j = int(np.argmin(lengths))
+    np.testing.assert_allclose(best, paths[j].ctrls(), atol=0)
+    np.testing.assert_allclose(p.evaluate(0.0), Q_START, atol=1e-6)
+    np.testing.assert_allclose(p.evaluate(1.0), Q_END, atol=1e-6)
+    # defaults + repeated calls draw new samples; same seed reproduces
+    ok2, paths2 = p.plan(Q_START, Q_END, 0.08, lim)
+    assert len(paths2) <= 50
+    p.set_seed(SEED)
+    ok3, paths3 = p.plan(Q_START, Q_END, 0.08, lim, 100, 100, 7)
+    assert len(paths3) == len(paths) and all(np.array_equal(a.ctrls(), b.ctrls()) for a, b in zip(paths, paths3))
+
+
+@pytest.mark.gpu
+def test_plan_device_buffers(sp):
+    import torch
+    p = sp.SamplingPathPlanner7(XML)
+    p.set_verbose(False)
+    d = p.plan_device(Q_START, Q_END, 0.08, np.full(7, np.pi), 512, 64, 10)
+    assert d["n_candidates"] == 512 and d["ctrl"].shape == (512, 4, 7)
+    assert (d["status"] == 0).sum() == d["n_success"]
+    ok = d["status"] == 0
+    assert d["best_idx"] == int(np.flatnonzero(ok)[np.argmin(d["arc_length"][ok])])
+
+    class Dev:
+        def __init__(self, ptr, shape, typestr):
+            self.__cuda_array_interface__ = dict(shape=shape, typestr=typestr, data=(ptr, False), version=2)
+    t = torch.as_tensor(Dev(d["device_ptrs"]["arc_length"], (512,), "<f4"), device="cuda")
+    np.testing.assert_array_equal(t.cpu().numpy(), d["arc_length"])          # zero-copy view of the device results
