@@ -69,14 +69,14 @@ def test_initialize_evaluate_arclength_host_side(sp):
 
 
 @pytest.mark.gpu
-def test_plan_semantics_on_gpu(sp, capsys):
+def test_plan_semantics_on_gpu(sp, capfd):
     case = joint_case(n_samples=100, check_points=100, n_points=7)
     o1 = o1_for(case)
     p = sp.SamplingPathPlanner7(XML)
     p.set_seed(SEED)
     lim = np.full(7, np.pi)
     ok, paths = p.plan(Q_START, Q_END, 0.08, lim, 100, 100, 7)          # scripts/main.py:168-173 parameters
-    out = capsys.readouterr().out
+    out = capfd.readouterr().out
     assert f"Sampled 100 splines. Successful paths found: {len(paths)}" in out
     assert ok and 0 < len(paths) < 100
     # every returned spline is collision free at the reference's check grid, per the FP64 oracle
