@@ -170,8 +170,12 @@ int ssppcu_get_base(ssppcu_t* h, float* base);
 /* ---- population sharding: each rank scores its shard with ssppcu_iterate, gathers the sorted
  * shard keys of all ranks (8 bytes per candidate) and applies the identical update ---- */
 int ssppcu_shard_keys(ssppcu_t* h, unsigned long long** dev_keys, int32_t* n_keys);
-int ssppcu_merge_update(ssppcu_t* h, const unsigned long long* dev_gathered_keys, int n_keys,
+/* dev_gathered_keys: n_shards equal-length ascending shards back to back (the all-gather output);
+ * asynchronous on the handle's stream */
+int ssppcu_merge_update(ssppcu_t* h, const unsigned long long* dev_gathered_keys, int n_keys, int n_shards,
                         uint64_t seed, uint32_t iter);
+
+int ssppcu_get_merged(ssppcu_t* h, uint32_t* idx, float* cost, float* weight, int cap);
 
 /* ---- host-side spline algebra the handle applies (no device needed; FP64) ----
  * Restates Eigen's KnotAveraging + SplineFitting::Interpolate + Spline::operator() as the

@@ -220,4 +220,67 @@ int o2_iterate(void* h, const float* psi_col, const float* psi_arc, const float*
   return k;
 }
 
+// Population-sharded path: restates sspp_merge_rank_kernel + sspp_merge_finish_kernel.  keys: the
+// gathered keys of every shard (any order: the merged order of unique keys is their sorted order).
+// In/out: mean, sigma, best [nfd], best_valid.  Elites' rows are regenerated from the Philox counters
+// with the PRE-update state, as the kernel does.  Returns k; keys come back sorted.
+int o2_merge_update(void* h, unsigned long long* keys, int n_keys, uint64_t seed, uint32_t iter, float* mean, float* sigma,
+                    float* best, int32_t* best_valid, float* weights, int32_t* n_success, int32_t* best_idx) {
+  Replica* r = static_cast<Replica*>(h);
+  const ScoreConfig& c = r->cfg;
+  const int D = c.D, nfd = c.n_free * D;
+  std::sort(keys, keys + n_keys);
+  int n_succ = 0;
+  for (int i = 0; i < n_keys; ++i) if ((uint32_t)(keys[i] >> 32) != 0xFFFFFFFFu) ++n_succ;
+  *n_success = n_succ;
+  const int k = elite_count(n_succ, c.elite_frac);
+  if (n_succ == 0) {
+    *best_idx = -1;
+    if (c.do_update) for (int t = 0; t < nfd; ++t) sigma[t] = clamp_sigma(c, sigma[t] * c.inc);
+    return 0;
+  }
+  const std::vector<float> mean0(mean, mean + nfd), sigma0(sigma, sigma + nfd), best0(best, best + nfd);
+  const int best_ok0 = c.include_best ? *best_valid : 0;
+  auto P = [&](int j, int t) {
+    const int idx = (int)(uint32_t)(keys[j] & 0xFFFFFFFFu);
+    return candidate_param(c, seed, iter, 0u, idx, candidate_kind(c, idx, best_ok0), t, mean0.data(), sigma0.data(), best0.data());
+  };
+  *best_idx = (int)(uint32_t)(keys[0] & 0xFFFFFFFFu);
+  const float lk = log_poly((float)k + 0.5f);
+  for (int j = 0; j < k; ++j) weights[j] = lk - log_poly((float)j + 1.0f);
+  const float sumw = strided_sum(weights, k);
+  for (int j = 0; j < k; ++j) weights[j] = weights[j] / sumw;
+  for (int t = 0; t < nfd; ++t) best[t] = P(0, t);
+  *best_valid = 1;
+  if (c.do_update) {
+    for (int t = 0; t < nfd; ++t) {
+      const int d = t % D;
+      float part[32];
+      for (int l = 0; l < 32; ++l) { float acc = 0.0f; for (int j = l; j < k; j += 32) acc = fmaf(weights[j], P(j, t), acc); part[l] = acc; }
+      const float em = butterfly(part);
+      const float m0 = mean[t];
+      float nm = fmaf(c.mean_lr, em - m0, m0);
+      if (c.mode == MODE_TASK && d == 2) nm = fmaxf(nm, c.dist_zmin);
+      nm = fminf(fmaxf(nm, c.lo[d]), c.hi[d]);
+      const bool wrap = (c.mode == MODE_TASK && d == 3 && c.lo[3] != c.hi[3]);
+      for (int l = 0; l < 32; ++l) {
+        float acc = 0.0f;
+        for (int j = l; j < k; j += 32) {
+          const float v = P(j, t);
+          const float df = wrap ? wrap_angle_diff(v, nm, c.lo[3], c.hi[3]) : v - nm;
+          acc = fmaf(weights[j], df * df, acc);
+        }
+        part[l] = acc;
+      }
+      const float var = butterfly(part);
+      const float s0 = sigma[t];
+      const float blend = fmaf(c.var_beta, var, (1.0f - c.var_beta) * (s0 * s0));
+      float sg = clamp_sigma(c, sqrtf(blend));
+      sg = clamp_sigma(c, sg * c.dec);
+      mean[t] = nm; sigma[t] = sg;
+    }
+  }
+  return k;
+}
+
 }  // extern "C"

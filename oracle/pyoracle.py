@@ -217,6 +217,7 @@ class O2:
         L.o2_sincos.argtypes = [C.c_float, C.POINTER(C.c_float), C.POINTER(C.c_float)]
         L.o2_philox.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
         L.o2_iterate.argtypes = [C.c_void_p] + [C.c_void_p] * 7 + [C.c_uint64, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 11
+        L.o2_merge_update.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_uint32] + [C.c_void_p] * 7
         err = C.create_string_buffer(1024)
         self.cfg = planner_cfg
         self.h = L.o2_create(str(mjcf_path).encode(), C.addressof(planner_cfg), err, len(err))
@@ -276,3 +277,16 @@ class O2:
                    best_valid=int(bv[0]), pts=pts)
         out["weights"] = out["weights"][:k]
         return out
+
+    def merge_update(self, keys, seed: int, it: int, mean, sigma, best, best_valid: int):
+        """population-sharded K6/K7 over the gathered keys of all shards (restates the merge kernels)"""
+        f = lambda a: np.ascontiguousarray(a, np.float32).copy().ravel()
+        keys = np.ascontiguousarray(keys, np.uint64).copy().ravel()
+        mean, sigma, best = f(mean), f(sigma), f(best)
+        bv = np.array([best_valid], np.int32); ns = np.zeros(1, np.int32); bi = np.zeros(1, np.int32)
+        w = np.zeros(max(len(keys), 1), np.float32)
+        p = lambda a: a.ctypes.data_as(C.c_void_p)
+        k = self.lib.o2_merge_update(self.h, p(keys), len(keys), C.c_uint64(seed), it, p(mean), p(sigma), p(best), p(bv), p(w), p(ns), p(bi))
+        return dict(keys=keys, n_elite=k, weights=w[:k], n_success=int(ns[0]), best_idx=int(bi[0]),
+                    mean=mean.reshape(self.n_free, self.D), sigma=sigma.reshape(self.n_free, self.D),
+                    best=best.reshape(self.n_free, self.D), best_valid=int(bv[0]))

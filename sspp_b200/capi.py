@@ -87,7 +87,7 @@ SYMBOLS = [
     "ssppcu_get_params", "ssppcu_get_best", "ssppcu_get_elites", "ssppcu_device_view", "ssppcu_eval_points",
     "ssppcu_get_collocation", "ssppcu_get_base", "ssppcu_shard_keys", "ssppcu_merge_update", "ssppcu_version",
     "ssppcu_spline_setup", "ssppcu_collocation_matrix", "ssppcu_save_state", "ssppcu_restore_state",
-    "ssppcu_fp32_peak",
+    "ssppcu_fp32_peak", "ssppcu_get_merged",
 ]
 
 lib = _load()
@@ -128,7 +128,8 @@ lib.ssppcu_eval_points.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
 lib.ssppcu_get_collocation.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
 lib.ssppcu_get_base.argtypes = [C.c_void_p, C.c_void_p]
 lib.ssppcu_shard_keys.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), _ip]
-lib.ssppcu_merge_update.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_uint32]
+lib.ssppcu_merge_update.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_uint32]
+lib.ssppcu_get_merged.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
 lib.ssppcu_save_state.argtypes = [C.c_void_p]
 lib.ssppcu_restore_state.argtypes = [C.c_void_p]
 lib.ssppcu_fp32_peak.argtypes = [C.c_int, _dp, _dp]
@@ -396,5 +397,10 @@ class Handle:
         self._ck(lib.ssppcu_shard_keys(self._h, C.byref(p), C.byref(n)))
         return p.value, n.value
 
-    def merge_update(self, dev_keys_ptr: int, n_keys: int, seed: int, it: int):
-        self._ck(lib.ssppcu_merge_update(self._h, C.c_void_p(dev_keys_ptr), int(n_keys), C.c_uint64(seed), C.c_uint32(it)))
+    def merge_update(self, dev_keys_ptr: int, n_keys: int, n_shards: int, seed: int, it: int):
+        self._ck(lib.ssppcu_merge_update(self._h, C.c_void_p(dev_keys_ptr), int(n_keys), int(n_shards), C.c_uint64(seed), C.c_uint32(it)))
+
+    def merged(self, cap: int):
+        idx = np.zeros(cap, np.uint32); cost = np.zeros(cap, np.float32); w = np.zeros(cap, np.float32)
+        n = self._ck(lib.ssppcu_get_merged(self._h, _ptr(idx), _ptr(cost), _ptr(w), cap))
+        return idx[:n], cost[:n], w[:n]

@@ -39,7 +39,7 @@ struct ssppcu_planner {
   std::vector<float> psi_col, psi_arc, base_host;
   std::vector<void*> allocs;
   float* d_eval_pts = nullptr; float* d_eval_out = nullptr; int eval_cap = 0;
-  unsigned long long* d_merge_keys = nullptr; int merge_cap = 0;
+  unsigned long long* d_merge_keys = nullptr; int merge_cap = 0, merged_n = 0;
   float* d_live = nullptr;       // mean | sigma | best | best_valid | any_success (ints), one block
   float* d_state = nullptr;      // snapshot of d_live
   size_t state_words = 0; bool state_saved = false;
@@ -643,30 +643,57 @@ int ssppcu_shard_keys(ssppcu_t* h, unsigned long long** keys, int32_t* n) {
   return SSPPCU_OK;
 }
 
-int ssppcu_merge_update(ssppcu_t* h, const unsigned long long* gathered, int n_keys, uint64_t seed, uint32_t iter) {
+int ssppcu_merge_update(ssppcu_t* h, const unsigned long long* gathered, int n_keys, int n_shards, uint64_t seed, uint32_t iter) {
   if (int rc = check(h)) return rc;
-  if (!gathered || n_keys < 1) return fail(h, SSPPCU_EINVAL, "bad arguments");
+  if (!gathered || n_keys < 1 || n_shards < 1 || n_keys % n_shards) return fail(h, SSPPCU_EINVAL, "bad arguments: n_keys must be n_shards equal shards");
   if (h->cfg.shard_global <= 0) return fail(h, SSPPCU_EINVAL, "handle is not a population shard");
   const int n_pad = next_pow2(std::max(2, n_keys));
+  const int nfd = h->P.cfg.n_free * h->P.cfg.D;
   if (n_pad > h->merge_cap) {
     if (h->d_merge_keys) cudaFree(h->d_merge_keys);
     h->d_merge_keys = nullptr; h->merge_cap = 0;
-    CU(h, cudaMalloc(&h->d_merge_keys, (size_t)n_pad * (sizeof(unsigned long long) + sizeof(float))));
+    CU(h, cudaMalloc(&h->d_merge_keys, (size_t)n_pad * (sizeof(unsigned long long) + sizeof(float)) + (3 * nfd + 2) * sizeof(float)));
     h->merge_cap = n_pad;
   }
-  CU(h, cudaMemcpyAsync(h->d_merge_keys, gathered, (size_t)n_keys * sizeof(unsigned long long), cudaMemcpyDeviceToDevice, h->stream));
   MergeParams M;
   std::memset(&M, 0, sizeof(M));
   M.cfg = h->P.cfg;
   M.cfg.n_cand = h->cfg.shard_global;
-  M.n_keys = n_keys; M.n_pad = n_pad; M.iter = iter; M.seed = seed;
+  M.n_keys = n_keys; M.n_shards = n_shards; M.shard_len = n_keys / n_shards; M.n_pad = n_pad; M.iter = iter; M.seed = seed;
+  M.gathered = gathered;
   M.keys = h->d_merge_keys;
   M.elite_w = reinterpret_cast<float*>(h->d_merge_keys + n_pad);
+  M.state0 = M.elite_w + n_pad;
+  M.succ_acc = h->P.succ_acc;
   M.mean = h->P.mean; M.sigma = h->P.sigma; M.best = h->P.best; M.best_valid = h->P.best_valid;
   M.n_success = h->P.n_success; M.n_elite = h->P.n_elite; M.best_idx = h->P.best_idx; M.best_cost = h->P.best_cost;
   M.any_success = h->P.any_success;
+  CU(h, cudaMemsetAsync(h->P.succ_acc, 0, sizeof(int), h->stream));
   CU(h, launch_merge_update(M, h->stream));
+  h->merged_n = n_keys;
   return SSPPCU_OK;
+}
+
+/* merged global order of the last ssppcu_merge_update: up to cap entries, elites first with weights */
+int ssppcu_get_merged(ssppcu_t* h, uint32_t* idx, float* cost, float* weight, int cap) {
+  if (int rc = check(h)) return rc;
+  if (!h->d_merge_keys || cap < 0) return fail(h, SSPPCU_EINVAL, "no merged keys");
+  const int n = std::min(cap, h->merged_n);
+  std::vector<unsigned long long> keys(n);
+  std::vector<float> w(n);
+  if (int rc = d2h(h, keys.data(), h->d_merge_keys, n)) return rc;
+  if (int rc = d2h(h, w.data(), reinterpret_cast<float*>(h->d_merge_keys + h->merge_cap), n)) return rc;
+  CU(h, cudaStreamSynchronize(h->stream));
+  for (int i = 0; i < n; ++i) {
+    if (idx) idx[i] = (uint32_t)(keys[i] & 0xFFFFFFFFull);
+    if (cost) {
+      uint32_t ob = (uint32_t)(keys[i] >> 32);
+      if (ob == 0xFFFFFFFFu) cost[i] = INFINITY;
+      else { ob = (ob & 0x80000000u) ? (ob & 0x7FFFFFFFu) : ~ob; std::memcpy(&cost[i], &ob, 4); }
+    }
+    if (weight) weight[i] = w[i];
+  }
+  return n;
 }
 
 }  // extern "C"

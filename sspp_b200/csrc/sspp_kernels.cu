@@ -27,6 +27,8 @@
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
 
+#include <algorithm>
+
 namespace cg = cooperative_groups;
 
 namespace sspp {
@@ -468,19 +470,66 @@ struct RegenParams {
   }
 };
 
-__global__ void __launch_bounds__(1024, 1)
-sspp_merge_update_kernel(const __grid_constant__ MergeParams P) {
-  __shared__ int s_int[4];
-  __shared__ float s_mean0[MAX_K * MAX_DOF], s_sigma0[MAX_K * MAX_DOF], s_best0[MAX_K * MAX_DOF];
+__global__ void __launch_bounds__(256)
+sspp_merge_rank_kernel(const __grid_constant__ MergeParams P) {
   const ScoreConfig& c = P.cfg;
-  const int tid = threadIdx.x, T = blockDim.x;
   const int nfd = c.n_free * c.D;
-  for (int t = tid; t < nfd; t += T) { s_mean0[t] = P.mean[t]; s_sigma0[t] = P.sigma[t]; s_best0[t] = P.best[t]; }
-  for (int i = P.n_keys + tid; i < P.n_pad; i += T) P.keys[i] = ~0ull;
-  __syncthreads();
-  RegenParams gp{&c, P.seed, P.iter, s_mean0, s_sigma0, s_best0, c.include_best ? *P.best_valid : 0};
-  cta_elites_and_update(c, P.keys, P.n_pad, P.elite_w, P.mean, P.sigma, P.best, P.best_valid, P.n_success, P.n_elite,
-                        P.best_idx, P.best_cost, P.any_success, gp, s_int);
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (blockIdx.x == 0) {           // snapshot of the state the elites were sampled from
+    for (int t = threadIdx.x; t < nfd; t += blockDim.x) {
+      P.state0[t] = P.mean[t]; P.state0[nfd + t] = P.sigma[t]; P.state0[2 * nfd + t] = P.best[t];
+    }
+    if (threadIdx.x == 0) reinterpret_cast<int*>(P.state0)[3 * nfd] = *P.best_valid;
+  }
+  for (int k = P.n_keys + i; k < P.n_pad; k += gridDim.x * blockDim.x) P.keys[k] = ~0ull;
+  int succ_hi = 0;
+  if (i < P.n_keys) {
+    const int shard = i / P.shard_len;
+    const unsigned long long key = P.gathered[i];
+    int rank = i - shard * P.shard_len;
+    for (int s = 0; s < P.n_shards; ++s) {
+      if (s == shard) continue;
+      const unsigned long long* a = P.gathered + (size_t)s * P.shard_len;
+      int lo = 0, hi = P.shard_len;                 // first position with a[pos] >= key
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if (a[mid] < key) lo = mid + 1; else hi = mid; }
+      rank += lo;
+    }
+    P.keys[rank] = key;
+    if (key_success(key)) succ_hi = rank + 1;
+  }
+  succ_hi = __reduce_max_sync(0xFFFFFFFFu, succ_hi);
+  if ((threadIdx.x & 31) == 0 && succ_hi) atomicMax(P.succ_acc, succ_hi);
+}
+
+__global__ void __launch_bounds__(256)
+sspp_merge_finish_kernel(const __grid_constant__ MergeParams P) {
+  const ScoreConfig& c = P.cfg;
+  const int lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+  const int nfd = c.n_free * c.D;
+  const int gw = blockIdx.x * nwarp + (threadIdx.x >> 5), gstride = gridDim.x * nwarp;
+  const int n_succ = *P.succ_acc;
+  const int k = elite_count(n_succ, c.elite_frac);
+  const int best_ok0 = c.include_best ? reinterpret_cast<const int*>(P.state0)[3 * nfd] : 0;
+  RegenParams gp{&c, P.seed, P.iter, P.state0, P.state0 + nfd, P.state0 + 2 * nfd, best_ok0};
+  for (int t = gw; t <= nfd; t += gstride) {
+    if (t == nfd) {
+      if (lane == 0) { *P.n_success = n_succ; *P.n_elite = k; }
+      const unsigned long long k0 = P.keys[0];
+      if (n_succ > 0) {
+        if (lane == 0) { *P.best_idx = (int)(unsigned)(k0 & 0xFFFFFFFFu); *P.best_cost = key_cost(k0); *P.any_success = 1; *P.best_valid = 1; }
+        for (int e = lane; e < nfd; e += 32) P.best[e] = gp((unsigned)(k0 & 0xFFFFFFFFu), e);
+        const float lk = log_poly((float)k + 0.5f);
+        const float sumw = ces_weight_sum(k, lk, lane);
+        for (int j = lane; j < k; j += 32) P.elite_w[j] = (lk - log_poly((float)j + 1.0f)) / sumw;
+      } else if (lane == 0) { *P.best_idx = -1; *P.best_cost = __int_as_float(0x7F800000); }
+      continue;
+    }
+    if (!c.do_update) continue;
+    if (n_succ == 0) { if (lane == 0) P.sigma[t] = clamp_sigma(c, P.sigma[t] * c.inc); continue; }
+    const float lk = log_poly((float)k + 0.5f);
+    const float sumw = ces_weight_sum(k, lk, lane);
+    update_element(c, P.keys, k, lk, sumw, t, P.mean, P.sigma, gp, lane);
+  }
 }
 
 __global__ void __launch_bounds__(128)
@@ -578,7 +627,11 @@ cudaError_t launch_eval_points(const DevModel& M, int D, const float* pts, int n
 }
 
 cudaError_t launch_merge_update(const MergeParams& P, cudaStream_t stream) {
-  sspp_merge_update_kernel<<<1, 1024, 0, stream>>>(P);
+  const int nfd = P.cfg.n_free * P.cfg.D;
+  sspp_merge_rank_kernel<<<(std::max(P.n_keys, 1) + 255) / 256, 256, 0, stream>>>(P);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  sspp_merge_finish_kernel<<<(nfd + 1 + 7) / 8, 256, 0, stream>>>(P);
   return cudaGetLastError();
 }
 

@@ -52,15 +52,21 @@ cudaError_t launch_iterate(const ssppm::DevModel& M, const IterParams& P, int th
 // co-resident CTAs per SM of the cooperative variant for this launch shape
 cudaError_t iterate_occupancy(int threads, size_t smem_bytes, int* ctas_per_sm);
 
-// second kernel of the population-sharded path: every rank applies the same CES update from the
-// gathered (cost bits << 32 | global candidate index) keys of all shards; elites' sampled rows are
-// regenerated from the Philox counters, so only 8-byte keys cross NVLink.
+// Population-sharded path, after the all-gather of every shard's sorted keys: two small launches that
+// every rank runs identically.  (1) merge-rank: the global position of a key = its position in its own
+// shard + the number of smaller keys in every other shard (binary searches; keys are unique), which
+// merges the sorted shards without a sort; (2) finish: elites, CES weights and the distribution update,
+// one warp per distribution element; elites' sampled rows are regenerated from the Philox counters, so
+// only 8-byte keys ever cross NVLink.
 struct MergeParams {
   ssppm::ScoreConfig cfg;      // n_cand = global population
-  int n_keys, n_pad;           // gathered keys, padded sort length
+  int n_keys, n_shards, shard_len, n_pad;
   uint32_t iter; uint64_t seed;
-  unsigned long long* keys;    // [n_pad] gathered keys (sorted in place)
+  const unsigned long long* gathered;   // [n_shards][shard_len], each shard ascending
+  unsigned long long* keys;    // [n_pad] merged ascending order (tail ~0)
   float* elite_w;              // [n_pad]
+  float* state0;               // [3 * nfd + 1] snapshot of mean | sigma | best | best_valid taken by (1)
+  int* succ_acc;               // zeroed by the caller before (1)
   float* mean; float* sigma; float* best; int* best_valid;
   int* n_success; int* n_elite; int* best_idx; float* best_cost; int* any_success;
 };

@@ -124,3 +124,45 @@ def test_no_device_memory_growth_and_errors():
         capi.Handle(bad.model, bad.cfg)
     for _ in range(20):
         h = _handle(case); h.iterate(SEED, 0, 1); h.sync(); h.close()
+
+
+@pytest.mark.parametrize("kind,n_global", [("task", 1024), ("joint", 4096)])
+def test_population_shards_match_unsharded(kind, n_global):
+    """population sharding (cfg 3 shape) emulated on one GPU: two shard handles + the merge kernels reach the
+    state of the unsharded handle bit for bit (multi-rank transport is covered by tests/test_sharding.py)."""
+    import torch
+    from sspp_b200 import capi
+    from sspp_b200.sharding import DeviceShard
+
+    def mk(n_samples, offset=0, glob=0):
+        case = task_case(n_samples=n_samples, check_points=32) if kind == "task" else \
+            joint_case(n_samples=n_samples, check_points=32, do_update=True)
+        case.cfg.shard_offset, case.cfg.shard_global = offset, glob
+        h = capi.Handle(case.model, case.cfg)
+        case.prepare(h)
+        return h
+    slots = 2 if kind == "task" else 0
+    full = mk(n_global - slots)
+    half = n_global // 2
+    shards = [DeviceShard(mk(half, 0, n_global)), DeviceShard(mk(half, half, n_global))]
+    for it in range(4):
+        full.iterate(SEED, it, 1)
+        r = full.results()
+        fi, fc, fw = full.elites(0)
+        keys = torch.cat([s.score(SEED, it) for s in shards])
+        torch.cuda.synchronize()
+        for s in shards:
+            s.merge(keys, 2, SEED, it)
+            mi, mc, mw = s.h.merged(n_global)
+            assert np.array_equal(mi, fi) and np.array_equal(mc.view(np.uint32), fc.view(np.uint32))
+            k = int(r["n_elite"][0])
+            assert np.array_equal(mw[:k].view(np.uint32), fw[:k].view(np.uint32))
+            rs = s.h.results()
+            assert rs["n_success"][0] == r["n_success"][0] and rs["best_idx"][0] == r["best_idx"][0]
+            m0, s0 = full.get_distribution(); m1, s1 = s.h.get_distribution()
+            assert np.array_equal(m0, m1) and np.array_equal(s0, s1)
+            b0, v0 = full.best(); b1, v1 = s.h.best()
+            assert np.array_equal(b0, b1) and np.array_equal(v0, v1)
+    for s in shards:
+        s.h.close()
+    full.close()
