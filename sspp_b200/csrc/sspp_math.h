@@ -49,6 +49,9 @@ struct DevBody {
   int qidx;         // first planned coordinate this joint reads
   int geom_begin, geom_end;  // moving geoms attached to this body
   int has_anchor;
+  int axis_kind;    // 0,1,2: the joint axis is +-e_x, +-e_y, +-e_z (axis_sign); 3: general axis
+  float axis_sign;
+  int r0_identity;  // R0 == I: the body frame is a pure translation of the parent frame
 };
 struct DevMGeom {
   float pos[3];     // in the body frame
@@ -278,6 +281,18 @@ SSPP_HD void rodrigues(v3 a, float th, float* Rj) {
   Rj[6] = fmaf(-a.y, s, xz);     Rj[7] = fmaf(a.x, s, yz);      Rj[8] = fmaf(a.z * a.z, t, c);
 }
 
+// R <- R * Rot(e_K, theta): only the two other columns mix (compile-time indices keep R in registers)
+template <int K>
+SSPP_HD void rot_axis(m3& R, float s, float c) {
+  constexpr int i1 = (K + 1) % 3, i2 = (K + 2) % 3;
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const float u = R.a[3 * r + i1], v = R.a[3 * r + i2];
+    R.a[3 * r + i1] = fmaf(s, v, c * u);
+    R.a[3 * r + i2] = fmaf(c, v, -(s * u));
+  }
+}
+
 // parent frame (Rp,pp) -> this body's frame (R,p) given planned coordinates q
 template <class QA>
 SSPP_HD void fk_body(const DevBody& B, bool has_parent, const m3& Rp, v3 pp, QA& q, m3* R, v3* p) {
@@ -291,12 +306,22 @@ SSPP_HD void fk_body(const DevBody& B, bool has_parent, const m3& Rp, v3 pp, QA&
     return;
   }
   m3 Rw; v3 pw;
-  if (has_parent) { Rw = mulm(Rp, B.R0); pw = add(pp, mulv(Rp, ld3(B.pos))); }
+  if (has_parent) { Rw = B.r0_identity ? Rp : mulm(Rp, B.R0); pw = add(pp, mulv(Rp, ld3(B.pos))); }
   else { Rw = ldm(B.R0); pw = ld3(B.pos); }
   if (B.jtype == JT_HINGE) {
-    float Rj[9];
-    rodrigues(ld3(B.axis), q.get(B.qidx), Rj);
-    const m3 Rn = mulm(Rw, Rj);
+    m3 Rn;
+    if (B.axis_kind < 3) {
+      // rotation about a coordinate axis of the body frame: only the two other columns mix
+      float s, c;
+      sincos_poly(q.get(B.qidx), &s, &c);
+      s *= B.axis_sign;
+      Rn = Rw;
+      if (B.axis_kind == 0) rot_axis<0>(Rn, s, c); else if (B.axis_kind == 1) rot_axis<1>(Rn, s, c); else rot_axis<2>(Rn, s, c);
+    } else {
+      float Rj[9];
+      rodrigues(ld3(B.axis), q.get(B.qidx), Rj);
+      Rn = mulm(Rw, Rj);
+    }
     if (B.has_anchor) { const v3 an = ld3(B.anchor); pw = add(pw, sub(mulv(Rw, an), mulv(Rn, an))); }
     Rw = Rn;
   } else if (B.jtype == JT_SLIDE) {
@@ -390,7 +415,9 @@ SSPP_HD void sat_max(float s, float l2, float* bs, float* bl2) {
 
 // box-box: 15-axis separating-axis test; > 0 separation along the best axis (a lower bound of
 // the distance), < 0 the smallest penetration depth
-SSPP_HD float box_box_sd(const Prim& A, const Prim& B) {
+// thr: once the face axes alone separate the boxes by more than thr the 9 edge axes are skipped (the
+// result only has to stay above thr: callers compare it with a margin below thr)
+SSPP_HD float box_box_sd(const Prim& A, const Prim& B, float thr = 3.0e38f) {
   float Rm[9], Ab[9];
   const v3 dlt = sub(B.p, A.p);
   const v3 t = multv(A.R, dlt);
@@ -419,6 +446,7 @@ SSPP_HD float box_box_sd(const Prim& A, const Prim& B) {
     const float s = fabsf(pr) - (ra + rb);
     if (s > bs) bs = s;
   }
+  if (bs > thr) return bs;
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
     const int i1 = (i + 1) % 3, i2 = (i + 2) % 3;
@@ -442,7 +470,7 @@ SSPP_HD float cyl_support(v3 a, float r, float h, v3 L, float l2) {  // support 
   const float la = dot(L, a);
   return fmaf(h, fabsf(la), r * sqrtf(fmaxf(fmaf(-la, la, l2), 0.0f)));
 }
-SSPP_HD float cyl_box_sd(const Prim& C, const Prim& B) {
+SSPP_HD float cyl_box_sd(const Prim& C, const Prim& B, float thr = 3.0e38f) {
   const v3 a = col(C.R, 2);
   const float r = C.s.x, h = C.s.y;
   const v3 dlt = sub(C.p, B.p);
@@ -459,6 +487,7 @@ SSPP_HD float cyl_box_sd(const Prim& C, const Prim& B) {
     const float s = fabsf(dot(dlt, a)) - rb - h;
     if (s > bs) bs = s;
   }
+  if (bs > thr) return bs;
 #pragma unroll
   for (int i = 0; i < 3; ++i) {   // axis x box normal
     const v3 L = cross(a, bx[i]);
@@ -544,6 +573,40 @@ SSPP_HD float prim_sd(const Prim& A, const Prim& B, bool* ok) {
   *ok = false; return 3.0e38f;
 }
 
+// Signed distance of a MOVING primitive P to a STATIC one S for the pairings the scenes use, without
+// the by-value operand swap of prim_sd, and with conservative early exits: as soon as a cheap lower
+// bound of the distance exceeds thr (> the pair's margin) that bound is returned instead of the exact
+// distance — the contact rule maps both to "no contact".  Other pairings fall back to prim_sd.
+SSPP_HD float moving_static_sd(const Prim& P, const Prim& S, float thr) {
+  if (S.type == GT_PLANE) {
+    const v3 n = col(S.R, 2);
+    const float d0 = dot(n, sub(P.p, S.p));
+    if (P.type == GT_SPHERE) return d0 - P.s.x;
+    if (P.type == GT_CAPSULE) return d0 - P.s.y * fabsf(dot(n, col(P.R, 2))) - P.s.x;
+    if (P.type == GT_CYLINDER) {
+      const float na = dot(n, col(P.R, 2));
+      return d0 - P.s.y * fabsf(na) - P.s.x * sqrtf(fmaxf(fmaf(-na, na, 1.0f), 0.0f));
+    }
+    if (P.type == GT_BOX)
+      return d0 - fmaf(P.s.z, fabsf(dot(n, col(P.R, 2))),
+                       fmaf(P.s.y, fabsf(dot(n, col(P.R, 1))), P.s.x * fabsf(dot(n, col(P.R, 0)))));
+  }
+  if (S.type == GT_BOX) {
+    if (P.type == GT_CAPSULE) {
+      const v3 c = multv(S.R, sub(P.p, S.p));
+      const float lb = point_box_sd(c, S.s) - P.s.y - P.s.x;     // centre distance minus half length minus radius
+      if (lb > thr) return lb;
+      const v3 al = multv(S.R, col(P.R, 2));
+      return seg_box_dist(madd(al, -P.s.y, c), scale(al, 2.0f * P.s.y), S.s) - P.s.x;
+    }
+    if (P.type == GT_BOX) return box_box_sd(P, S, thr);
+    if (P.type == GT_CYLINDER) return cyl_box_sd(P, S, thr);
+    if (P.type == GT_SPHERE) return point_box_sd(multv(S.R, sub(P.p, S.p)), S.s) - P.s.x;
+  }
+  bool ok;
+  return prim_sd(P, S, &ok);
+}
+
 // contribution of one geom pair at signed distance d (centres ca, cb) under the model's rule
 SSPP_HD float contact_cost(int rule, float d, float margin, v3 ca, v3 cb) {
   if (rule == CR_COUNT) return (d < margin) ? 1.0f : 0.0f;
@@ -561,6 +624,15 @@ SSPP_HD Prim place(const DevMGeom& g, const m3& R, v3 p) {
   P.s = ld3(g.size);
   P.type = g.type;
   return P;
+}
+// orientation part of a placement, as little as the type needs: capsules and cylinders only use their
+// axis (column 2), spheres nothing; element formulas are those of mulm
+SSPP_HD void place_rotation(const DevMGeom& g, const m3& R, Prim* P) {
+  if (g.type == GT_BOX) { P->R = mulm(R, g.R); return; }
+  if (g.type == GT_SPHERE) return;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+    P->R.a[3 * i + 2] = fmaf(R.a[3 * i + 2], g.R[8], fmaf(R.a[3 * i + 1], g.R[5], R.a[3 * i] * g.R[2]));
 }
 SSPP_HD Prim static_prim(const DevSGeom& g) {
   Prim P; P.p = ld3(g.pos); P.R = ldm(g.R); P.s = ld3(g.size); P.type = g.type; return P;
@@ -599,19 +671,27 @@ SSPP_HD float point_collision_cost(const DevModel& M, QA& q, XF& xf) {
 #pragma unroll 1
     for (int g = B.geom_begin; g < B.geom_end; ++g) {
       const DevMGeom& G = M.mg[g];
-      const Prim P = place(G, R, p);
+      Prim P;
+      P.p = add(p, mulv(R, ld3(G.pos)));
+      P.s = ld3(G.size);
+      P.type = G.type;
+      bool rotated = false;
 #pragma unroll 1
       for (int k = G.pair_begin; k < G.pair_end; ++k) {
         const DevSGeom& S = M.sg[M.pair[k].s];
         const float margin = M.pair[k].margin;
-        if (S.rbound >= 0.0f) {   // bounding-sphere cull (conservative: + margin + slack)
+        const float thr = fmaxf(margin, 0.0f) + 1e-4f;      // conservative: margin + slack
+        if (S.rbound >= 0.0f) {                             // bounding-sphere cull
           const v3 w = sub(P.p, ld3(S.pos));
-          const float rr = G.rbound + S.rbound + fmaxf(margin, 0.0f) + 1e-4f;
+          const float rr = G.rbound + S.rbound + thr;
           if (dot(w, w) > rr * rr) continue;
+        } else {                                            // plane: bounding sphere against the half space
+          const v3 n = mk(S.R[2], S.R[5], S.R[8]);
+          if (dot(n, sub(P.p, ld3(S.pos))) - G.rbound > thr) continue;
         }
-        bool ok;
+        if (!rotated) { place_rotation(G, R, &P); rotated = true; }
         const Prim Q = static_prim(S);
-        const float d = prim_sd(P, Q, &ok);
+        const float d = moving_static_sd(P, Q, thr);
         cost += contact_cost(M.rule, d, margin, P.p, Q.p);
       }
     }

@@ -481,6 +481,13 @@ ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const 
     for (int k = 0; k < 3; ++k) { B.pos[k] = (float)rel.p[k]; B.axis[k] = (float)m.jnt_axis[3 * b + k]; B.anchor[k] = (float)m.jnt_pos[3 * b + k]; }
     for (int k = 0; k < 9; ++k) B.R0[k] = (float)rel.R[k];
     B.has_anchor = (m.jnt_pos[3 * b] != 0 || m.jnt_pos[3 * b + 1] != 0 || m.jnt_pos[3 * b + 2] != 0);
+    B.axis_kind = 3; B.axis_sign = 1.0f;
+    for (int k = 0; k < 3; ++k)
+      if (std::fabs(m.jnt_axis[3 * b + k]) == 1.0 && m.jnt_axis[3 * b + (k + 1) % 3] == 0.0 && m.jnt_axis[3 * b + (k + 2) % 3] == 0.0) {
+        B.axis_kind = k; B.axis_sign = (float)m.jnt_axis[3 * b + k];
+      }
+    B.r0_identity = 1;
+    for (int k = 0; k < 9; ++k) if (B.R0[k] != ((k % 4 == 0) ? 1.0f : 0.0f)) B.r0_identity = 0;
     B.jtype = (m.body_jtype[b] == MJ_HINGE) ? JT_HINGE : (m.body_jtype[b] == MJ_SLIDE) ? JT_SLIDE : JT_FREE4;
     B.qidx = qidx[b];
   }

@@ -54,7 +54,8 @@ class DeviceShard:
 
     def __init__(self, handle, stream: "torch.cuda.Stream | None" = None):
         self.h = handle
-        self.stream = stream or torch.cuda.current_stream()
+        # the legacy default stream cannot be handed to the C ABI (NULL means "the handle's own stream")
+        self.stream = stream if stream is not None and stream.cuda_stream != 0 else torch.cuda.Stream()
         handle.set_stream(self.stream.cuda_stream)
         ptr, n = handle.shard_keys()
         self.n_local = n

@@ -149,7 +149,10 @@ def test_population_shards_match_unsharded(kind, n_global):
         full.iterate(SEED, it, 1)
         r = full.results()
         fi, fc, fw = full.elites(0)
-        keys = torch.cat([s.score(SEED, it) for s in shards])
+        for s in shards:
+            s.score(SEED, it)
+        torch.cuda.synchronize()                     # the shards run on their own streams
+        keys = torch.cat([s.keys for s in shards])
         torch.cuda.synchronize()
         for s in shards:
             s.merge(keys, 2, SEED, it)
