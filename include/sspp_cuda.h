@@ -40,6 +40,9 @@ extern "C" {
 #define SSPPCU_MODE_JOINT 0  /* planner A: sspp::SamplingPathPlanner<kDOF>, joint space, cubic */
 #define SSPPCU_MODE_TASK 1   /* planner B: tsp::Planner, (x,y,z,yaw) of a free body, quadratic */
 
+#define SSPPCU_COLLIDE_PRIMITIVES 0  /* analytic primitive pairs (MuJoCo's narrow phase restated) */
+#define SSPPCU_COLLIDE_SDF 1         /* static scene baked into a dense signed-distance grid, moving geoms sphere-sampled */
+
 #define SSPPCU_ST_CONVERGED 0
 #define SSPPCU_ST_FAILED 1
 #define SSPPCU_ST_ABSENT 2   /* the forwarded-best slot of a cold iteration */
@@ -83,6 +86,14 @@ typedef struct SsppPlannerConfig {
   double sample_zmin;      /* cfg_.z_min (tsp_sampler.h:47) */
   double dist_zmin;        /* dist_.z_min (tsp_distribution.h:64) */
   double lo[SSPPCU_MAX_DOF], hi[SSPPCU_MAX_DOF];   /* sampler limits / mean clamp */
+  /* collision back end */
+  int32_t collision_mode;  /* SSPPCU_COLLIDE_PRIMITIVES (default) or SSPPCU_COLLIDE_SDF */
+  int32_t use_center_dist; /* TASK cost per contact: 1 = -1/(centre distance + 1e-4), 0 = -dist (Collision.h:84,93-98);
+                              SDF mode always uses -dist (a grid has no geom centres) */
+  int32_t sdf_dims[3];     /* grid nodes per axis (SDF mode), e.g. 128 128 128 */
+  int32_t reserved_;
+  double sdf_lo[3], sdf_hi[3];   /* world box the grid spans */
+  double sdf_sphere_ratio; /* sample-sphere radius / smallest half extent of a moving box (default 0.5) */
 } SsppPlannerConfig;
 
 /* sizes derived from a config, for sizing caller buffers */
@@ -161,6 +172,11 @@ int ssppcu_device_view(ssppcu_t* h, SsppDeviceView* out);
 /* Score explicit spline points: pts [n][dof] host floats -> collision cost per point (the
  * contact rule of the handle's mode).  The unit check of FK + narrow phase. */
 int ssppcu_eval_points(ssppcu_t* h, const float* pts, int n, float* cost_out);
+
+/* SDF mode: the baked node grid [nz][ny][nx] (host copy) and its geometry; nodes may be NULL to query sizes */
+int ssppcu_get_sdf(ssppcu_t* h, float* nodes, int32_t dims[3], double lo[3], double cell[3]);
+/* SDF mode: sample spheres of the moving geoms, [n][5] = centre (body frame) x,y,z, radius, body index; returns n */
+int ssppcu_get_spheres(ssppcu_t* h, float* out, int cap);
 
 /* collocation matrices the handle applies (host copies, row-major [rows][n_points]) */
 int ssppcu_get_collocation(ssppcu_t* h, float* psi_collision, float* psi_arc);

@@ -70,7 +70,24 @@ struct Model {
   std::vector<double> bpos, bquat, jaxis, jpos, qpos0, gsize, gpos, gquat, gmargin;
   int mode, dof, plan_body;
   std::vector<std::pair<int, int>> pairs;   // geom pairs that pass MuJoCo's filters
+  // SDF collision mode (build-defined, not in the reference): FP64 grid of the static partners + sample spheres
+  bool sdf = false;
+  int nx = 0, ny = 0, nz = 0;
+  double glo[3], gh[3];
+  std::vector<double> nodes;
+  struct Sph { V3 c; double r; int body; };
+  std::vector<Sph> spheres;
+  double sdf_margin = 0.0;
 };
+
+std::vector<char> moving_bodies(const Model& m) {
+  std::vector<char> mv(m.nbody, 0);
+  for (int b = 1; b < m.nbody; ++b) {
+    const bool planned = (m.mode == 0) ? ((m.jtype[b] == 2 || m.jtype[b] == 3) && m.qadr[b] >= 0 && m.qadr[b] < m.dof) : (b == m.plan_body);
+    mv[b] = planned || mv[m.parent[b]];
+  }
+  return mv;
+}
 
 bool filter_pass(const Model& m, int g1, int g2) {
   const int b1 = m.gbody[g1], b2 = m.gbody[g2];
@@ -262,6 +279,27 @@ double geom_dist(const Geom& A0, const Geom& B0, bool* ok) {
   return std::numeric_limits<double>::infinity();
 }
 
+double point_geom(V3 x, const Geom& G) {   // exact signed distance of a point to a primitive
+  switch (G.type) {
+    case 0: return dot(G.ax[2], x - G.p);
+    case 2: return norm(x - G.p) - G.s.x;
+    case 3: return point_segment(x, G.p - G.s.y * G.ax[2], G.p + G.s.y * G.ax[2]) - G.s.x;
+    case 5: return point_cyl(x, G);
+    default: return point_box(to_local(G, x), G.s);
+  }
+}
+double sdf_value(const Model& m, V3 x) {   // trilinear interpolation, coordinates clamped to the grid
+  const double g[3] = {std::min(std::max((x.x - m.glo[0]) / m.gh[0], 0.0), (double)(m.nx - 1)),
+                       std::min(std::max((x.y - m.glo[1]) / m.gh[1], 0.0), (double)(m.ny - 1)),
+                       std::min(std::max((x.z - m.glo[2]) / m.gh[2], 0.0), (double)(m.nz - 1))};
+  const int i = std::min((int)g[0], m.nx - 2), j = std::min((int)g[1], m.ny - 2), k = std::min((int)g[2], m.nz - 2);
+  const double fx = g[0] - i, fy = g[1] - j, fz = g[2] - k;
+  auto N = [&](int a, int b, int c) { return m.nodes[((size_t)(k + c) * m.ny + (j + b)) * m.nx + (i + a)]; };
+  const double c00 = N(0, 0, 0) * (1 - fx) + N(1, 0, 0) * fx, c10 = N(0, 1, 0) * (1 - fx) + N(1, 1, 0) * fx;
+  const double c01 = N(0, 0, 1) * (1 - fx) + N(1, 0, 1) * fx, c11 = N(0, 1, 1) * (1 - fx) + N(1, 1, 1) * fx;
+  return (c00 * (1 - fy) + c10 * fy) * (1 - fz) + (c01 * (1 - fy) + c11 * fy) * fz;
+}
+
 // collision cost of one configuration: the whole scene, as mj_forward + the reference's read-out
 double point_cost(const Model& m, const double* q, int* ncon_out, double* min_dist_out) {
   std::vector<V3> xpos; std::vector<Quat> xquat; std::vector<Geom> G;
@@ -269,6 +307,20 @@ double point_cost(const Model& m, const double* q, int* ncon_out, double* min_di
   geom_frames(m, xpos, xquat, G);
   double cost = 0.0, mind = std::numeric_limits<double>::infinity();
   int ncon = 0;
+  if (m.sdf) {   // sphere samples against the trilinear grid; cost rule of Collision.h:97-98 (use_center_dist = false)
+    for (const auto& sp : m.spheres) {
+      const V3 c = xpos[sp.body] + qrot(xquat[sp.body], sp.c);
+      const double d = sdf_value(m, c) - sp.r;
+      mind = std::min(mind, d);
+      if (!(d < m.sdf_margin)) continue;
+      ++ncon;
+      if (m.mode == 0) cost += 1.0;
+      else if (d < -1e-3) cost += -d;
+    }
+    if (ncon_out) *ncon_out = ncon;
+    if (min_dist_out) *min_dist_out = mind;
+    return cost;
+  }
   for (const auto& pr : m.pairs) {
     bool ok;
     const double d = geom_dist(G[pr.first], G[pr.second], &ok);
@@ -385,6 +437,47 @@ void* o1_create(const FlatView* v, int mode, int dof, int plan_body) {
 void o1_destroy(void* h) { delete static_cast<Model*>(h); }
 int o1_num_pairs(void* h) { return (int)static_cast<Model*>(h)->pairs.size(); }
 void o1_get_pairs(void* h, int32_t* out) { int k = 0; for (auto& p : static_cast<Model*>(h)->pairs) { out[k++] = p.first; out[k++] = p.second; } }
+
+// SDF mode: bake the FP64 grid from the static partners of the moving geoms (at the model's initial
+// pose) and take the sample spheres [n][5] = centre (frame of the k-th planned body), radius, k
+void o1_set_sdf(void* h, const int32_t* dims, const double* lo, const double* hi, const float* spheres, int n_spheres, double margin) {
+  Model& m = *static_cast<Model*>(h);
+  m.nx = dims[0]; m.ny = dims[1]; m.nz = dims[2];
+  const int d3[3] = {m.nx, m.ny, m.nz};
+  for (int a = 0; a < 3; ++a) {   // the product defines the cell size in FP32; the node positions are inputs like the samples
+    const float lo32 = (float)lo[a], h32 = (float)((hi[a] - lo[a]) / (d3[a] - 1));
+    m.glo[a] = lo32; m.gh[a] = h32;
+  }
+  const std::vector<char> mv = moving_bodies(m);
+  std::vector<char> obstacle(m.ngeom, 0);
+  for (const auto& pr : m.pairs) {
+    const bool m1 = mv[m.gbody[pr.first]], m2 = mv[m.gbody[pr.second]];
+    if (m1 && !m2) obstacle[pr.second] = 1;
+    if (m2 && !m1) obstacle[pr.first] = 1;
+  }
+  std::vector<V3> xpos; std::vector<Quat> xquat; std::vector<Geom> G;
+  kinematics(m, m.qpos0, xpos, xquat);
+  geom_frames(m, xpos, xquat, G);
+  m.nodes.assign((size_t)m.nx * m.ny * m.nz, 0.0);
+#pragma omp parallel for schedule(static)
+  for (int k = 0; k < m.nz; ++k)
+    for (int j = 0; j < m.ny; ++j)
+      for (int i = 0; i < m.nx; ++i) {
+        const V3 x{m.glo[0] + i * m.gh[0], m.glo[1] + j * m.gh[1], m.glo[2] + k * m.gh[2]};
+        double best = std::numeric_limits<double>::infinity();
+        for (int g = 0; g < m.ngeom; ++g) if (obstacle[g]) best = std::min(best, point_geom(x, G[g]));
+        m.nodes[((size_t)k * m.ny + j) * m.nx + i] = best;
+      }
+  std::vector<int> planned;   // the k-th planned body in id order (the product's moving-body numbering)
+  for (int b = 1; b < m.nbody; ++b)
+    if ((m.mode == 0) ? ((m.jtype[b] == 2 || m.jtype[b] == 3) && m.qadr[b] >= 0 && m.qadr[b] < m.dof) : (b == m.plan_body)) planned.push_back(b);
+  m.spheres.clear();
+  for (int s = 0; s < n_spheres; ++s)
+    m.spheres.push_back({V3{spheres[5 * s], spheres[5 * s + 1], spheres[5 * s + 2]}, spheres[5 * s + 3], planned[(int)spheres[5 * s + 4]]});
+  m.sdf_margin = margin;
+  m.sdf = true;
+}
+void o1_get_sdf(void* h, double* nodes) { const Model& m = *static_cast<Model*>(h); std::copy(m.nodes.begin(), m.nodes.end(), nodes); }
 
 double o1_point_cost(void* h, const double* q, int32_t* ncon, double* min_dist) {
   int nc; double md;

@@ -24,6 +24,7 @@ namespace {
 struct Replica {
   DevModel dev;
   ScoreConfig cfg;
+  std::vector<float> nodes;   // SDF mode: the node grid, baked with the same function as the device kernel
 };
 
 struct HostXF {
@@ -60,7 +61,27 @@ void* o2_create(const char* mjcf_path, const SsppPlannerConfig* c, char* err, si
     sspp::FlatModel fm = sspp::load_mjcf(mjcf_path);
     Replica* r = new Replica;
     const bool task = c->mode == SSPPCU_MODE_TASK;
-    r->dev = sspp::compile_model(fm, task ? sspp::PLAN_TASK : sspp::PLAN_JOINT, c->dof, c->body_name ? c->body_name : "", nullptr);
+    sspp::CompileOptions opt;
+    opt.sdf = c->collision_mode == SSPPCU_COLLIDE_SDF;
+    opt.sphere_ratio = c->sdf_sphere_ratio > 0 ? c->sdf_sphere_ratio : 0.5;
+    opt.use_center_dist = c->use_center_dist != 0;
+    r->dev = sspp::compile_model(fm, task ? sspp::PLAN_TASK : sspp::PLAN_JOINT, c->dof, c->body_name ? c->body_name : "", nullptr, opt);
+    if (r->dev.sdf_mode) {      // same grid geometry arithmetic as ssppcu_create
+      SdfGrid& g = r->dev.grid;
+      g.nx = c->sdf_dims[0]; g.ny = c->sdf_dims[1]; g.nz = c->sdf_dims[2];
+      const int dims[3] = {g.nx, g.ny, g.nz};
+      for (int a = 0; a < 3; ++a) {
+        g.lo[a] = (float)c->sdf_lo[a];
+        g.h[a] = (float)((c->sdf_hi[a] - c->sdf_lo[a]) / (dims[a] - 1));
+        g.inv_h[a] = 1.0f / g.h[a];
+      }
+      r->nodes.resize((size_t)g.nx * g.ny * g.nz);
+#pragma omp parallel for schedule(static)
+      for (int k = 0; k < g.nz; ++k)
+        for (int j = 0; j < g.ny; ++j)
+          for (int i = 0; i < g.nx; ++i) r->nodes[((size_t)k * g.ny + j) * g.nx + i] = sdf_node_value(r->dev, i, j, k);
+      g.nodes = r->nodes.data(); g.cells = nullptr;
+    }
     ScoreConfig& s = r->cfg;
     std::memset(&s, 0, sizeof(s));
     s.mode = task ? MODE_TASK : MODE_JOINT;
@@ -85,6 +106,19 @@ void* o2_create(const char* mjcf_path, const SsppPlannerConfig* c, char* err, si
   }
 }
 void o2_destroy(void* h) { delete static_cast<Replica*>(h); }
+const float* o2_sdf_nodes(void* h, int32_t dims[3]) {
+  Replica* r = static_cast<Replica*>(h);
+  dims[0] = r->dev.grid.nx; dims[1] = r->dev.grid.ny; dims[2] = r->dev.grid.nz;
+  return r->nodes.data();
+}
+int o2_spheres(void* h, float* out, int cap) {   // [n][5] like ssppcu_get_spheres
+  const DevModel& d = static_cast<Replica*>(h)->dev;
+  for (int i = 0; out && i < d.n_sphere && i < cap; ++i) {
+    out[5 * i] = d.sph[i].c[0]; out[5 * i + 1] = d.sph[i].c[1]; out[5 * i + 2] = d.sph[i].c[2]; out[5 * i + 3] = d.sph[i].r; out[5 * i + 4] = (float)d.sph[i].body;
+  }
+  return d.n_sphere;
+}
+float o2_sdf_sample(void* h, const float* x) { return sdf_sample_nodes(static_cast<Replica*>(h)->dev.grid, mk(x[0], x[1], x[2])); }
 int o2_n_cand(void* h) { return static_cast<Replica*>(h)->cfg.n_cand; }
 
 float o2_point_cost(void* h, const float* q) {

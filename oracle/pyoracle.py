@@ -88,6 +88,8 @@ class O1:
         L.o1_spline_eval.argtypes = [_dp, C.c_int, C.c_int, C.c_int, C.c_double, _dp]
         L.o1_spline_eval_knots.argtypes = [_dp, C.c_int, C.c_int, C.c_int, _dp, C.c_double, _dp]
         L.o1_basis_row.argtypes = [C.c_int, C.c_int, _dp, C.c_double, _dp]
+        L.o1_set_sdf.argtypes = [C.c_void_p, C.c_void_p, _dp, _dp, C.c_void_p, C.c_int, C.c_double]
+        L.o1_get_sdf.argtypes = [C.c_void_p, _dp]
         self.model = model
         self.mode, self.dof = mode, dof
         plan_body = model.body_id(body) if mode == 1 else -1
@@ -100,6 +102,19 @@ class O1:
         if getattr(self, "h", None):
             self.lib.o1_destroy(self.h)
             self.h = None
+
+    def set_sdf(self, dims, lo, hi, spheres, margin: float = 0.0):
+        """switch to the SDF collision mode: FP64 grid of the static partners, sample spheres as an input"""
+        d = np.ascontiguousarray(dims, np.int32); lo = np.ascontiguousarray(lo, np.float64); hi = np.ascontiguousarray(hi, np.float64)
+        sp = np.ascontiguousarray(spheres, np.float32)
+        self._sdf_dims = tuple(int(x) for x in d)
+        self.lib.o1_set_sdf(self.h, d.ctypes.data_as(C.c_void_p), _d(lo), _d(hi), sp.ctypes.data_as(C.c_void_p), len(sp), float(margin))
+
+    def sdf_nodes(self) -> np.ndarray:
+        nx, ny, nz = self._sdf_dims
+        out = np.zeros((nz, ny, nx))
+        self.lib.o1_get_sdf(self.h, _d(out))
+        return out
 
     def pairs(self) -> np.ndarray:
         n = self.lib.o1_num_pairs(self.h)
@@ -217,6 +232,10 @@ class O2:
         L.o2_sincos.argtypes = [C.c_float, C.POINTER(C.c_float), C.POINTER(C.c_float)]
         L.o2_philox.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
         L.o2_iterate.argtypes = [C.c_void_p] + [C.c_void_p] * 7 + [C.c_uint64, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 11
+        L.o2_sdf_nodes.restype = C.POINTER(C.c_float)
+        L.o2_sdf_nodes.argtypes = [C.c_void_p, C.POINTER(C.c_int32 * 3)]
+        L.o2_sdf_sample.restype = C.c_float
+        L.o2_sdf_sample.argtypes = [C.c_void_p, C.c_void_p]
         L.o2_merge_update.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_uint32] + [C.c_void_p] * 7
         err = C.create_string_buffer(1024)
         self.cfg = planner_cfg
@@ -237,6 +256,22 @@ class O2:
     def point_cost(self, q) -> float:
         q = np.ascontiguousarray(q, np.float32)
         return self.lib.o2_point_cost(self.h, q.ctypes.data_as(C.c_void_p))
+
+    def sdf_nodes(self) -> np.ndarray:
+        dims = (C.c_int32 * 3)()
+        p = self.lib.o2_sdf_nodes(self.h, C.byref(dims))
+        return np.ctypeslib.as_array(p, shape=(dims[2], dims[1], dims[0])).copy()
+
+    def spheres(self) -> np.ndarray:
+        self.lib.o2_spheres.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        n = self.lib.o2_spheres(self.h, None, 0)
+        out = np.zeros((max(n, 1), 5), np.float32)
+        self.lib.o2_spheres(self.h, out.ctypes.data_as(C.c_void_p), n)
+        return out[:n]
+
+    def sdf_sample(self, x) -> float:
+        x = np.ascontiguousarray(x, np.float32)
+        return self.lib.o2_sdf_sample(self.h, x.ctypes.data_as(C.c_void_p))
 
     def normal(self, seed, it, query, cand, stream, j) -> float:
         return self.lib.o2_normal(C.c_uint64(seed), it, query, cand, stream, j)

@@ -13,10 +13,11 @@ from pathlib import Path
 import numpy as np
 
 _HERE = Path(__file__).resolve().parent
-LIB_PATH = _HERE / "csrc" / "libsspp_cuda.so"
+LIB_PATH = Path(os.environ.get("SSPP_CUDA_LIB", _HERE / "csrc" / "libsspp_cuda.so"))   # override: kernel experiments only
 
 MAX_DOF = 9
 MODE_JOINT, MODE_TASK = 0, 1
+COLLIDE_PRIMITIVES, COLLIDE_SDF = 0, 1
 ST_CONVERGED, ST_FAILED, ST_ABSENT = 0, 1, 2
 OK, EINVAL, EMODEL, ECUDA, ELIMIT = 0, -1, -2, -3, -4
 
@@ -61,7 +62,9 @@ class PlannerConfig(C.Structure):
                 ("stddev_min", C.c_double), ("stddev_max", C.c_double),
                 ("eval_zmin", C.c_double), ("floor_margin", C.c_double), ("floor_scale", C.c_double),
                 ("limit_scale", C.c_double), ("sample_zmin", C.c_double), ("dist_zmin", C.c_double),
-                ("lo", C.c_double * MAX_DOF), ("hi", C.c_double * MAX_DOF)]
+                ("lo", C.c_double * MAX_DOF), ("hi", C.c_double * MAX_DOF),
+                ("collision_mode", C.c_int32), ("use_center_dist", C.c_int32), ("sdf_dims", C.c_int32 * 3), ("reserved_", C.c_int32),
+                ("sdf_lo", C.c_double * 3), ("sdf_hi", C.c_double * 3), ("sdf_sphere_ratio", C.c_double)]
 
 
 class Dims(C.Structure):
@@ -87,7 +90,7 @@ SYMBOLS = [
     "ssppcu_get_params", "ssppcu_get_best", "ssppcu_get_elites", "ssppcu_device_view", "ssppcu_eval_points",
     "ssppcu_get_collocation", "ssppcu_get_base", "ssppcu_shard_keys", "ssppcu_merge_update", "ssppcu_version",
     "ssppcu_spline_setup", "ssppcu_collocation_matrix", "ssppcu_save_state", "ssppcu_restore_state",
-    "ssppcu_fp32_peak", "ssppcu_get_merged",
+    "ssppcu_fp32_peak", "ssppcu_get_merged", "ssppcu_get_sdf", "ssppcu_get_spheres",
 ]
 
 lib = _load()
@@ -130,6 +133,8 @@ lib.ssppcu_get_base.argtypes = [C.c_void_p, C.c_void_p]
 lib.ssppcu_shard_keys.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), _ip]
 lib.ssppcu_merge_update.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_uint32]
 lib.ssppcu_get_merged.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+lib.ssppcu_get_sdf.argtypes = [C.c_void_p, C.c_void_p, _ip, _dp, _dp]
+lib.ssppcu_get_spheres.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
 lib.ssppcu_save_state.argtypes = [C.c_void_p]
 lib.ssppcu_restore_state.argtypes = [C.c_void_p]
 lib.ssppcu_fp32_peak.argtypes = [C.c_int, _dp, _dp]
@@ -378,6 +383,20 @@ class Handle:
         out = np.zeros(len(p), np.float32)
         self._ck(lib.ssppcu_eval_points(self._h, _ptr(p), len(p), _ptr(out)))
         return out
+
+    def sdf(self):
+        """(nodes [nz][ny][nx] float32, lo[3], cell[3]) of an SDF-mode handle"""
+        dims = (C.c_int32 * 3)(); lo = np.zeros(3); cell = np.zeros(3)
+        self._ck(lib.ssppcu_get_sdf(self._h, None, dims, _dptr(lo), _dptr(cell)))
+        nodes = np.zeros((dims[2], dims[1], dims[0]), np.float32)
+        self._ck(lib.ssppcu_get_sdf(self._h, _ptr(nodes), dims, _dptr(lo), _dptr(cell)))
+        return nodes, lo, cell
+
+    def spheres(self) -> np.ndarray:
+        n = lib.ssppcu_get_spheres(self._h, None, 0)
+        out = np.zeros((max(n, 1), 5), np.float32)
+        lib.ssppcu_get_spheres(self._h, _ptr(out), n)
+        return out[:n]
 
     def collocation(self):
         d = self.dims

@@ -156,6 +156,8 @@ void ssppcu_default_config(int mode, SsppPlannerConfig* c) {
   c->mode = mode;
   c->n_queries = 1;
   c->elite_fraction = 0.3;
+  c->collision_mode = SSPPCU_COLLIDE_PRIMITIVES; c->use_center_dist = 1; c->sdf_sphere_ratio = 0.5;
+  c->sdf_dims[0] = c->sdf_dims[1] = c->sdf_dims[2] = 128;
   if (mode == SSPPCU_MODE_JOINT) {        // sspp.h:195-196 defaults; classic planner A does no CES update
     c->dof = 7; c->degree = 3; c->n_points = 10; c->check_points = 50; c->n_samples = 50;
     c->w_collision = 0.0; c->inc = 1.5; c->dec = 0.95; c->var_beta = 0.2; c->mean_lr = 0.5;
@@ -211,9 +213,26 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
   h->body_name = c.body_name ? c.body_name : "";
   h->cfg.body_name = nullptr;
   try {
-    h->dev = compile_model(mm->m, task ? PLAN_TASK : PLAN_JOINT, c.dof, h->body_name, nullptr);
+    CompileOptions opt;
+    opt.sdf = c.collision_mode == SSPPCU_COLLIDE_SDF;
+    opt.sphere_ratio = c.sdf_sphere_ratio > 0 ? c.sdf_sphere_ratio : 0.5;
+    opt.use_center_dist = c.use_center_dist != 0;
+    h->dev = compile_model(mm->m, task ? PLAN_TASK : PLAN_JOINT, c.dof, h->body_name, nullptr, opt);
     h->spl = make_setup(c.n_points, c.degree);
   } catch (const std::exception& e) { set_err(err, errlen, e.what()); delete h; return SSPPCU_EMODEL; }
+  if (c.collision_mode != SSPPCU_COLLIDE_PRIMITIVES && c.collision_mode != SSPPCU_COLLIDE_SDF) { set_err(err, errlen, "unknown collision_mode"); delete h; return SSPPCU_EINVAL; }
+  if (h->dev.sdf_mode) {
+    ssppm::SdfGrid& g = h->dev.grid;
+    g.nx = c.sdf_dims[0]; g.ny = c.sdf_dims[1]; g.nz = c.sdf_dims[2];
+    if (g.nx < 2 || g.ny < 2 || g.nz < 2 || (double)g.nx * g.ny * g.nz > 512.0 * 512 * 512) { set_err(err, errlen, "sdf_dims must be in [2, 512^3 nodes]"); delete h; return SSPPCU_EINVAL; }
+    const int dims[3] = {g.nx, g.ny, g.nz};
+    for (int a = 0; a < 3; ++a) {
+      if (!(c.sdf_hi[a] > c.sdf_lo[a])) { set_err(err, errlen, "sdf_hi must exceed sdf_lo on every axis"); delete h; return SSPPCU_EINVAL; }
+      g.lo[a] = (float)c.sdf_lo[a];
+      g.h[a] = (float)((c.sdf_hi[a] - c.sdf_lo[a]) / (dims[a] - 1));
+      g.inv_h[a] = 1.0f / g.h[a];
+    }
+  }
   // ---- collocation grids (sspp.h:134-137,157-160; tsp_evaluator.h:19-24) ----
   const int M = c.check_points;
   std::vector<double> gcol, garc;
@@ -276,37 +295,45 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
   h->smem = iterate_smem_bytes(h->dev, P, h->threads);
   const bool one_cta_ok = h->smem <= std::min<size_t>(smem_cap, 64 * 1024) && (long)s.n_cand * s.Mc <= 4096 && c.n_queries >= h->n_sm;
   if (!one_cta_ok) {
+    // one wave of tiles over the co-resident CTAs: guess the residency, shape the tiles, ask the
+    // occupancy calculator, and reshape once if it answers differently
     P.coop = 1;
     h->threads = 256;
-    int ctas = std::max(1, std::min(s.n_cand, (2 * h->n_sm + c.n_queries - 1) / c.n_queries));
-    for (;;) {
-      P.cand_per_cta = (s.n_cand + ctas - 1) / ctas;
-      P.ctas_per_query = (s.n_cand + P.cand_per_cta - 1) / P.cand_per_cta;
-      h->smem = iterate_smem_bytes(h->dev, P, h->threads);
-      if (h->smem <= std::min<size_t>(smem_cap, 100 * 1024) || P.cand_per_cta == 1) break;
-      ctas = std::min(s.n_cand, ctas * 2);
-    }
-  }
-  if (h->smem > smem_cap) { set_err(err, errlen, "problem shape needs more shared memory than a CTA has"); delete h; return SSPPCU_ELIMIT; }
-  P.n_tiles = P.ctas_per_query * c.n_queries;
-  h->grid = P.n_tiles;
-  if (P.coop) {
-    // ranking scratch: a chunk of keys + this CTA's own keys and counters; grid = co-resident CTAs
-    int per_sm = 0;
-    for (int pass = 0; pass < 2; ++pass) {
-      if ((ce = iterate_occupancy(h->threads, h->smem, &per_sm)) != cudaSuccess || per_sm < 1) {
+    int per_sm = 2;
+    for (int round = 0; round < 3; ++round) {
+      int ctas = std::max(1, std::min(s.n_cand, (per_sm * h->n_sm + c.n_queries - 1) / c.n_queries));
+      for (;;) {
+        P.cand_per_cta = (s.n_cand + ctas - 1) / ctas;
+        P.ctas_per_query = (s.n_cand + P.cand_per_cta - 1) / P.cand_per_cta;
+        h->smem = iterate_smem_bytes(h->dev, P, h->threads);
+        if (h->smem <= std::min<size_t>(smem_cap, 100 * 1024) || P.cand_per_cta == 1) break;
+        ctas = std::min(s.n_cand, ctas * 2);
+      }
+      if (h->smem > smem_cap) { set_err(err, errlen, "problem shape needs more shared memory than a CTA has"); delete h; return SSPPCU_ELIMIT; }
+      P.n_tiles = P.ctas_per_query * c.n_queries;
+      // ranking scratch (phase B reuses the scoring shared memory): a chunk of keys + this CTA's own keys and counters
+      const long long total = (long long)c.n_queries * s.n_cand;
+      const int grid_guess = std::min(P.n_tiles, per_sm * h->n_sm);
+      const long long per = (total + grid_guess - 1) / grid_guess;
+      const size_t fixed = (size_t)per * 12 + 64;
+      if (fixed + 256 * 8 > smem_cap) { set_err(err, errlen, "population too large for the ranking scratch"); delete h; return SSPPCU_ELIMIT; }
+      h->smem = std::max(h->smem, std::min<size_t>(std::min<size_t>((size_t)s.n_cand, 2048) * 8 + fixed, smem_cap));
+      int got = 0;
+      if ((ce = iterate_occupancy(h->threads, h->smem, &got)) != cudaSuccess || got < 1) {
         set_err(err, errlen, std::string("occupancy query failed: ") + cudaGetErrorString(ce)); delete h; return SSPPCU_ECUDA;
       }
-      h->grid = std::min(P.n_tiles, per_sm * h->n_sm);
-      const long long total = (long long)c.n_queries * s.n_cand;
-      const long long per = (total + h->grid - 1) / h->grid;
-      const size_t fixed = (size_t)per * 12 + 64;
-      const size_t want = std::min<size_t>((size_t)s.n_cand, 4096) * 8 + fixed;
-      if (fixed + 256 * 8 > smem_cap) { set_err(err, errlen, "population too large for the ranking scratch"); delete h; return SSPPCU_ELIMIT; }
-      if (want > h->smem && pass == 0) { h->smem = std::min(want, smem_cap); continue; }   // re-query occupancy with the larger footprint
-      P.rank_chunk = (int)std::min<size_t>((size_t)s.n_cand, (h->smem - fixed) / 8);
-      break;
+      h->grid = std::min(P.n_tiles, got * h->n_sm);
+      const long long per2 = (total + h->grid - 1) / h->grid;
+      const size_t fixed2 = (size_t)per2 * 12 + 64;
+      if (fixed2 + 256 * 8 > h->smem) { per_sm = std::max(1, got - 1); continue; }
+      P.rank_chunk = (int)std::min<size_t>((size_t)s.n_cand, (h->smem - fixed2) / 8);
+      if (got == per_sm || round == 2) break;
+      per_sm = got;
     }
+  } else {
+    if (h->smem > smem_cap) { set_err(err, errlen, "problem shape needs more shared memory than a CTA has"); delete h; return SSPPCU_ELIMIT; }
+    P.n_tiles = c.n_queries;
+    h->grid = P.n_tiles;
   }
   if ((ce = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking)) != cudaSuccess) { set_err(err, errlen, std::string("cudaStreamCreate: ") + cudaGetErrorString(ce)); delete h; return SSPPCU_ECUDA; }
   h->stream = h->own_stream;
@@ -342,6 +369,16 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
   if (ce == cudaSuccess && !band_arc.empty()) ce = cudaMemcpy(d_psi_arc, band_arc.data(), band_arc.size() * sizeof(float), cudaMemcpyHostToDevice);
   if (ce == cudaSuccess && !band_arc.empty()) ce = cudaMemcpy(d_first_arc, first_arc.data(), first_arc.size() * sizeof(int), cudaMemcpyHostToDevice);
   if (ce != cudaSuccess) { set_err(err, errlen, std::string("cudaMemcpy: ") + cudaGetErrorString(ce)); ssppcu_destroy(h); return SSPPCU_ECUDA; }
+  if (h->dev.sdf_mode) {
+    ssppm::SdfGrid& g = h->dev.grid;
+    const size_t n_nodes = (size_t)g.nx * g.ny * g.nz, n_cells = (size_t)(g.nx - 1) * (g.ny - 1) * (g.nz - 1);
+    float *d_nodes = nullptr, *d_cells = nullptr;
+    if (dalloc(h, &d_nodes, n_nodes) || dalloc(h, &d_cells, n_cells * 8)) { set_err(err, errlen, h->err); ssppcu_destroy(h); return SSPPCU_ECUDA; }
+    g.nodes = d_nodes; g.cells = d_cells;
+    ce = launch_sdf_bake(h->dev, d_nodes, d_cells, h->stream);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(h->stream);
+    if (ce != cudaSuccess) { set_err(err, errlen, std::string("SDF bake: ") + cudaGetErrorString(ce)); ssppcu_destroy(h); return SSPPCU_ECUDA; }
+  }
   h->base_host.assign(Q * s.K * s.D, 0.0f);
   *out = h;
   return SSPPCU_OK;
@@ -622,6 +659,29 @@ int ssppcu_eval_points(ssppcu_t* h, const float* pts, int n, float* out) {
   CU(h, cudaMemcpyAsync(out, h->d_eval_out, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
   CU(h, cudaStreamSynchronize(h->stream));
   return SSPPCU_OK;
+}
+
+int ssppcu_get_sdf(ssppcu_t* h, float* nodes, int32_t dims[3], double lo[3], double cell[3]) {
+  if (int rc = check(h)) return rc;
+  if (!h->dev.sdf_mode) return fail(h, SSPPCU_EINVAL, "handle is not in SDF collision mode");
+  const ssppm::SdfGrid& g = h->dev.grid;
+  if (dims) { dims[0] = g.nx; dims[1] = g.ny; dims[2] = g.nz; }
+  for (int a = 0; a < 3; ++a) { if (lo) lo[a] = g.lo[a]; if (cell) cell[a] = g.h[a]; }
+  if (nodes) {
+    CU(h, cudaMemcpyAsync(nodes, g.nodes, (size_t)g.nx * g.ny * g.nz * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+  }
+  return SSPPCU_OK;
+}
+
+int ssppcu_get_spheres(ssppcu_t* h, float* out, int cap) {
+  if (!h) return SSPPCU_EINVAL;
+  const int n = std::min(cap, h->dev.n_sphere);
+  for (int i = 0; out && i < n; ++i) {
+    const ssppm::DevSphere& S = h->dev.sph[i];
+    out[5 * i] = S.c[0]; out[5 * i + 1] = S.c[1]; out[5 * i + 2] = S.c[2]; out[5 * i + 3] = S.r; out[5 * i + 4] = (float)S.body;
+  }
+  return h->dev.n_sphere;
 }
 
 int ssppcu_get_collocation(ssppcu_t* h, float* pc, float* pa) {

@@ -67,7 +67,7 @@ __device__ __forceinline__ bool key_success(unsigned long long key) { return (un
 // shared memory carve-up of the scoring phase (all 4-byte words)
 struct Smem {
   unsigned long long* keys;   // coop == 0 only: n_pad sort keys
-  float *psi_col, *psi_arc, *X, *q, *cc, *cw, *seg, *qs, *xf;
+  float *psi_col, *psi_arc, *X, *cc, *cw, *seg, *qs, *xf;
   int *first_col, *first_arc;
 };
 __device__ __forceinline__ Smem carve(unsigned char* raw, const ScoreConfig& c, const IterParams& P, int T) {
@@ -80,7 +80,6 @@ __device__ __forceinline__ Smem carve(unsigned char* raw, const ScoreConfig& c, 
   s.first_col = reinterpret_cast<int*>(sm); sm += c.Mc;
   s.first_arc = reinterpret_cast<int*>(sm); sm += c.arc_same ? 0 : c.Ma;
   s.X = sm;         sm += CT * c.K * c.D;
-  s.q = sm;         sm += CT * P.mq * c.D;
   s.cc = sm;        sm += CT * c.Mc;     // collision cost per point
   s.cw = sm;        sm += CT * c.Mc;     // collision cost + penalty per point
   s.seg = sm;       sm += CT * P.mq;     // segment lengths
@@ -129,16 +128,24 @@ __device__ __forceinline__ void score_tile(const DevModel& M, const IterParams& 
   }
   __syncthreads();
   // ---- K2-K4: spline point, kinematics, collision per (candidate, point) item ----
+  // Segment lengths (K5) are formed by the thread that owns the segment's end point, which evaluates
+  // the start point a second time instead of reading it from a staging buffer (a banded row is <= 4 FMA
+  // per coordinate): no per-point buffer, and the same bits as any other evaluation of that point.
   for (int w = tid; w < nc * Mc; w += T) {
     const int cl = w / Mc, m = w - cl * Mc;
     const float* row = s.psi_col + m * wc;
     const int first = s.first_col[m];
     const float* X = s.X + cl * K * D;
+    float s2 = 0.0f;
     for (int d = 0; d < D; ++d) {
       const float acc = spline_coord(row, first, P.w_col, X, D, d);
       s.qs[d * T + tid] = acc;
-      if (c.arc_same) s.q[(cl * Mq + m) * D + d] = acc;
+      if (c.arc_same && m > 0) {
+        const float df = acc - spline_coord(row - wc, s.first_col[m - 1], P.w_col, X, D, d);
+        s2 = fmaf(df, df, s2);
+      }
     }
+    if (c.arc_same && m > 0) s.seg[cl * Mq + m - 1] = sqrtf(s2);
     float cc = 0.0f, cw = 0.0f;
     if (m >= c.col_first) {
       cc = point_collision_cost(M, qa, xf);
@@ -148,22 +155,18 @@ __device__ __forceinline__ void score_tile(const DevModel& M, const IterParams& 
     s.cw[cl * Mc + m] = cw;
   }
   if (!c.arc_same) {
-    for (int w = tid; w < nc * Ma; w += T) {
-      const int cl = w / Ma, m = w - cl * Ma;
+    for (int w = tid; w < nc * (Ma - 1); w += T) {
+      const int cl = w / (Ma - 1), m = 1 + (w - cl * (Ma - 1));
       const float* row = s.psi_arc + m * wa;
-      const int first = s.first_arc[m];
       const float* X = s.X + cl * K * D;
-      for (int d = 0; d < D; ++d) s.q[(cl * Mq + m) * D + d] = spline_coord(row, first, P.w_arc, X, D, d);
+      const int f1 = s.first_arc[m], f0 = s.first_arc[m - 1];
+      float s2 = 0.0f;
+      for (int d = 0; d < D; ++d) {
+        const float df = spline_coord(row, f1, P.w_arc, X, D, d) - spline_coord(row - wa, f0, P.w_arc, X, D, d);
+        s2 = fmaf(df, df, s2);
+      }
+      s.seg[cl * Mq + m - 1] = sqrtf(s2);
     }
-  }
-  __syncthreads();
-  // ---- K5: segment lengths, then one warp per candidate reduces ----
-  for (int w = tid; w < nc * (Marc - 1); w += T) {
-    const int cl = w / (Marc - 1), m = 1 + (w - cl * (Marc - 1));
-    const float* a = s.q + (cl * Mq + m) * D;
-    float s2 = 0.0f;
-    for (int d = 0; d < D; ++d) { const float df = a[d] - a[d - D]; s2 = fmaf(df, df, s2); }
-    s.seg[cl * Mq + m - 1] = sqrtf(s2);
   }
   __syncthreads();
   for (int cl = warp; cl < nc; cl += nwarp) {
@@ -404,8 +407,11 @@ __device__ void update_phase(const IterParams& P) {
   }
 }
 
+#ifndef SSPP_MIN_CTAS
+#define SSPP_MIN_CTAS 2
+#endif
 template <bool COOP>
-__global__ void __launch_bounds__(256, 2)
+__global__ void __launch_bounds__(256, SSPP_MIN_CTAS)
 sspp_iterate_kernel(const __grid_constant__ DevModel M, const __grid_constant__ IterParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_int[4];
@@ -546,6 +552,29 @@ sspp_eval_points_kernel(const __grid_constant__ DevModel M, int D, const float* 
   out[i] = point_collision_cost(M, qa, xf);
 }
 
+// node value = min over the static primitives of the exact point-primitive signed distance
+__global__ void __launch_bounds__(256)
+sspp_sdf_bake_kernel(const __grid_constant__ DevModel M, float* __restrict__ nodes) {
+  const SdfGrid& g = M.grid;
+  const size_t n = (size_t)g.nx * g.ny * g.nz;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
+    const int i = (int)(e % g.nx), j = (int)((e / g.nx) % g.ny), k = (int)(e / ((size_t)g.nx * g.ny));
+    nodes[e] = sdf_node_value(M, i, j, k);
+  }
+}
+__global__ void __launch_bounds__(256)
+sspp_sdf_pack_kernel(const __grid_constant__ DevModel M, const float* __restrict__ nodes, float* __restrict__ cells) {
+  const SdfGrid& g = M.grid;
+  const int cx = g.nx - 1, cy = g.ny - 1, cz = g.nz - 1;
+  const size_t n = (size_t)cx * cy * cz;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
+    const int i = (int)(e % cx), j = (int)((e / cx) % cy), k = (int)(e / ((size_t)cx * cy));
+#pragma unroll
+    for (int c = 0; c < 8; ++c)
+      cells[e * 8 + c] = nodes[((size_t)(k + (c >> 2)) * g.ny + (j + ((c >> 1) & 1))) * g.nx + (i + (c & 1))];
+  }
+}
+
 __global__ void __launch_bounds__(256)
 sspp_fma_probe_kernel(float* sink, int iters) {
   float a[8];
@@ -566,6 +595,14 @@ sspp_fma_probe_kernel(float* sink, int iters) {
 
 }  // namespace
 
+cudaError_t launch_sdf_bake(const DevModel& M, float* nodes, float* cells, cudaStream_t stream) {
+  sspp_sdf_bake_kernel<<<148 * 8, 256, 0, stream>>>(M, nodes);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  sspp_sdf_pack_kernel<<<148 * 8, 256, 0, stream>>>(M, nodes, cells);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_fma_probe(float* sink, int blocks, int threads, int iters, cudaStream_t stream) {
   sspp_fma_probe_kernel<<<blocks, threads, 0, stream>>>(sink, iters);
   return cudaGetLastError();
@@ -576,7 +613,6 @@ size_t iterate_smem_bytes(const DevModel& M, const IterParams& P, int threads) {
   const int wc = P.w_col | 1, wa = P.w_arc | 1;
   size_t f = (size_t)c.Mc * (wc + 1) + (c.arc_same ? 0 : (size_t)c.Ma * (wa + 1));
   f += (size_t)P.cand_per_cta * c.K * c.D;
-  f += (size_t)P.cand_per_cta * P.mq * c.D;
   f += (size_t)P.cand_per_cta * c.Mc * 2;
   f += (size_t)P.cand_per_cta * P.mq;
   f += (size_t)c.D * threads;

@@ -75,6 +75,10 @@ cudaError_t launch_merge_update(const MergeParams& P, cudaStream_t stream);
 // collision cost of n explicit points pts[n][D] (unit check of kinematics + narrow phase)
 cudaError_t launch_eval_points(const ssppm::DevModel& M, int D, const float* pts, int n, float* out, cudaStream_t stream);
 
+// SDF mode: bake the node grid from the handle's static primitives (M.sg[0..n_sgeom)) and pack the
+// 8 corners of every cell contiguously for the kernel's two 16-byte loads per sample
+cudaError_t launch_sdf_bake(const ssppm::DevModel& M, float* nodes, float* cells, cudaStream_t stream);
+
 // FP32 FMA peak probe: every thread runs `iters` rounds of 8 independent FMA chains
 cudaError_t launch_fma_probe(float* sink, int blocks, int threads, int iters, cudaStream_t stream);
 

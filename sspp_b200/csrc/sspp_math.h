@@ -32,12 +32,13 @@ namespace ssppm {
 // limits of the flattened model (kernel-parameter resident, < 32 KB)
 // ----------------------------------------------------------------------------------------
 enum { MAX_MBODY = 16, MAX_MGEOM = 32, MAX_SGEOM = 112, MAX_PAIR = 1024, MAX_MMPAIR = 64,
-       MAX_DOF = 9, MAX_K = 16 };
+       MAX_DOF = 9, MAX_K = 16, MAX_SPHERE = 256 };
 
 enum GeomType { GT_PLANE = 0, GT_SPHERE = 2, GT_CAPSULE = 3, GT_CYLINDER = 5, GT_BOX = 6 };
 enum JointType { JT_NONE = 0, JT_HINGE = 1, JT_SLIDE = 2, JT_FREE4 = 3 };
 enum ContactRule { CR_COUNT = 0,   // planner A: every contact with dist < margin counts 1
-                   CR_CENTER = 1 };// planner B: dist < -1e-3 adds -1/(centre distance + 1e-4)
+                   CR_CENTER = 1,  // planner B: dist < -1e-3 adds -1/(centre distance + 1e-4)   (Collision.h:93-96)
+                   CR_DEPTH = 2 }; // planner B, use_center_dist = false: dist < -1e-3 adds -dist (Collision.h:97-98)
 
 struct DevBody {
   float pos[3];     // frame origin in the parent frame (world frame when parent < 0)
@@ -48,6 +49,7 @@ struct DevBody {
   int jtype;        // JointType
   int qidx;         // first planned coordinate this joint reads
   int geom_begin, geom_end;  // moving geoms attached to this body
+  int sph_begin, sph_end;    // SDF mode: sphere samples attached to this body
   int has_anchor;
   int axis_kind;    // 0,1,2: the joint axis is +-e_x, +-e_y, +-e_z (axis_sign); 3: general axis
   float axis_sign;
@@ -70,6 +72,15 @@ struct DevSGeom {
   int type;
 };
 struct DevPair { int s; float margin; };
+// SDF mode: a moving geom is sampled by spheres (centre in the frame of moving body `body`)
+struct DevSphere { float c[3]; float r; float margin; int body; };
+// dense signed-distance grid of the static scene: node (i,j,k) sits at lo + (i,j,k) * h
+struct SdfGrid {
+  int nx, ny, nz;
+  float lo[3], h[3], inv_h[3];
+  const float* nodes;   // [nz][ny][nx] node values (host replica; device read-back)
+  const float* cells;   // [(nz-1)][(ny-1)][(nx-1)][8] the 8 corners of every cell, contiguous (32 B = one sector)
+};
 struct DevMMPair { int a, b; float margin; };
 
 struct DevModel {
@@ -77,11 +88,15 @@ struct DevModel {
   int rule;          // ContactRule
   int chain;         // 1: parent[b] == b-1 for every b and no moving-moving pairs (no transform store)
   float static_cost; // contribution of pairs that never move (added to every point)
+  int sdf_mode;      // 1: static scene = SdfGrid, moving geoms = sphere samples (pairs unused)
+  int n_sphere;
+  SdfGrid grid;
   DevBody body[MAX_MBODY];
   DevMGeom mg[MAX_MGEOM];
   DevSGeom sg[MAX_SGEOM];
   DevPair pair[MAX_PAIR];
   DevMMPair mm[MAX_MMPAIR];
+  DevSphere sph[MAX_SPHERE];   // grouped by body: body[b].sph_begin .. sph_end
 };
 
 // ----------------------------------------------------------------------------------------
@@ -523,6 +538,69 @@ SSPP_HD float point_cyl_sd(v3 x, const Prim& C) {  // signed distance of a world
   return (out2 > 0.0f) ? sqrtf(out2) : fmaxf(dz, dr);
 }
 
+// ----------------------------------------------------------------------------------------
+// SDF mode: exact point-to-primitive signed distances (grid baking) and the trilinear read
+// ----------------------------------------------------------------------------------------
+SSPP_HD float point_prim_sd(v3 x, const Prim& G) {
+  if (G.type == GT_PLANE) return dot(col(G.R, 2), sub(x, G.p));
+  if (G.type == GT_SPHERE) { const v3 d = sub(x, G.p); return sqrtf(dot(d, d)) - G.s.x; }
+  if (G.type == GT_CAPSULE) {
+    const v3 ax = col(G.R, 2);
+    const v3 a0 = madd(ax, -G.s.y, G.p), dd = scale(ax, 2.0f * G.s.y);
+    return sqrtf(seg_point_dist2(a0, dd, dot(dd, dd), x)) - G.s.x;
+  }
+  if (G.type == GT_CYLINDER) return point_cyl_sd(x, G);
+  return point_box_sd(multv(G.R, sub(x, G.p)), G.s);
+}
+
+// cell index and fractions of a world point; points outside the grid read the boundary cell
+SSPP_HD void sdf_locate(const SdfGrid& g, v3 x, int* ix, int* iy, int* iz, float* fx, float* fy, float* fz) {
+  const float gx = clampf((x.x - g.lo[0]) * g.inv_h[0], 0.0f, (float)(g.nx - 1));
+  const float gy = clampf((x.y - g.lo[1]) * g.inv_h[1], 0.0f, (float)(g.ny - 1));
+  const float gz = clampf((x.z - g.lo[2]) * g.inv_h[2], 0.0f, (float)(g.nz - 1));
+  int i = (int)gx, j = (int)gy, k = (int)gz;
+  if (i > g.nx - 2) i = g.nx - 2;
+  if (j > g.ny - 2) j = g.ny - 2;
+  if (k > g.nz - 2) k = g.nz - 2;
+  *ix = i; *iy = j; *iz = k;
+  *fx = gx - (float)i; *fy = gy - (float)j; *fz = gz - (float)k;
+}
+// corners ordered v000 v100 v010 v110 v001 v101 v011 v111 (x fastest)
+SSPP_HD float trilerp(const float v[8], float fx, float fy, float fz) {
+  const float c00 = fmaf(fx, v[1] - v[0], v[0]), c10 = fmaf(fx, v[3] - v[2], v[2]);
+  const float c01 = fmaf(fx, v[5] - v[4], v[4]), c11 = fmaf(fx, v[7] - v[6], v[6]);
+  const float c0 = fmaf(fy, c10 - c00, c00), c1 = fmaf(fy, c11 - c01, c01);
+  return fmaf(fz, c1 - c0, c0);
+}
+// host / replica read from the node array
+SSPP_HD float sdf_sample_nodes(const SdfGrid& g, v3 x) {
+  int i, j, k; float fx, fy, fz;
+  sdf_locate(g, x, &i, &j, &k, &fx, &fy, &fz);
+  float v[8];
+#pragma unroll
+  for (int c = 0; c < 8; ++c)
+    v[c] = g.nodes[((size_t)(k + (c >> 2)) * g.ny + (j + ((c >> 1) & 1))) * g.nx + (i + (c & 1))];
+  return trilerp(v, fx, fy, fz);
+}
+// kernel read: the 8 corners of a cell are one 32-byte sector, fetched as two 16-byte read-only loads
+SSPP_HD float sdf_sample(const SdfGrid& g, v3 x) {
+#if defined(__CUDA_ARCH__)
+  int i, j, k; float fx, fy, fz;
+  sdf_locate(g, x, &i, &j, &k, &fx, &fy, &fz);
+  const float4* c = reinterpret_cast<const float4*>(g.cells) + 2 * (((size_t)k * (g.ny - 1) + j) * (g.nx - 1) + i);
+  const float4 a = __ldg(c), b = __ldg(c + 1);
+  const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+  return trilerp(v, fx, fy, fz);
+#else
+  return sdf_sample_nodes(g, x);
+#endif
+}
+// contribution of one sphere sample at signed distance d
+SSPP_HD float sphere_contact_cost(int rule, float d, float margin) {
+  if (rule == CR_COUNT) return (d < margin) ? 1.0f : 0.0f;
+  return (d < margin && d < -1e-3f) ? -d : 0.0f;
+}
+
 // signed distance between two world primitives; *ok = false for an unsupported pairing
 SSPP_HD float prim_sd(const Prim& A, const Prim& B, bool* ok) {
   *ok = true;
@@ -610,6 +688,7 @@ SSPP_HD float moving_static_sd(const Prim& P, const Prim& S, float thr) {
 // contribution of one geom pair at signed distance d (centres ca, cb) under the model's rule
 SSPP_HD float contact_cost(int rule, float d, float margin, v3 ca, v3 cb) {
   if (rule == CR_COUNT) return (d < margin) ? 1.0f : 0.0f;
+  if (rule == CR_DEPTH) return (d < margin && d < -1e-3f) ? -d : 0.0f;
   if (d < margin && d < -1e-3f) {
     const v3 w = sub(cb, ca);
     return -1.0f / (sqrtf(dot(w, w)) + 1e-4f);
@@ -668,6 +747,15 @@ SSPP_HD float point_collision_cost(const DevModel& M, QA& q, XF& xf) {
       for (int k = 0; k < 9; ++k) xf.put(b, k, R.a[k]);
       xf.put(b, 9, p.x); xf.put(b, 10, p.y); xf.put(b, 11, p.z);
     }
+    if (M.sdf_mode) {                                        // sphere samples of this body against the grid
+#pragma unroll 1
+      for (int k = B.sph_begin; k < B.sph_end; ++k) {
+        const DevSphere& S = M.sph[k];
+        const float d = sdf_sample(M.grid, add(p, mulv(R, ld3(S.c)))) - S.r;
+        cost += sphere_contact_cost(M.rule, d, S.margin);
+      }
+      continue;
+    }
 #pragma unroll 1
     for (int g = B.geom_begin; g < B.geom_end; ++g) {
       const DevMGeom& G = M.mg[g];
@@ -714,6 +802,15 @@ SSPP_HD float point_collision_cost(const DevModel& M, QA& q, XF& xf) {
     cost += contact_cost(M.rule, d, M.mm[k].margin, P.p, Q.p);
   }
   return cost;
+}
+
+// value of grid node (i,j,k): min over the static primitives (shared by the bake kernel and the replica)
+SSPP_HD float sdf_node_value(const DevModel& M, int i, int j, int k) {
+  const SdfGrid& g = M.grid;
+  const v3 x = mk(fmaf((float)i, g.h[0], g.lo[0]), fmaf((float)j, g.h[1], g.lo[1]), fmaf((float)k, g.h[2], g.lo[2]));
+  float best = 3.0e38f;
+  for (int s = 0; s < M.n_sgeom; ++s) best = fminf(best, point_prim_sd(x, static_prim(M.sg[s])));
+  return best;
 }
 
 // floor penalty (include/sspp/tsp_evaluator.h:10-14) and its joint-space analogue

@@ -413,7 +413,49 @@ struct Xf { double R[9]; double p[3]; };
 
 }  // namespace
 
-ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const std::string& body, CompileInfo* info) {
+// Spheres inscribed in a primitive.  Boxes: radius rho = ratio * smallest half extent, centres on a
+// lattice with spacing <= rho that reaches h - rho on every axis.  Capsules: radius r along the axis,
+// spacing <= ratio * r.  Cylinders: rho = ratio * min(r, half length) on axial layers, a centre line plus
+// rings out to r - rho.  Spheres: themselves.
+void sample_spheres(int type, const double* size, double ratio, std::vector<double>* out) {
+  using namespace ssppm;
+  auto lattice = [](double h, double rho) {     // coordinates covering [-(h-rho), h-rho] with spacing <= rho
+    std::vector<double> v;
+    const double span = std::max(0.0, h - rho);
+    const int n = (span <= 1e-12) ? 1 : 1 + (int)std::ceil(2.0 * span / rho - 1e-9);
+    for (int i = 0; i < n; ++i) v.push_back(n == 1 ? 0.0 : -span + 2.0 * span * i / (n - 1));
+    return v;
+  };
+  auto push = [&](double x, double y, double z, double r) { out->push_back(x); out->push_back(y); out->push_back(z); out->push_back(r); };
+  ratio = std::min(1.0, std::max(0.05, ratio));
+  if (type == GT_SPHERE) { push(0, 0, 0, size[0]); return; }
+  if (type == GT_CAPSULE) {
+    const double r = size[0], h = size[1];
+    const int n = 1 + (int)std::ceil(2.0 * h / (ratio * r) - 1e-9);
+    for (int i = 0; i < n; ++i) push(0, 0, n == 1 ? 0.0 : -h + 2.0 * h * i / (n - 1), r);
+    return;
+  }
+  if (type == GT_CYLINDER) {
+    const double r = size[0], h = size[1], rho = ratio * std::min(r, h);
+    for (double z : lattice(h, rho)) {
+      push(0, 0, z, rho);
+      for (double rr = rho; rr <= r - rho + 1e-12; rr += rho) {
+        const int n = std::max(3, (int)std::ceil(2.0 * M_PI * rr / rho));
+        for (int i = 0; i < n; ++i) push(rr * std::cos(2.0 * M_PI * i / n), rr * std::sin(2.0 * M_PI * i / n), z, rho);
+      }
+    }
+    return;
+  }
+  if (type == GT_BOX) {
+    const double rho = ratio * std::min(size[0], std::min(size[1], size[2]));
+    for (double x : lattice(size[0], rho)) for (double y : lattice(size[1], rho)) for (double z : lattice(size[2], rho)) push(x, y, z, rho);
+    return;
+  }
+  throw std::runtime_error("SDF mode cannot sample this geom type with spheres");
+}
+
+ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const std::string& body, CompileInfo* info,
+                              const CompileOptions& opt) {
   using namespace ssppm;
   // --- which joints are planned ---------------------------------------------------------
   std::vector<int> planned(m.nbody, 0), qidx(m.nbody, -1);
@@ -460,7 +502,7 @@ ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const 
   }
   DevModel D;
   std::memset(&D, 0, sizeof(D));
-  D.rule = (mode == PLAN_JOINT) ? CR_COUNT : CR_CENTER;
+  D.rule = (mode == PLAN_JOINT) ? CR_COUNT : ((opt.use_center_dist && !opt.sdf) ? CR_CENTER : CR_DEPTH);
   // --- moving bodies = cluster roots, in id order (parents precede children) ---------------
   std::vector<int> mb_of(m.nbody, -1);
   for (int b = 1; b < m.nbody; ++b) {
@@ -563,6 +605,39 @@ ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const 
       D.mm[D.n_mmpair].margin = (float)std::max(m.geom_margin[g], m.geom_margin[h]);
       ++D.n_mmpair;
     }
+  if (opt.sdf) {
+    // The grid is the union of the static partners; it cannot express a per-geom collision mask, so every
+    // sampled moving geom must see exactly the same static geoms, and nothing may collide moving-vs-moving.
+    if (D.n_mmpair) throw std::runtime_error("SDF collision mode does not support pairs of geoms that move relative to each other");
+    std::vector<int> ref;
+    double margin = 0.0;
+    for (int ig = 0; ig < D.n_mgeom; ++ig) {
+      std::vector<int> mine;
+      for (int k = D.mg[ig].pair_begin; k < D.mg[ig].pair_end; ++k) { mine.push_back(D.pair[k].s); margin = std::max(margin, (double)D.pair[k].margin); }
+      std::sort(mine.begin(), mine.end());
+      if (ig == 0) ref = mine;
+      else if (mine != ref) throw std::runtime_error("SDF collision mode needs a uniform collision mask: geom '" + m.geom_name[mgeom_src[ig]] +
+                                                     "' collides with a different set of static geoms than '" + m.geom_name[mgeom_src[0]] + "'");
+    }
+    D.sdf_mode = 1;
+    for (int mb = 0; mb < D.n_mbody; ++mb) {
+      D.body[mb].sph_begin = D.n_sphere;
+      for (int ig = D.body[mb].geom_begin; ig < D.body[mb].geom_end; ++ig) {
+        const int g = mgeom_src[ig];
+        std::vector<double> sp;
+        sample_spheres(m.geom_type[g], &m.geom_size[3 * g], opt.sphere_ratio, &sp);
+        for (size_t k = 0; k + 3 < sp.size(); k += 4) {
+          if (D.n_sphere >= MAX_SPHERE) throw std::runtime_error("SDF collision mode: more than " + std::to_string((int)MAX_SPHERE) +
+                                                                 " sample spheres; raise sdf_sphere_ratio");
+          DevSphere& S = D.sph[D.n_sphere++];
+          const v3 c = add(ld3(D.mg[ig].pos), mulv(ldm(D.mg[ig].R), mk((float)sp[k], (float)sp[k + 1], (float)sp[k + 2])));
+          S.c[0] = c.x; S.c[1] = c.y; S.c[2] = c.z; S.r = (float)sp[k + 3]; S.margin = (float)margin; S.body = mb;
+        }
+      }
+      D.body[mb].sph_end = D.n_sphere;
+    }
+    D.n_pair = 0;        // the narrow phase is the grid
+  }
   // --- pairs that never move: evaluated once with the same FP32 narrow phase ------------------
   float static_cost = 0.0f;
   for (int g = 0; g < m.ngeom; ++g)

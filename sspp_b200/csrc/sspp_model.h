@@ -49,8 +49,16 @@ struct CompileInfo {
 // Specialise the flat model.  mode JOINT: dof planned coordinates; mode TASK: `body` is the free
 // body that is planned.  Throws std::runtime_error when limits of DevModel are exceeded or the
 // planned coordinates are not of a supported joint type.
+struct CompileOptions {
+  bool sdf = false;            // static scene will be a signed-distance grid: build sphere samples instead of pairs
+  double sphere_ratio = 0.5;   // sample-sphere radius / smallest half extent (boxes), see sample_spheres()
+  bool use_center_dist = true; // TASK contact cost: centre-distance rule or penetration depth
+};
 ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const std::string& body,
-                              CompileInfo* info = nullptr);
+                              CompileInfo* info = nullptr, const CompileOptions& opt = CompileOptions());
+
+// sphere samples (centre in the geom frame, radius) covering a primitive from the inside
+void sample_spheres(int type, const double* size, double ratio, std::vector<double>* out /* x,y,z,r per sphere */);
 
 // FP64 helpers shared by the loader and the host planner (not the oracle)
 void quat_to_mat(const double* q, double* R);   // (w,x,y,z) -> row-major 3x3, normalises

@@ -95,14 +95,67 @@ def task_case(scene="robocrane.xml", body=ICRA_BODY, n_samples=15, check_points=
     return Case(path, cfg, s, e, sigma0=0.3 if faithful_quirks else 0.2, body=body, model=capi.Model(path=str(path)))
 
 
+def clutter_scene(n_boxes=64, seed=SEED, keep_clear=()):
+    """cfg 3 scene: stacking.xml (floor + 3 boxes, block1 moving) plus n_boxes seeded static boxes,
+    half extents U(0.02,0.08), centres U([-0.6,0.6]^2 x [0.05,0.5]); boxes touching the shipped blocks or a
+    keep_clear point (start / goal, with the moving block's circumscribed radius) are rejected.  Returns MJCF text."""
+    rng = np.random.default_rng(seed)
+    base = (FIX / "stacking.xml").read_text()
+    blocks = [np.array([0.205, 0, 0.1]), np.array([0.0, 0, 0.1]), np.array([-0.205, 0, 0.1])]
+    geoms = []
+    while len(geoms) < n_boxes:
+        h = rng.uniform(0.02, 0.08, 3)
+        c = np.array([rng.uniform(-0.6, 0.6), rng.uniform(-0.6, 0.6), rng.uniform(0.05, 0.5)])
+        c[2] = max(c[2], h[2] + 0.002)                       # not sunk into the floor
+        if any(np.all(np.abs(c - b) < h + 0.1 + 0.01) for b in blocks):
+            continue
+        if any(np.linalg.norm(np.maximum(np.abs(c - np.asarray(p)[:3]) - h, 0)) < 0.1 * np.sqrt(3) + 0.02 for p in keep_clear):
+            continue
+        geoms.append(f'    <geom name="clutter{len(geoms)}" type="box" size="{h[0]:.6f} {h[1]:.6f} {h[2]:.6f}" '
+                     f'pos="{c[0]:.6f} {c[1]:.6f} {c[2]:.6f}" contype="1" conaffinity="1"/>')
+    return base.replace("  <worldbody>\n", "  <worldbody>\n" + "\n".join(geoms) + "\n", 1)
+
+
+CFG3_START = np.array([0.5, -0.5, 0.3, 0.0])
+CFG3_END = np.array([-0.5, 0.5, 0.3, 1.0])
+
+
+def sdf_case(n_samples=254, check_points=64, n_points=5, dims=(64, 64, 64), n_boxes=64, n_queries=1) -> Case:
+    """cfg 3 shape: Planner B on the cluttered stacking scene, SDF-grid collision, via points sampled"""
+    capi = _capi()
+    text = clutter_scene(n_boxes, keep_clear=(CFG3_START, CFG3_END))
+    path = ROOT / "fixtures" / f"_cfg3_clutter{n_boxes}.xml"
+    if not path.exists() or path.read_text() != text:
+        path.write_text(text)
+    case = task_case(f"_cfg3_clutter{n_boxes}.xml", "block1", n_samples=n_samples, check_points=check_points, n_points=n_points,
+                     n_queries=n_queries, start=CFG3_START, end=CFG3_END)
+    cfg = case.cfg
+    cfg.collision_mode = capi.COLLIDE_SDF
+    cfg.use_center_dist = 0
+    cfg.sdf_sphere_ratio = 0.5
+    lo, hi = [-0.8, -0.8, 0.0], [0.8, 0.8, 0.9]
+    for a in range(3):
+        cfg.sdf_dims[a], cfg.sdf_lo[a], cfg.sdf_hi[a] = dims[a], lo[a], hi[a]
+    for d, (l, h) in enumerate(zip([-0.7, -0.7, 0.1, -1.6], [0.7, 0.7, 0.78, 1.6])):   # paths may climb over the clutter
+        cfg.lo[d], cfg.hi[d] = l, h
+    return case
+
+
 def o2_for(case: Case):
     from oracle import pyoracle
     return pyoracle.O2(str(case.mjcf), case.cfg)
 
 
-def o1_for(case: Case):
+def o1_for(case: Case, spheres=None):
+    """FP64 oracle of the case; SDF-mode cases also need the product's sample spheres (an input, like the noise)"""
     from oracle import pyoracle
-    return pyoracle.O1(case.model, case.cfg.mode, case.cfg.dof, case.body)
+    o1 = pyoracle.O1(case.model, case.cfg.mode, case.cfg.dof, case.body)
+    if case.cfg.collision_mode == 1:
+        if spheres is None:
+            raise ValueError("SDF-mode oracle needs the sample spheres")
+        c = case.cfg
+        o1.set_sdf(list(c.sdf_dims), list(c.sdf_lo), list(c.sdf_hi), spheres, 0.0)
+    return o1
 
 
 def compare_iteration(h, case: Case, seed=SEED, iters=1, query=0, check_o1=True, eps_contact=1e-4):
@@ -142,7 +195,7 @@ def compare_iteration(h, case: Case, seed=SEED, iters=1, query=0, check_o1=True,
         rep["n_success"].append(int(r["n_success"][query]))
         if check_o1:
             from oracle import pyoracle
-            o1 = o1_for(case)
+            o1 = o1_for(case, h.spheres() if case.cfg.collision_mode == 1 else None)
             oc = pyoracle.o1_cfg_from(case.cfg)
             # O1 consumes the GPU's sampled rows; for JOINT mode base already holds control points
             s1 = o1.score(oc, base.astype(np.float64), gp.astype(np.float64).reshape(len(gp), -1))

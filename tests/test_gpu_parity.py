@@ -169,3 +169,33 @@ def test_population_shards_match_unsharded(kind, n_global):
     for s in shards:
         s.h.close()
     full.close()
+
+
+def test_sdf_mode_matches_oracles():
+    """cfg 3 back end: grid baked on the device == the replica's grid bit for bit; scored iterations bit-exact
+    against the replica and within tolerance of the FP64 statement."""
+    from tests.helpers import sdf_case
+    case = sdf_case(n_samples=510, check_points=64, n_points=5, dims=(64, 64, 48))
+    h = _handle(case)
+    o2 = o2_for(case)
+    nodes, lo, cell = h.sdf()
+    assert np.array_equal(nodes.view(np.uint32), o2.sdf_nodes().view(np.uint32))
+    assert np.array_equal(h.spheres(), o2.spheres())
+    rng = np.random.default_rng(4)
+    Q = np.column_stack([rng.uniform(-0.9, 0.9, 3000), rng.uniform(-0.9, 0.9, 3000), rng.uniform(-0.1, 1.0, 3000), rng.uniform(-1.6, 1.6, 3000)]).astype(np.float32)
+    g = h.eval_points(Q)                                   # includes points outside the grid (clamped reads)
+    r = np.array([o2.point_cost(q) for q in Q], np.float32)
+    assert np.array_equal(g.view(np.uint32), r.view(np.uint32))
+    rep = compare_iteration(h, case, iters=6, eps_contact=1e-4)
+    for k in ("status_mismatch", "elite_mismatch", "key_mismatch", "value_bits_mismatch", "param_bits_mismatch", "dist_bits_mismatch"):
+        assert rep[k] == 0, rep
+    assert rep["o1_max_rel"] <= REL, rep
+    assert max(rep["n_success"]) > 0
+    h.close()
+    bad = task_case()                                      # robocrane gripper: geoms with different collision masks
+    bad.cfg.collision_mode = 1
+    for a in range(3):
+        bad.cfg.sdf_dims[a], bad.cfg.sdf_lo[a], bad.cfg.sdf_hi[a] = 16, -1.0, 1.0
+    from sspp_b200 import capi
+    with pytest.raises(capi.SsppError, match="uniform collision mask"):
+        capi.Handle(bad.model, bad.cfg)

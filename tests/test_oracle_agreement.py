@@ -161,3 +161,46 @@ def test_scored_iteration_agrees(kind):
             np.testing.assert_allclose(r["mean"].ravel(), m1, rtol=1e-5, atol=1e-6)
             np.testing.assert_allclose(r["sigma"].ravel(), sg1, rtol=2e-5, atol=1e-7)
         mean, sigma, best, bv = r["mean"], r["sigma"], r["best"], r["best_valid"]
+
+
+def test_sdf_mode_oracles_agree():
+    """SDF-grid collision (cfg 3): the FP64 statement (own grid bake, own trilinear) against the FP32 replica"""
+    from tests.helpers import sdf_case
+    case = sdf_case(n_samples=62, check_points=32, dims=(40, 40, 28), n_boxes=64)
+    o2 = o2_for(case)
+    sp = o2.spheres()
+    assert len(sp) == 27 and np.allclose(sp[:, 3], 0.05)            # 0.1^3 cube, ratio 0.5 -> 3x3x3 lattice of r = 0.05
+    o1 = o1_for(case, sp)
+    n1, n2 = o1.sdf_nodes(), o2.sdf_nodes()
+    assert n1.shape == n2.shape == (28, 40, 40)
+    np.testing.assert_allclose(n2, n1, atol=5e-7)
+    assert (n1 < 0).any() and (n1 > 0.3).any()
+    # grid property: 1-Lipschitz along the axes (exact distances of a union of convex solids), up to rounding
+    cell = np.array([1.6 / 39, 1.6 / 39, 0.9 / 27])
+    for ax, h in zip((2, 1, 0), cell):
+        assert np.abs(np.diff(n1, axis=ax)).max() <= h + 1e-6
+    rng = np.random.default_rng(0)
+    Q = np.column_stack([rng.uniform(-0.7, 0.7, 2500), rng.uniform(-0.7, 0.7, 2500), rng.uniform(0.1, 0.75, 2500), rng.uniform(-1.6, 1.6, 2500)])
+    bad = hits = 0
+    for q in Q:
+        c1, ncon, md = o1.point_cost(q)
+        c2 = o2.point_cost(q)
+        hits += c1 != 0
+        if (c1 != 0) != (c2 != 0):
+            bad += abs(md + 1e-3) > EPS_CONTACT
+        elif c1 != 0:
+            assert abs(c1 - c2) <= 1e-5 + 1e-4 * abs(c1)
+    assert bad == 0 and 0.1 < hits / len(Q) < 0.9
+    # whole iterations: flags outside the band, values within tolerance
+    oc = pyoracle.o1_cfg_from(case.cfg)
+    psi_col, psi_arc, base, mean, sigma = _host_state(case)
+    best = np.zeros_like(mean); bv = 0
+    for it in range(3):
+        r = o2.iterate(psi_col, psi_arc, base, mean, sigma, best, bv, SEED, it)
+        s1 = o1.score(oc, base.astype(np.float64), r["params"].astype(np.float64).reshape(o2.n_cand, -1))
+        live = r["status"] != 2
+        diff = ((r["status"] == 0) != (s1["status"] == 0)) & live
+        assert not (diff & (np.abs(s1["min_dist"] + 1e-3) > EPS_CONTACT)).any()
+        ok = live & ~diff
+        np.testing.assert_allclose(r["L"][ok], s1["L"][ok], rtol=REL)
+        mean, sigma, best, bv = r["mean"], r["sigma"], r["best"], r["best_valid"]
