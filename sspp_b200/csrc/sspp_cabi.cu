@@ -302,6 +302,7 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
     int per_sm = 2;
     for (int round = 0; round < 3; ++round) {
       int ctas = std::max(1, std::min(s.n_cand, (per_sm * h->n_sm + c.n_queries - 1) / c.n_queries));
+      ctas = std::max(ctas, (s.n_cand + 31) / 32);     // large populations: tiles of <= 32 candidates, several rounds per CTA
       for (;;) {
         P.cand_per_cta = (s.n_cand + ctas - 1) / ctas;
         P.ctas_per_query = (s.n_cand + P.cand_per_cta - 1) / P.cand_per_cta;
