@@ -91,7 +91,8 @@ typedef struct SsppPlannerConfig {
   int32_t use_center_dist; /* TASK cost per contact: 1 = -1/(centre distance + 1e-4), 0 = -dist (Collision.h:84,93-98);
                               SDF mode always uses -dist (a grid has no geom centres) */
   int32_t sdf_dims[3];     /* grid nodes per axis (SDF mode), e.g. 128 128 128 */
-  int32_t reserved_;
+  int32_t tile_hint;       /* 0 = automatic.  Tuning knob: bits 0-7 kernel launch-bound variant + 1, bits 8-19 candidates
+                              per CTA, bits 20-31 threads per CTA (multiple of 32) */
   double sdf_lo[3], sdf_hi[3];   /* world box the grid spans */
   double sdf_sphere_ratio; /* sample-sphere radius / smallest half extent of a moving box (default 0.5) */
 } SsppPlannerConfig;
@@ -102,6 +103,7 @@ typedef struct SsppDims {
   int32_t rows_collision, rows_arc, first_free_row;
   int32_t threads, cand_per_cta, ctas_per_query; int64_t smem_bytes;
   int32_t n_mbody, n_mgeom, n_sgeom, n_pair, n_mmpair, chain;
+  int32_t variant, grid;   /* kernel launch-bound variant and CTAs per launch */
 } SsppDims;
 
 /* raw device pointers of the handle-owned result buffers (device-buffer path; valid until the

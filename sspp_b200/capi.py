@@ -63,7 +63,7 @@ class PlannerConfig(C.Structure):
                 ("eval_zmin", C.c_double), ("floor_margin", C.c_double), ("floor_scale", C.c_double),
                 ("limit_scale", C.c_double), ("sample_zmin", C.c_double), ("dist_zmin", C.c_double),
                 ("lo", C.c_double * MAX_DOF), ("hi", C.c_double * MAX_DOF),
-                ("collision_mode", C.c_int32), ("use_center_dist", C.c_int32), ("sdf_dims", C.c_int32 * 3), ("reserved_", C.c_int32),
+                ("collision_mode", C.c_int32), ("use_center_dist", C.c_int32), ("sdf_dims", C.c_int32 * 3), ("tile_hint", C.c_int32),
                 ("sdf_lo", C.c_double * 3), ("sdf_hi", C.c_double * 3), ("sdf_sphere_ratio", C.c_double)]
 
 
@@ -71,7 +71,7 @@ class Dims(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("n_queries", "n_cand", "n_free", "dof", "n_points", "nfd", "n_pad",
                                           "rows_collision", "rows_arc", "first_free_row", "threads", "cand_per_cta",
                                           "ctas_per_query")] + [("smem_bytes", C.c_int64)] + \
-               [(n, C.c_int32) for n in ("n_mbody", "n_mgeom", "n_sgeom", "n_pair", "n_mmpair", "chain")]
+               [(n, C.c_int32) for n in ("n_mbody", "n_mgeom", "n_sgeom", "n_pair", "n_mmpair", "chain", "variant", "grid")]
 
 
 class DeviceView(C.Structure):

@@ -28,9 +28,12 @@ struct ssppcu_model {
 struct ssppcu_planner {
   SsppPlannerConfig cfg;
   std::string body_name;
-  DevModel dev;
+  DevModel dev;            // host copy of the scene (tables + scalars)
+  ssppm::ModelView view;   // the same scalars with the tables in device global memory
+  size_t smem_model = 0;   // bytes of the tables staged at the front of the kernel's shared memory
   IterParams P;
   int threads = 256;
+  int variant = 0;   // index into kIterVariants
   size_t smem = 0;
   int n_sm = 148, grid = 1;
   cudaStream_t own_stream = nullptr, stream = nullptr;
@@ -286,11 +289,24 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
   cudaDeviceProp prop;
   if ((ce = cudaGetDeviceProperties(&prop, c.device)) != cudaSuccess) { set_err(err, errlen, std::string("cudaGetDeviceProperties: ") + cudaGetErrorString(ce)); delete h; return SSPPCU_ECUDA; }
   h->n_sm = prop.multiProcessorCount;
-  const size_t smem_cap = std::min<size_t>(prop.sharedMemPerBlockOptin, 200 * 1024);
+  h->smem_model = model_smem_bytes(h->dev);
+  P.model_bytes = (int)h->smem_model;
+  if (h->smem_model + 16 * 1024 > std::min<size_t>(prop.sharedMemPerBlockOptin, 200 * 1024)) { set_err(err, errlen, "scene tables exceed the shared memory of a CTA"); delete h; return SSPPCU_ELIMIT; }
+  const size_t smem_cap = std::min<size_t>(prop.sharedMemPerBlockOptin, 200 * 1024) - h->smem_model;   // h->smem excludes the tables
   // ---- tile shape ----
   // many small queries: one CTA per query, whole plans inside one launch (coop = 0);
   // otherwise a persistent cooperative grid over candidate tiles (coop = 1).
+  // cfg.tile_hint (0 = automatic) forces the kernel variant / tile: bits 0-7 variant + 1, 8-19 candidates per
+  // CTA, 20-31 threads per CTA.
+  const int hint_variant = (c.tile_hint & 0xFF) - 1, hint_cpc = (c.tile_hint >> 8) & 0xFFF, hint_threads = (c.tile_hint >> 20) & 0xFFF;
+  if (hint_variant >= kNumIterVariants || (hint_threads && (hint_threads % 32 || hint_threads > 1024))) {
+    set_err(err, errlen, "tile_hint: unknown kernel variant or thread count"); delete h; return SSPPCU_EINVAL;
+  }
+  h->variant = hint_variant >= 0 ? hint_variant : 0;
+  const bool auto_shape = hint_variant < 0 && !hint_threads;
   h->threads = ((long)s.n_cand * s.Mc <= 1024) ? 128 : 256;
+  if (hint_threads) h->threads = hint_threads;
+  if (h->threads > kIterVariants[h->variant].max_threads) { set_err(err, errlen, "tile_hint: threads exceed the variant's launch bound"); delete h; return SSPPCU_EINVAL; }
   P.coop = 0; P.cand_per_cta = s.n_cand; P.ctas_per_query = 1;
   h->smem = iterate_smem_bytes(h->dev, P, h->threads);
   const bool one_cta_ok = h->smem <= std::min<size_t>(smem_cap, 64 * 1024) && (long)s.n_cand * s.Mc <= 4096 && c.n_queries >= h->n_sm;
@@ -298,11 +314,13 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
     // one wave of tiles over the co-resident CTAs: guess the residency, shape the tiles, ask the
     // occupancy calculator, and reshape once if it answers differently
     P.coop = 1;
-    h->threads = 256;
-    int per_sm = 2;
+    if (auto_shape) { h->variant = 2; h->threads = 320; }   // 2 x 320 threads per SM at <= 96 registers: the measured optimum (profiles/)
+    else if (!hint_threads) h->threads = std::min(256, kIterVariants[h->variant].max_threads);
+    int per_sm = kIterVariants[h->variant].min_ctas;
     for (int round = 0; round < 3; ++round) {
       int ctas = std::max(1, std::min(s.n_cand, (per_sm * h->n_sm + c.n_queries - 1) / c.n_queries));
       ctas = std::max(ctas, (s.n_cand + 31) / 32);     // large populations: tiles of <= 32 candidates, several rounds per CTA
+      if (hint_cpc) ctas = (s.n_cand + hint_cpc - 1) / hint_cpc;
       for (;;) {
         P.cand_per_cta = (s.n_cand + ctas - 1) / ctas;
         P.ctas_per_query = (s.n_cand + P.cand_per_cta - 1) / P.cand_per_cta;
@@ -320,7 +338,7 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
       if (fixed + 256 * 8 > smem_cap) { set_err(err, errlen, "population too large for the ranking scratch"); delete h; return SSPPCU_ELIMIT; }
       h->smem = std::max(h->smem, std::min<size_t>(std::min<size_t>((size_t)s.n_cand, 2048) * 8 + fixed, smem_cap));
       int got = 0;
-      if ((ce = iterate_occupancy(h->threads, h->smem, &got)) != cudaSuccess || got < 1) {
+      if ((ce = iterate_occupancy(h->variant, h->threads, h->smem + h->smem_model, &got)) != cudaSuccess || got < 1) {
         set_err(err, errlen, std::string("occupancy query failed: ") + cudaGetErrorString(ce)); delete h; return SSPPCU_ECUDA;
       }
       h->grid = std::min(P.n_tiles, got * h->n_sm);
@@ -370,13 +388,33 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
   if (ce == cudaSuccess && !band_arc.empty()) ce = cudaMemcpy(d_psi_arc, band_arc.data(), band_arc.size() * sizeof(float), cudaMemcpyHostToDevice);
   if (ce == cudaSuccess && !band_arc.empty()) ce = cudaMemcpy(d_first_arc, first_arc.data(), first_arc.size() * sizeof(int), cudaMemcpyHostToDevice);
   if (ce != cudaSuccess) { set_err(err, errlen, std::string("cudaMemcpy: ") + cudaGetErrorString(ce)); ssppcu_destroy(h); return SSPPCU_ECUDA; }
+  // ---- scene tables in global memory (the kernels stage them into shared memory) ----
+  {
+    const DevModel& D = h->dev;
+    ssppm::DevBody* d_body = nullptr; ssppm::DevMGeom* d_mg = nullptr; ssppm::DevSGeom* d_sg = nullptr;
+    ssppm::DevPair* d_pair = nullptr; ssppm::DevMMPair* d_mm = nullptr; ssppm::DevSphere* d_sph = nullptr;
+    int rt = 0;
+    rt |= dalloc(h, &d_body, D.n_mbody); rt |= dalloc(h, &d_mg, D.n_mgeom); rt |= dalloc(h, &d_sg, D.n_sgeom);
+    rt |= dalloc(h, &d_pair, D.n_pair); rt |= dalloc(h, &d_mm, D.n_mmpair); rt |= dalloc(h, &d_sph, D.n_sphere);
+    if (rt) { set_err(err, errlen, h->err); ssppcu_destroy(h); return SSPPCU_ECUDA; }
+    ce = cudaMemcpy(d_body, D.body, D.n_mbody * sizeof(ssppm::DevBody), cudaMemcpyHostToDevice);
+    if (ce == cudaSuccess) ce = cudaMemcpy(d_mg, D.mg, D.n_mgeom * sizeof(ssppm::DevMGeom), cudaMemcpyHostToDevice);
+    if (ce == cudaSuccess) ce = cudaMemcpy(d_sg, D.sg, D.n_sgeom * sizeof(ssppm::DevSGeom), cudaMemcpyHostToDevice);
+    if (ce == cudaSuccess) ce = cudaMemcpy(d_pair, D.pair, D.n_pair * sizeof(ssppm::DevPair), cudaMemcpyHostToDevice);
+    if (ce == cudaSuccess) ce = cudaMemcpy(d_mm, D.mm, D.n_mmpair * sizeof(ssppm::DevMMPair), cudaMemcpyHostToDevice);
+    if (ce == cudaSuccess) ce = cudaMemcpy(d_sph, D.sph, D.n_sphere * sizeof(ssppm::DevSphere), cudaMemcpyHostToDevice);
+    if (ce != cudaSuccess) { set_err(err, errlen, std::string("cudaMemcpy (scene tables): ") + cudaGetErrorString(ce)); ssppcu_destroy(h); return SSPPCU_ECUDA; }
+    static_cast<ssppm::DevModelHead&>(h->view) = D;
+    h->view.body = d_body; h->view.mg = d_mg; h->view.sg = d_sg; h->view.pair = d_pair; h->view.mm = d_mm; h->view.sph = d_sph;
+  }
   if (h->dev.sdf_mode) {
     ssppm::SdfGrid& g = h->dev.grid;
     const size_t n_nodes = (size_t)g.nx * g.ny * g.nz, n_cells = (size_t)(g.nx - 1) * (g.ny - 1) * (g.nz - 1);
     float *d_nodes = nullptr, *d_cells = nullptr;
     if (dalloc(h, &d_nodes, n_nodes) || dalloc(h, &d_cells, n_cells * 8)) { set_err(err, errlen, h->err); ssppcu_destroy(h); return SSPPCU_ECUDA; }
     g.nodes = d_nodes; g.cells = d_cells;
-    ce = launch_sdf_bake(h->dev, d_nodes, d_cells, h->stream);
+    h->view.grid = g;
+    ce = launch_sdf_bake(h->view, d_nodes, d_cells, h->stream);
     if (ce == cudaSuccess) ce = cudaStreamSynchronize(h->stream);
     if (ce != cudaSuccess) { set_err(err, errlen, std::string("SDF bake: ") + cudaGetErrorString(ce)); ssppcu_destroy(h); return SSPPCU_ECUDA; }
   }
@@ -425,7 +463,8 @@ int ssppcu_dims(const ssppcu_t* h, SsppDims* o) {
   o->n_queries = h->P.n_query; o->n_cand = s.n_cand; o->n_free = s.n_free; o->dof = s.D; o->n_points = s.K;
   o->nfd = s.n_free * s.D; o->n_pad = h->P.n_pad; o->rows_collision = s.Mc; o->rows_arc = s.arc_same ? s.Mc : s.Ma;
   o->first_free_row = s.free_begin; o->threads = h->threads; o->cand_per_cta = h->P.cand_per_cta;
-  o->ctas_per_query = h->P.ctas_per_query; o->smem_bytes = (int64_t)h->smem;
+  o->ctas_per_query = h->P.ctas_per_query; o->smem_bytes = (int64_t)(h->smem + h->smem_model);
+  o->variant = h->variant; o->grid = h->grid;
   o->n_mbody = h->dev.n_mbody; o->n_mgeom = h->dev.n_mgeom; o->n_sgeom = h->dev.n_sgeom; o->n_pair = h->dev.n_pair;
   o->n_mmpair = h->dev.n_mmpair; o->chain = h->dev.chain;
   return SSPPCU_OK;
@@ -568,7 +607,7 @@ int ssppcu_iterate(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters) {
   if (n_iters < 1) return fail(h, SSPPCU_EINVAL, "n_iters must be positive");
   IterParams P = h->P;
   P.seed = seed; P.iter0 = iter0; P.n_inner = n_iters;
-  CU(h, launch_iterate(h->dev, P, h->threads, h->smem, h->grid, h->stream));
+  CU(h, launch_iterate(h->view, P, h->variant, h->threads, h->smem + h->smem_model, h->grid, h->stream));
   return SSPPCU_OK;
 }
 
@@ -656,7 +695,7 @@ int ssppcu_eval_points(ssppcu_t* h, const float* pts, int n, float* out) {
     h->eval_cap = n;
   }
   CU(h, cudaMemcpyAsync(h->d_eval_pts, pts, (size_t)n * D * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-  CU(h, launch_eval_points(h->dev, D, h->d_eval_pts, n, h->d_eval_out, h->stream));
+  CU(h, launch_eval_points(h->view, D, h->d_eval_pts, n, h->d_eval_out, h->stream));
   CU(h, cudaMemcpyAsync(out, h->d_eval_out, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
   CU(h, cudaStreamSynchronize(h->stream));
   return SSPPCU_OK;

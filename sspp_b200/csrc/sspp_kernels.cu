@@ -87,6 +87,44 @@ __device__ __forceinline__ Smem carve(unsigned char* raw, const ScoreConfig& c, 
   s.xf = sm;                              // link frames (only when !chain)
   return s;
 }
+// Scene tables staged at the front of dynamic shared memory (they stay there for the whole launch): every
+// record is a multiple of 16 bytes, copied as 128-bit words.  The staged view addresses them by 32-bit
+// offsets from the dynamic shared-memory base, so every access compiles to an LDS (warp-uniform index ->
+// one broadcast wavefront) instead of an indexed constant load through the ADU or a generic load.
+extern __shared__ __align__(16) unsigned char smem_all[];
+template <class T>
+struct SmemTab {
+  unsigned off;
+  __device__ __forceinline__ const T& operator[](int i) const { return *reinterpret_cast<const T*>(smem_all + off + (unsigned)i * (unsigned)sizeof(T)); }
+};
+struct SmemModel : ssppm::DevModelHead {
+  SmemTab<DevBody> body; SmemTab<DevMGeom> mg; SmemTab<DevSGeom> sg; SmemTab<DevPair> pair; SmemTab<DevMMPair> mm; SmemTab<DevSphere> sph;
+};
+__device__ __forceinline__ unsigned stage_table(const void* src, unsigned bytes, unsigned& at, int tid, int T) {
+  const uint4* s4 = reinterpret_cast<const uint4*>(src);
+  uint4* d4 = reinterpret_cast<uint4*>(smem_all + at);
+  for (int i = tid; i < (int)(bytes >> 4); i += T) d4[i] = __ldg(s4 + i);
+  const unsigned off = at;
+  at += bytes;
+  return off;
+}
+__device__ __forceinline__ SmemModel stage_model(const ModelView& G, int tid, int T) {
+  SmemModel S;
+  static_cast<ssppm::DevModelHead&>(S) = G;
+  unsigned at = 0;
+  S.body.off = stage_table(G.body, G.n_mbody * (unsigned)sizeof(DevBody), at, tid, T);
+  S.mg.off = S.sg.off = S.pair.off = S.mm.off = S.sph.off = 0;
+  if (G.sdf_mode) {
+    S.sph.off = stage_table(G.sph, G.n_sphere * (unsigned)sizeof(DevSphere), at, tid, T);
+  } else {
+    S.mg.off = stage_table(G.mg, G.n_mgeom * (unsigned)sizeof(DevMGeom), at, tid, T);
+    S.sg.off = stage_table(G.sg, G.n_sgeom * (unsigned)sizeof(DevSGeom), at, tid, T);
+    S.pair.off = stage_table(G.pair, G.n_pair * (unsigned)sizeof(DevPair), at, tid, T);
+    S.mm.off = stage_table(G.mm, G.n_mmpair * (unsigned)sizeof(DevMMPair), at, tid, T);
+  }
+  return S;
+}
+
 __device__ __forceinline__ void load_basis(const Smem& s, const ScoreConfig& c, const IterParams& P, int tid, int T) {
   const int wc = P.w_col | 1, wa = P.w_arc | 1;
   for (int e = tid; e < c.Mc * P.w_col; e += T) s.psi_col[(e / P.w_col) * wc + (e % P.w_col)] = P.psi_col[e];
@@ -99,7 +137,7 @@ __device__ __forceinline__ void load_basis(const Smem& s, const ScoreConfig& c, 
 
 // Phase A for one tile: candidates [c0, c0 + nc) of `query`.  Ends with the per-candidate outputs
 // and raw keys in global memory; no trailing barrier.
-__device__ __forceinline__ void score_tile(const DevModel& M, const IterParams& P, const Smem& s, int query, int c0, int nc,
+__device__ __forceinline__ void score_tile(const SmemModel& M, const IterParams& P, const Smem& s, int query, int c0, int nc,
                                            uint32_t iter) {
   const ScoreConfig& c = P.cfg;
   const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarp = T >> 5;
@@ -407,17 +445,17 @@ __device__ void update_phase(const IterParams& P) {
   }
 }
 
-#ifndef SSPP_MIN_CTAS
-#define SSPP_MIN_CTAS 2
-#endif
-template <bool COOP>
-__global__ void __launch_bounds__(256, SSPP_MIN_CTAS)
-sspp_iterate_kernel(const __grid_constant__ DevModel M, const __grid_constant__ IterParams P) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+// Launch-bound variants: (max threads, min CTAs per SM) fixes the register budget ptxas works with, and so
+// the resident warps per SM; the handle picks one per problem shape (kIterVariants, sspp_kernels.h).
+template <bool COOP, int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB)
+sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant__ IterParams P) {
   __shared__ int s_int[4];
   const ScoreConfig& c = P.cfg;
   const int tid = threadIdx.x, T = blockDim.x;
   const int nfd = c.n_free * c.D;
+  const SmemModel M = stage_model(MG, tid, T);      // visible after the first barrier below (load_basis / score_tile)
+  unsigned char* smem_raw = smem_all + P.model_bytes;
   const Smem s = carve(smem_raw, c, P, T);
   if (!COOP) {
     // one CTA per query: every iteration of the launch stays inside this CTA
@@ -539,7 +577,7 @@ sspp_merge_finish_kernel(const __grid_constant__ MergeParams P) {
 }
 
 __global__ void __launch_bounds__(128)
-sspp_eval_points_kernel(const __grid_constant__ DevModel M, int D, const float* __restrict__ pts, int n, float* __restrict__ out) {
+sspp_eval_points_kernel(const __grid_constant__ ModelView M, int D, const float* __restrict__ pts, int n, float* __restrict__ out) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float* s_qs = reinterpret_cast<float*>(smem_raw);
   float* s_xf = s_qs + D * blockDim.x;
@@ -554,7 +592,7 @@ sspp_eval_points_kernel(const __grid_constant__ DevModel M, int D, const float* 
 
 // node value = min over the static primitives of the exact point-primitive signed distance
 __global__ void __launch_bounds__(256)
-sspp_sdf_bake_kernel(const __grid_constant__ DevModel M, float* __restrict__ nodes) {
+sspp_sdf_bake_kernel(const __grid_constant__ ModelView M, float* __restrict__ nodes) {
   const SdfGrid& g = M.grid;
   const size_t n = (size_t)g.nx * g.ny * g.nz;
   for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
@@ -563,7 +601,7 @@ sspp_sdf_bake_kernel(const __grid_constant__ DevModel M, float* __restrict__ nod
   }
 }
 __global__ void __launch_bounds__(256)
-sspp_sdf_pack_kernel(const __grid_constant__ DevModel M, const float* __restrict__ nodes, float* __restrict__ cells) {
+sspp_sdf_pack_kernel(const __grid_constant__ ModelView M, const float* __restrict__ nodes, float* __restrict__ cells) {
   const SdfGrid& g = M.grid;
   const int cx = g.nx - 1, cy = g.ny - 1, cz = g.nz - 1;
   const size_t n = (size_t)cx * cy * cz;
@@ -595,7 +633,7 @@ sspp_fma_probe_kernel(float* sink, int iters) {
 
 }  // namespace
 
-cudaError_t launch_sdf_bake(const DevModel& M, float* nodes, float* cells, cudaStream_t stream) {
+cudaError_t launch_sdf_bake(const ModelView& M, float* nodes, float* cells, cudaStream_t stream) {
   sspp_sdf_bake_kernel<<<148 * 8, 256, 0, stream>>>(M, nodes);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
@@ -608,7 +646,14 @@ cudaError_t launch_fma_probe(float* sink, int blocks, int threads, int iters, cu
   return cudaGetLastError();
 }
 
-size_t iterate_smem_bytes(const DevModel& M, const IterParams& P, int threads) {
+size_t model_smem_bytes(const ssppm::DevModelHead& M) {
+  size_t b = (size_t)M.n_mbody * sizeof(DevBody);
+  if (M.sdf_mode) return b + (size_t)M.n_sphere * sizeof(DevSphere);
+  return b + (size_t)M.n_mgeom * sizeof(DevMGeom) + (size_t)M.n_sgeom * sizeof(DevSGeom) + (size_t)M.n_pair * sizeof(DevPair) +
+         (size_t)M.n_mmpair * sizeof(DevMMPair);
+}
+
+size_t iterate_smem_bytes(const ssppm::DevModelHead& M, const IterParams& P, int threads) {
   const ScoreConfig& c = P.cfg;
   const int wc = P.w_col | 1, wa = P.w_arc | 1;
   size_t f = (size_t)c.Mc * (wc + 1) + (c.arc_same ? 0 : (size_t)c.Ma * (wa + 1));
@@ -622,34 +667,43 @@ size_t iterate_smem_bytes(const DevModel& M, const IterParams& P, int threads) {
 }
 
 namespace {
-template <bool COOP>
-cudaError_t set_smem(size_t smem_bytes) {   // per device / context, so no caching across calls
+using IterKernel = void (*)(const ModelView, const IterParams);
+struct VariantFns { IterKernel coop, solo; };
+template <int MAXT, int MINB>
+constexpr VariantFns variant_fns() { return {sspp_iterate_kernel<true, MAXT, MINB>, sspp_iterate_kernel<false, MAXT, MINB>}; }
+// same order as kIterVariants
+const VariantFns kFns[kNumIterVariants] = {variant_fns<256, 2>(), variant_fns<256, 3>(), variant_fns<320, 2>(), variant_fns<320, 3>(),
+                                           variant_fns<448, 2>(), variant_fns<384, 2>(), variant_fns<128, 6>(), variant_fns<192, 5>()};
+cudaError_t set_smem(IterKernel k, size_t smem_bytes) {   // per device / context, so no caching across calls
   if (smem_bytes <= 48 * 1024) return cudaSuccess;
-  return cudaFuncSetAttribute(sspp_iterate_kernel<COOP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+  return cudaFuncSetAttribute(reinterpret_cast<const void*>(k), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
 }
 }  // namespace
 
-cudaError_t iterate_occupancy(int threads, size_t smem_bytes, int* ctas_per_sm) {
-  cudaError_t e = set_smem<true>(smem_bytes);
+cudaError_t iterate_occupancy(int variant, int threads, size_t smem_bytes, int* ctas_per_sm) {
+  if (variant < 0 || variant >= kNumIterVariants || threads > kIterVariants[variant].max_threads) return cudaErrorInvalidValue;
+  cudaError_t e = set_smem(kFns[variant].coop, smem_bytes);
   if (e != cudaSuccess) return e;
-  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, sspp_iterate_kernel<true>, threads, smem_bytes);
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, reinterpret_cast<const void*>(kFns[variant].coop), threads, smem_bytes);
 }
 
-cudaError_t launch_iterate(const DevModel& M, const IterParams& P, int threads, size_t smem_bytes, int grid, cudaStream_t stream) {
+cudaError_t launch_iterate(const ModelView& M, const IterParams& P, int variant, int threads, size_t smem_bytes, int grid,
+                           cudaStream_t stream) {
+  if (variant < 0 || variant >= kNumIterVariants || threads > kIterVariants[variant].max_threads) return cudaErrorInvalidValue;
   if (!P.coop) {
-    cudaError_t e = set_smem<false>(smem_bytes);
+    cudaError_t e = set_smem(kFns[variant].solo, smem_bytes);
     if (e != cudaSuccess) return e;
-    sspp_iterate_kernel<false><<<(unsigned)P.n_tiles, threads, smem_bytes, stream>>>(M, P);
+    kFns[variant].solo<<<(unsigned)P.n_tiles, threads, smem_bytes, stream>>>(M, P);
     return cudaGetLastError();
   }
-  cudaError_t e = set_smem<true>(smem_bytes);
+  cudaError_t e = set_smem(kFns[variant].coop, smem_bytes);
   if (e != cudaSuccess) return e;
-  void* args[] = {const_cast<DevModel*>(&M), const_cast<IterParams*>(&P)};
-  return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(sspp_iterate_kernel<true>), dim3((unsigned)grid), dim3((unsigned)threads),
+  void* args[] = {const_cast<ModelView*>(&M), const_cast<IterParams*>(&P)};
+  return cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(kFns[variant].coop), dim3((unsigned)grid), dim3((unsigned)threads),
                                      args, smem_bytes, stream);
 }
 
-cudaError_t launch_eval_points(const DevModel& M, int D, const float* pts, int n, float* out, cudaStream_t stream) {
+cudaError_t launch_eval_points(const ModelView& M, int D, const float* pts, int n, float* out, cudaStream_t stream) {
   const int T = 128;
   const size_t smem = (size_t)(D + (M.chain ? 0 : M.n_mbody * 12)) * T * sizeof(float);
   static size_t configured = 0;

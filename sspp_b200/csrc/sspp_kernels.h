@@ -21,6 +21,7 @@ struct IterParams {
   int rank_chunk;           // keys staged in shared memory per ranking pass (coop)
   int w_col, w_arc;         // band widths of the collocation matrices
   int mq;                   // pitch (rows) of the per-candidate point buffer: max(Mc, Ma)
+  int model_bytes;          // scene tables staged at the front of dynamic shared memory (model_smem_bytes)
   uint32_t iter0;           // iteration counter of the first inner iteration (Philox counter word)
   uint64_t seed;
   const float* psi_col;     // [Mc][w_col]  banded collocation matrix of the collision grid
@@ -43,14 +44,22 @@ struct IterParams {
   int* succ_acc;            // [Q] scratch: success count accumulated by the ranking phase
 };
 
-// shared-memory bytes of the scoring phase for the given tile shape
-size_t iterate_smem_bytes(const ssppm::DevModel& M, const IterParams& P, int threads);
+// shared-memory bytes of the staged scene tables, and of the scoring phase for the given tile shape (the
+// launch needs their sum)
+size_t model_smem_bytes(const ssppm::DevModelHead& M);
+size_t iterate_smem_bytes(const ssppm::DevModelHead& M, const IterParams& P, int threads);
+
+// Launch-bound variants of the iteration kernel: __launch_bounds__(max_threads, min_ctas) sets the register
+// budget (65536 / (max_threads * min_ctas), rounded down to 8) and with it the resident warps per SM.
+struct IterVariant { int max_threads, min_ctas; };
+constexpr int kNumIterVariants = 8;
+constexpr IterVariant kIterVariants[kNumIterVariants] = {{256, 2}, {256, 3}, {320, 2}, {320, 3}, {448, 2}, {384, 2}, {128, 6}, {192, 5}};
 
 // grid size: n_tiles CTAs (coop == 0) or `grid` co-resident CTAs looping over the tiles (coop == 1)
-cudaError_t launch_iterate(const ssppm::DevModel& M, const IterParams& P, int threads, size_t smem_bytes, int grid,
+cudaError_t launch_iterate(const ssppm::ModelView& M, const IterParams& P, int variant, int threads, size_t smem_bytes, int grid,
                            cudaStream_t stream);
 // co-resident CTAs per SM of the cooperative variant for this launch shape
-cudaError_t iterate_occupancy(int threads, size_t smem_bytes, int* ctas_per_sm);
+cudaError_t iterate_occupancy(int variant, int threads, size_t smem_bytes, int* ctas_per_sm);
 
 // Population-sharded path, after the all-gather of every shard's sorted keys: two small launches that
 // every rank runs identically.  (1) merge-rank: the global position of a key = its position in its own
@@ -73,11 +82,11 @@ struct MergeParams {
 cudaError_t launch_merge_update(const MergeParams& P, cudaStream_t stream);
 
 // collision cost of n explicit points pts[n][D] (unit check of kinematics + narrow phase)
-cudaError_t launch_eval_points(const ssppm::DevModel& M, int D, const float* pts, int n, float* out, cudaStream_t stream);
+cudaError_t launch_eval_points(const ssppm::ModelView& M, int D, const float* pts, int n, float* out, cudaStream_t stream);
 
 // SDF mode: bake the node grid from the handle's static primitives (M.sg[0..n_sgeom)) and pack the
 // 8 corners of every cell contiguously for the kernel's two 16-byte loads per sample
-cudaError_t launch_sdf_bake(const ssppm::DevModel& M, float* nodes, float* cells, cudaStream_t stream);
+cudaError_t launch_sdf_bake(const ssppm::ModelView& M, float* nodes, float* cells, cudaStream_t stream);
 
 // FP32 FMA peak probe: every thread runs `iters` rounds of 8 independent FMA chains
 cudaError_t launch_fma_probe(float* sink, int blocks, int threads, int iters, cudaStream_t stream);

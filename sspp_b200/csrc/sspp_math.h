@@ -29,7 +29,7 @@
 namespace ssppm {
 
 // ----------------------------------------------------------------------------------------
-// limits of the flattened model (kernel-parameter resident, < 32 KB)
+// limits of the flattened model
 // ----------------------------------------------------------------------------------------
 enum { MAX_MBODY = 16, MAX_MGEOM = 32, MAX_SGEOM = 112, MAX_PAIR = 1024, MAX_MMPAIR = 64,
        MAX_DOF = 9, MAX_K = 16, MAX_SPHERE = 256 };
@@ -40,40 +40,49 @@ enum ContactRule { CR_COUNT = 0,   // planner A: every contact with dist < margi
                    CR_CENTER = 1,  // planner B: dist < -1e-3 adds -1/(centre distance + 1e-4)   (Collision.h:93-96)
                    CR_DEPTH = 2 }; // planner B, use_center_dist = false: dist < -1e-3 adds -dist (Collision.h:97-98)
 
-struct DevBody {
+// Every record is a whole number of 16-byte words with its hot fields grouped four by four: the kernels stage
+// the tables into shared memory and read them with warp-uniform (broadcast) 128-bit loads.
+struct alignas(16) DevBody {
   float pos[3];     // frame origin in the parent frame (world frame when parent < 0)
+  float axis_sign;
   float R0[9];      // frame orientation in the parent frame, row-major
   float axis[3];    // joint axis in the body frame (unit)
   float anchor[3];  // joint anchor in the body frame
+  float fpad_;
   int parent;       // index into the moving-body list, -1: static parent folded into pos/R0
   int jtype;        // JointType
   int qidx;         // first planned coordinate this joint reads
+  int axis_kind;    // 0,1,2: the joint axis is +-e_x, +-e_y, +-e_z (axis_sign); 3: general axis
+  int has_anchor;
+  int r0_identity;  // R0 == I: the body frame is a pure translation of the parent frame
   int geom_begin, geom_end;  // moving geoms attached to this body
   int sph_begin, sph_end;    // SDF mode: sphere samples attached to this body
-  int has_anchor;
-  int axis_kind;    // 0,1,2: the joint axis is +-e_x, +-e_y, +-e_z (axis_sign); 3: general axis
-  float axis_sign;
-  int r0_identity;  // R0 == I: the body frame is a pure translation of the parent frame
+  int pad_[2];
 };
-struct DevMGeom {
+struct alignas(16) DevMGeom {
   float pos[3];     // in the body frame
+  float rbound;     // bounding-sphere radius about pos
   float R[9];
   float size[3];    // sphere r | capsule,cylinder r,half-length | box half extents
-  float rbound;     // bounding-sphere radius about pos
   int type;
-  int pair_begin, pair_end;   // range in DevModel::pair
+  int pair_begin, pair_end;   // range in the pair table
   int body;
 };
-struct DevSGeom {
+struct alignas(16) DevSGeom {
   float pos[3];     // world frame
+  float rbound;     // < 0: unbounded (plane)
   float R[9];
   float size[3];
-  float rbound;     // < 0: unbounded (plane)
   int type;
+  int pad_[3];
 };
-struct DevPair { int s; float margin; };
+// One filtered (moving geom, static geom) pair with its broad-phase test precomputed by compile_model:
+//   bounded partner: culled when |p - c[0..2]|^2 > c[3],  c = (S.pos, (G.rbound + S.rbound + thr)^2)
+//   plane partner:   culled when n . p > c[3],            c = (n, n . S.pos + G.rbound + thr)
+// with p the moving geom's centre and thr = max(margin, 0) + 1e-4 (conservative: margin + slack).
+struct alignas(16) DevPair { float c[4]; int s; float margin; float thr; int plane; };
 // SDF mode: a moving geom is sampled by spheres (centre in the frame of moving body `body`)
-struct DevSphere { float c[3]; float r; float margin; int body; };
+struct alignas(16) DevSphere { float c[3]; float r; float margin; int body; int pad_[2]; };
 // dense signed-distance grid of the static scene: node (i,j,k) sits at lo + (i,j,k) * h
 struct SdfGrid {
   int nx, ny, nz;
@@ -81,9 +90,10 @@ struct SdfGrid {
   const float* nodes;   // [nz][ny][nx] node values (host replica; device read-back)
   const float* cells;   // [(nz-1)][(ny-1)][(nx-1)][8] the 8 corners of every cell, contiguous (32 B = one sector)
 };
-struct DevMMPair { int a, b; float margin; };
+struct alignas(16) DevMMPair { int a, b; float margin; int pad_; };
 
-struct DevModel {
+// scalars of the flattened scene (kernel-parameter resident)
+struct DevModelHead {
   int n_mbody, n_mgeom, n_sgeom, n_pair, n_mmpair;
   int rule;          // ContactRule
   int chain;         // 1: parent[b] == b-1 for every b and no moving-moving pairs (no transform store)
@@ -91,12 +101,24 @@ struct DevModel {
   int sdf_mode;      // 1: static scene = SdfGrid, moving geoms = sphere samples (pairs unused)
   int n_sphere;
   SdfGrid grid;
+};
+// host container of the scene (what compile_model returns and the replica oracle reads)
+struct DevModel : DevModelHead {
   DevBody body[MAX_MBODY];
   DevMGeom mg[MAX_MGEOM];
   DevSGeom sg[MAX_SGEOM];
   DevPair pair[MAX_PAIR];
   DevMMPair mm[MAX_MMPAIR];
   DevSphere sph[MAX_SPHERE];   // grouped by body: body[b].sph_begin .. sph_end
+};
+// the same scene through pointers: device global memory (kernel parameter) or shared memory (staged copy)
+struct ModelView : DevModelHead {
+  const DevBody* body;
+  const DevMGeom* mg;
+  const DevSGeom* sg;
+  const DevPair* pair;
+  const DevMMPair* mm;
+  const DevSphere* sph;
 };
 
 // ----------------------------------------------------------------------------------------
@@ -142,6 +164,42 @@ SSPP_HD m3 ldm(const float* p) {
   return R;
 }
 SSPP_HD float clampf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
+
+// Four consecutive words of a 16-byte aligned table record in one access (the records above group their
+// fields for this); the host build reads the same four words one by one.
+struct alignas(16) f4 { float x, y, z, w; };
+struct alignas(16) i4 { int x, y, z, w; };
+SSPP_HD f4 ld4(const float* p) {
+#if defined(__CUDA_ARCH__)
+  return *reinterpret_cast<const f4*>(p);
+#else
+  f4 r; r.x = p[0]; r.y = p[1]; r.z = p[2]; r.w = p[3]; return r;
+#endif
+}
+SSPP_HD i4 ld4i(const int* p) {
+#if defined(__CUDA_ARCH__)
+  return *reinterpret_cast<const i4*>(p);
+#else
+  i4 r; r.x = p[0]; r.y = p[1]; r.z = p[2]; r.w = p[3]; return r;
+#endif
+}
+// R[9] + 3 trailing words (size / axis) of a record as three 4-word loads
+SSPP_HD float word_as_float(int w) {
+#if defined(__CUDA_ARCH__)
+  return __int_as_float(w);
+#else
+  union { int i; float f; } b; b.i = w; return b.f;
+#endif
+}
+struct m3t { m3 R; v3 t; };
+SSPP_HD m3t ld_rot12(const float* R) {
+  const f4 a = ld4(R), b = ld4(R + 4), c = ld4(R + 8);
+  m3t o;
+  o.R.a[0] = a.x; o.R.a[1] = a.y; o.R.a[2] = a.z; o.R.a[3] = a.w;
+  o.R.a[4] = b.x; o.R.a[5] = b.y; o.R.a[6] = b.z; o.R.a[7] = b.w;
+  o.R.a[8] = c.x; o.t.x = c.y; o.t.y = c.z; o.t.z = c.w;
+  return o;
+}
 
 // ----------------------------------------------------------------------------------------
 // Philox4x32-10 (Salmon et al., SC'11) — counter based, so samples are a pure function of
@@ -311,36 +369,45 @@ SSPP_HD void rot_axis(m3& R, float s, float c) {
 // parent frame (Rp,pp) -> this body's frame (R,p) given planned coordinates q
 template <class QA>
 SSPP_HD void fk_body(const DevBody& B, bool has_parent, const m3& Rp, v3 pp, QA& q, m3* R, v3* p) {
-  if (B.jtype == JT_FREE4) {  // (x,y,z,yaw) -> pose; quaternion (cos y/2,0,0,sin y/2) == Rz(yaw)
+  const i4 jt = ld4i(&B.parent);        // parent, jtype, qidx, axis_kind
+  const int jtype = jt.y, qidx = jt.z, axis_kind = jt.w;
+  if (jtype == JT_FREE4) {  // (x,y,z,yaw) -> pose; quaternion (cos y/2,0,0,sin y/2) == Rz(yaw)
     float s, c;
-    sincos_poly(q.get(B.qidx + 3), &s, &c);
+    sincos_poly(q.get(qidx + 3), &s, &c);
     R->a[0] = c; R->a[1] = -s; R->a[2] = 0.0f;
     R->a[3] = s; R->a[4] = c;  R->a[5] = 0.0f;
     R->a[6] = 0.0f; R->a[7] = 0.0f; R->a[8] = 1.0f;
-    *p = mk(q.get(B.qidx), q.get(B.qidx + 1), q.get(B.qidx + 2));
+    *p = mk(q.get(qidx), q.get(qidx + 1), q.get(qidx + 2));
     return;
   }
+  const f4 ps = ld4(B.pos);             // pos, axis_sign
+  const int has_anchor = B.has_anchor, r0_identity = B.r0_identity;
   m3 Rw; v3 pw;
-  if (has_parent) { Rw = B.r0_identity ? Rp : mulm(Rp, B.R0); pw = add(pp, mulv(Rp, ld3(B.pos))); }
-  else { Rw = ldm(B.R0); pw = ld3(B.pos); }
-  if (B.jtype == JT_HINGE) {
+  v3 axis = mk(0.f, 0.f, 0.f);
+  if (has_parent) {
+    if (r0_identity && axis_kind < 3) Rw = Rp;
+    else { const m3t ra = ld_rot12(B.R0); axis = ra.t; Rw = r0_identity ? Rp : mulm(Rp, ra.R.a); }
+    pw = add(pp, mulv(Rp, mk(ps.x, ps.y, ps.z)));
+  } else { const m3t ra = ld_rot12(B.R0); axis = ra.t; Rw = ra.R; pw = mk(ps.x, ps.y, ps.z); }
+  if (jtype == JT_HINGE) {
     m3 Rn;
-    if (B.axis_kind < 3) {
+    if (axis_kind < 3) {
       // rotation about a coordinate axis of the body frame: only the two other columns mix
       float s, c;
-      sincos_poly(q.get(B.qidx), &s, &c);
-      s *= B.axis_sign;
+      sincos_poly(q.get(qidx), &s, &c);
+      s *= ps.w;
       Rn = Rw;
-      if (B.axis_kind == 0) rot_axis<0>(Rn, s, c); else if (B.axis_kind == 1) rot_axis<1>(Rn, s, c); else rot_axis<2>(Rn, s, c);
+      if (axis_kind == 0) rot_axis<0>(Rn, s, c); else if (axis_kind == 1) rot_axis<1>(Rn, s, c); else rot_axis<2>(Rn, s, c);
     } else {
       float Rj[9];
-      rodrigues(ld3(B.axis), q.get(B.qidx), Rj);
+      rodrigues(axis, q.get(qidx), Rj);
       Rn = mulm(Rw, Rj);
     }
-    if (B.has_anchor) { const v3 an = ld3(B.anchor); pw = add(pw, sub(mulv(Rw, an), mulv(Rn, an))); }
+    if (has_anchor) { const f4 an4 = ld4(B.anchor); const v3 an = mk(an4.x, an4.y, an4.z); pw = add(pw, sub(mulv(Rw, an), mulv(Rn, an))); }
     Rw = Rn;
-  } else if (B.jtype == JT_SLIDE) {
-    pw = madd(mulv(Rw, ld3(B.axis)), q.get(B.qidx), pw);
+  } else if (jtype == JT_SLIDE) {
+    if (r0_identity && axis_kind < 3 && has_parent) axis = ld3(B.axis);
+    pw = madd(mulv(Rw, axis), q.get(qidx), pw);
   }
   *R = Rw; *p = pw;
 }
@@ -707,14 +774,18 @@ SSPP_HD Prim place(const DevMGeom& g, const m3& R, v3 p) {
 // orientation part of a placement, as little as the type needs: capsules and cylinders only use their
 // axis (column 2), spheres nothing; element formulas are those of mulm
 SSPP_HD void place_rotation(const DevMGeom& g, const m3& R, Prim* P) {
-  if (g.type == GT_BOX) { P->R = mulm(R, g.R); return; }
+  if (g.type == GT_BOX) { const m3t rs = ld_rot12(g.R); P->R = mulm(R, rs.R.a); return; }
   if (g.type == GT_SPHERE) return;
 #pragma unroll
   for (int i = 0; i < 3; ++i)
     P->R.a[3 * i + 2] = fmaf(R.a[3 * i + 2], g.R[8], fmaf(R.a[3 * i + 1], g.R[5], R.a[3 * i] * g.R[2]));
 }
 SSPP_HD Prim static_prim(const DevSGeom& g) {
-  Prim P; P.p = ld3(g.pos); P.R = ldm(g.R); P.s = ld3(g.size); P.type = g.type; return P;
+  Prim P;
+  const f4 a = ld4(g.pos);
+  const m3t rs = ld_rot12(g.R);
+  P.p = mk(a.x, a.y, a.z); P.R = rs.R; P.s = rs.t; P.type = g.type;
+  return P;
 }
 
 // Collision cost of one configuration q: FK of every moving body, placement of its geoms,
@@ -722,8 +793,8 @@ SSPP_HD Prim static_prim(const DevSGeom& g) {
 // put(body, k, value) / get(body, k), k in 0..11 (R row-major then p) — shared memory on the
 // GPU, a plain array in the replica; unused when model.chain is set.
 // QA exposes the planned coordinates as q.get(i).
-template <class XF, class QA>
-SSPP_HD float point_collision_cost(const DevModel& M, QA& q, XF& xf) {
+template <class MT, class XF, class QA>
+SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf) {
   float cost = M.static_cost;
   m3 R; v3 p = mk(0.f, 0.f, 0.f);
 #pragma unroll
@@ -759,25 +830,23 @@ SSPP_HD float point_collision_cost(const DevModel& M, QA& q, XF& xf) {
 #pragma unroll 1
     for (int g = B.geom_begin; g < B.geom_end; ++g) {
       const DevMGeom& G = M.mg[g];
+      const f4 gp = ld4(G.pos);                              // pos, rbound
+      const i4 gi = ld4i(&G.type);                           // type, pair_begin, pair_end, body
       Prim P;
-      P.p = add(p, mulv(R, ld3(G.pos)));
-      P.s = ld3(G.size);
-      P.type = G.type;
+      P.p = add(p, mulv(R, mk(gp.x, gp.y, gp.z)));
+      P.type = gi.x;
       bool rotated = false;
 #pragma unroll 1
-      for (int k = G.pair_begin; k < G.pair_end; ++k) {
-        const DevSGeom& S = M.sg[M.pair[k].s];
-        const float margin = M.pair[k].margin;
-        const float thr = fmaxf(margin, 0.0f) + 1e-4f;      // conservative: margin + slack
-        if (S.rbound >= 0.0f) {                             // bounding-sphere cull
-          const v3 w = sub(P.p, ld3(S.pos));
-          const float rr = G.rbound + S.rbound + thr;
-          if (dot(w, w) > rr * rr) continue;
-        } else {                                            // plane: bounding sphere against the half space
-          const v3 n = mk(S.R[2], S.R[5], S.R[8]);
-          if (dot(n, sub(P.p, ld3(S.pos))) - G.rbound > thr) continue;
-        }
-        if (!rotated) { place_rotation(G, R, &P); rotated = true; }
+      for (int k = gi.y; k < gi.z; ++k) {
+        const DevPair& pr = M.pair[k];
+        const f4 c4 = ld4(pr.c);
+        const i4 t4 = ld4i(&pr.s);                           // s, margin, thr, plane (floats as raw words)
+        const v3 pc = mk(c4.x, c4.y, c4.z);
+        if (t4.w) { if (dot(pc, P.p) > c4.w) continue; }     // bounding sphere beyond the half space
+        else { const v3 w = sub(P.p, pc); if (dot(w, w) > c4.w) continue; }   // bounding spheres apart
+        const DevSGeom& S = M.sg[t4.x];
+        const float margin = word_as_float(t4.y), thr = word_as_float(t4.z);
+        if (!rotated) { P.s = ld3(G.size); place_rotation(G, R, &P); rotated = true; }
         const Prim Q = static_prim(S);
         const float d = moving_static_sd(P, Q, thr);
         cost += contact_cost(M.rule, d, margin, P.p, Q.p);
@@ -805,7 +874,8 @@ SSPP_HD float point_collision_cost(const DevModel& M, QA& q, XF& xf) {
 }
 
 // value of grid node (i,j,k): min over the static primitives (shared by the bake kernel and the replica)
-SSPP_HD float sdf_node_value(const DevModel& M, int i, int j, int k) {
+template <class MT>
+SSPP_HD float sdf_node_value(const MT& M, int i, int j, int k) {
   const SdfGrid& g = M.grid;
   const v3 x = mk(fmaf((float)i, g.h[0], g.lo[0]), fmaf((float)j, g.h[1], g.lo[1]), fmaf((float)k, g.h[2], g.lo[2]));
   float best = 3.0e38f;

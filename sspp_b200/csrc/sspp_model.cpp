@@ -593,6 +593,20 @@ ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const 
     }
     D.mg[ig].pair_end = D.n_pair;
   }
+  // broad-phase test of every pair, precomputed in FP32 (see DevPair)
+  for (int ig = 0; ig < D.n_mgeom; ++ig)
+    for (int k = D.mg[ig].pair_begin; k < D.mg[ig].pair_end; ++k) {
+      DevPair& pr = D.pair[k];
+      const DevSGeom& S = D.sg[pr.s];
+      pr.thr = std::max(pr.margin, 0.0f) + 1e-4f;
+      if (S.rbound >= 0.0f) {
+        const float rr = D.mg[ig].rbound + S.rbound + pr.thr;
+        pr.plane = 0; pr.c[0] = S.pos[0]; pr.c[1] = S.pos[1]; pr.c[2] = S.pos[2]; pr.c[3] = rr * rr;
+      } else {
+        const v3 n = mk(S.R[2], S.R[5], S.R[8]);
+        pr.plane = 1; pr.c[0] = n.x; pr.c[1] = n.y; pr.c[2] = n.z; pr.c[3] = dot(n, ld3(S.pos)) + D.mg[ig].rbound + pr.thr;
+      }
+    }
   for (int ig = 0; ig < D.n_mgeom; ++ig)
     for (int ih = ig + 1; ih < D.n_mgeom; ++ih) {
       const int g = mgeom_src[ig], h = mgeom_src[ih];
