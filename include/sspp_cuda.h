@@ -159,6 +159,11 @@ int ssppcu_restore_state(ssppcu_t* h);
 /* n_iters fused iterations, asynchronous on the handle's stream; Philox counters (seed, iter0+i) */
 int ssppcu_iterate(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters);
 int ssppcu_sync(ssppcu_t* h);
+/* Diagnostics of the cooperative kernel: with enable != 0 every CTA stamps %globaltimer (ns) at the phase
+ * boundaries of each launch's first iteration: start, scored, past grid barrier 1, ranked, past grid barrier 2,
+ * updated.  stamps (may be NULL) receives [min(cap_ctas, grid)][6] values of the last launch.  Returns the grid
+ * size or a negative error. */
+int ssppcu_phase_probe(ssppcu_t* h, int enable, unsigned long long* stamps, int cap_ctas);
 
 /* host copies of the last iteration; any pointer may be NULL.  Per-candidate arrays are
  * [n_queries][n_cand], per-query arrays [n_queries].  Synchronises the stream. */

@@ -51,6 +51,20 @@ float strided_sum(const float* v, int n) {
   for (int l = 0; l < 32; ++l) { float acc = 0.0f; for (int i = l; i < n; i += 32) acc += v[i]; part[l] = acc; }
   return butterfly(part);
 }
+// the kernel's wide sums (elite reductions): 8 groups of 32 virtual lanes, virtual lane v sums its terms
+// j = v, v + 256, ... in ascending order (term(j, acc) -> acc'), butterfly per group, group sums added in
+// ascending group order, empty groups skipped
+template <class Term>
+float wide_sum(int k, Term term) {
+  float tot = 0.0f;
+  for (int g = 0; g < 8 && (g == 0 || 32 * g < k); ++g) {
+    float part[32];
+    for (int l = 0; l < 32; ++l) { float acc = 0.0f; for (int j = 32 * g + l; j < k; j += 256) acc = term(j, acc); part[l] = acc; }
+    const float sg = butterfly(part);
+    tot = (g == 0) ? sg : tot + sg;
+  }
+  return tot;
+}
 
 }  // namespace
 
@@ -216,7 +230,7 @@ int o2_iterate(void* h, const float* psi_col, const float* psi_arc, const float*
   *best_idx = (int)(uint32_t)(keys[0] & 0xFFFFFFFFu);
   const float lk = log_poly((float)k + 0.5f);
   for (int j = 0; j < k; ++j) weights[j] = lk - log_poly((float)j + 1.0f);
-  const float sumw = strided_sum(weights, k);
+  const float sumw = wide_sum(k, [&](int j, float acc) { return acc + weights[j]; });
   for (int j = 0; j < k; ++j) weights[j] = weights[j] / sumw;
   auto P = [&](int j, int t) { return params[(size_t)((uint32_t)(keys[j] & 0xFFFFFFFFu) - cand_offset) * nfd + t]; };
   std::vector<float> bestn(nfd);
@@ -224,24 +238,17 @@ int o2_iterate(void* h, const float* psi_col, const float* psi_arc, const float*
   if (c.do_update) {
     for (int t = 0; t < nfd; ++t) {
       const int d = t % D;
-      float part[32];
-      for (int l = 0; l < 32; ++l) { float acc = 0.0f; for (int j = l; j < k; j += 32) acc = fmaf(weights[j], P(j, t), acc); part[l] = acc; }
-      const float em = butterfly(part);
+      const float em = wide_sum(k, [&](int j, float acc) { return fmaf(weights[j], P(j, t), acc); });
       const float m0 = mean[t];
       float nm = fmaf(c.mean_lr, em - m0, m0);
       if (c.mode == MODE_TASK && d == 2) nm = fmaxf(nm, c.dist_zmin);
       nm = fminf(fmaxf(nm, c.lo[d]), c.hi[d]);
       const bool wrap = (c.mode == MODE_TASK && d == 3 && c.lo[3] != c.hi[3]);
-      for (int l = 0; l < 32; ++l) {
-        float acc = 0.0f;
-        for (int j = l; j < k; j += 32) {
-          const float v = P(j, t);
-          const float df = wrap ? wrap_angle_diff(v, nm, c.lo[3], c.hi[3]) : v - nm;
-          acc = fmaf(weights[j], df * df, acc);
-        }
-        part[l] = acc;
-      }
-      const float var = butterfly(part);
+      const float var = wide_sum(k, [&](int j, float acc) {
+        const float v = P(j, t);
+        const float df = wrap ? wrap_angle_diff(v, nm, c.lo[3], c.hi[3]) : v - nm;
+        return fmaf(weights[j], df * df, acc);
+      });
       const float s0 = sigma[t];
       const float blend = fmaf(c.var_beta, var, (1.0f - c.var_beta) * (s0 * s0));
       float sg = clamp_sigma(c, sqrtf(blend));
@@ -282,31 +289,24 @@ int o2_merge_update(void* h, unsigned long long* keys, int n_keys, uint64_t seed
   *best_idx = (int)(uint32_t)(keys[0] & 0xFFFFFFFFu);
   const float lk = log_poly((float)k + 0.5f);
   for (int j = 0; j < k; ++j) weights[j] = lk - log_poly((float)j + 1.0f);
-  const float sumw = strided_sum(weights, k);
+  const float sumw = wide_sum(k, [&](int j, float acc) { return acc + weights[j]; });
   for (int j = 0; j < k; ++j) weights[j] = weights[j] / sumw;
   for (int t = 0; t < nfd; ++t) best[t] = P(0, t);
   *best_valid = 1;
   if (c.do_update) {
     for (int t = 0; t < nfd; ++t) {
       const int d = t % D;
-      float part[32];
-      for (int l = 0; l < 32; ++l) { float acc = 0.0f; for (int j = l; j < k; j += 32) acc = fmaf(weights[j], P(j, t), acc); part[l] = acc; }
-      const float em = butterfly(part);
+      const float em = wide_sum(k, [&](int j, float acc) { return fmaf(weights[j], P(j, t), acc); });
       const float m0 = mean[t];
       float nm = fmaf(c.mean_lr, em - m0, m0);
       if (c.mode == MODE_TASK && d == 2) nm = fmaxf(nm, c.dist_zmin);
       nm = fminf(fmaxf(nm, c.lo[d]), c.hi[d]);
       const bool wrap = (c.mode == MODE_TASK && d == 3 && c.lo[3] != c.hi[3]);
-      for (int l = 0; l < 32; ++l) {
-        float acc = 0.0f;
-        for (int j = l; j < k; j += 32) {
-          const float v = P(j, t);
-          const float df = wrap ? wrap_angle_diff(v, nm, c.lo[3], c.hi[3]) : v - nm;
-          acc = fmaf(weights[j], df * df, acc);
-        }
-        part[l] = acc;
-      }
-      const float var = butterfly(part);
+      const float var = wide_sum(k, [&](int j, float acc) {
+        const float v = P(j, t);
+        const float df = wrap ? wrap_angle_diff(v, nm, c.lo[3], c.hi[3]) : v - nm;
+        return fmaf(weights[j], df * df, acc);
+      });
       const float s0 = sigma[t];
       const float blend = fmaf(c.var_beta, var, (1.0f - c.var_beta) * (s0 * s0));
       float sg = clamp_sigma(c, sqrtf(blend));

@@ -90,7 +90,7 @@ SYMBOLS = [
     "ssppcu_get_params", "ssppcu_get_best", "ssppcu_get_elites", "ssppcu_device_view", "ssppcu_eval_points",
     "ssppcu_get_collocation", "ssppcu_get_base", "ssppcu_shard_keys", "ssppcu_merge_update", "ssppcu_version",
     "ssppcu_spline_setup", "ssppcu_collocation_matrix", "ssppcu_save_state", "ssppcu_restore_state",
-    "ssppcu_fp32_peak", "ssppcu_get_merged", "ssppcu_get_sdf", "ssppcu_get_spheres",
+    "ssppcu_fp32_peak", "ssppcu_get_merged", "ssppcu_get_sdf", "ssppcu_get_spheres", "ssppcu_phase_probe",
 ]
 
 lib = _load()
@@ -337,6 +337,19 @@ class Handle:
 
     def sync(self):
         self._ck(lib.ssppcu_sync(self._h))
+
+    def phase_probe(self, enable: bool = True, read: bool = False):
+        """diagnostics of the cooperative kernel: per-CTA %globaltimer stamps [grid][6] of the last launch's first
+        iteration (start, scored, past barrier 1, ranked, past barrier 2, updated); None unless `read`"""
+        lib.ssppcu_phase_probe.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        grid = lib.ssppcu_phase_probe(self._h, int(enable), None, 0)
+        if grid < 0:
+            self._ck(grid)
+        if not read:
+            return None
+        out = np.zeros((grid, 6), np.uint64)
+        self._ck(min(0, lib.ssppcu_phase_probe(self._h, int(enable), out.ctypes.data_as(C.c_void_p), grid)))
+        return out
 
     def save_state(self):
         self._ck(lib.ssppcu_save_state(self._h))

@@ -46,6 +46,7 @@ struct ssppcu_planner {
   float* d_live = nullptr;       // mean | sigma | best | best_valid | any_success (ints), one block
   float* d_state = nullptr;      // snapshot of d_live
   size_t state_words = 0; bool state_saved = false;
+  unsigned long long* d_probe = nullptr;   // phase probe stamps [grid][6], allocated on demand
 };
 
 namespace {
@@ -183,6 +184,7 @@ void ssppcu_destroy(ssppcu_t* h) {
   if (h->d_eval_pts) cudaFree(h->d_eval_pts);
   if (h->d_eval_out) cudaFree(h->d_eval_out);
   if (h->d_merge_keys) cudaFree(h->d_merge_keys);
+  if (h->d_probe) cudaFree(h->d_probe);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
 }
@@ -336,7 +338,7 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
       const long long per = (total + grid_guess - 1) / grid_guess;
       const size_t fixed = (size_t)per * 12 + 64;
       if (fixed + 256 * 8 > smem_cap) { set_err(err, errlen, "population too large for the ranking scratch"); delete h; return SSPPCU_ELIMIT; }
-      h->smem = std::max(h->smem, std::min<size_t>(std::min<size_t>((size_t)s.n_cand, 2048) * 8 + fixed, smem_cap));
+      h->smem = std::max(h->smem, std::min<size_t>(std::min<size_t>((size_t)s.n_cand + 1, 8192) * 8 + fixed, smem_cap));
       int got = 0;
       if ((ce = iterate_occupancy(h->variant, h->threads, h->smem + h->smem_model, &got)) != cudaSuccess || got < 1) {
         set_err(err, errlen, std::string("occupancy query failed: ") + cudaGetErrorString(ce)); delete h; return SSPPCU_ECUDA;
@@ -345,7 +347,7 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
       const long long per2 = (total + h->grid - 1) / h->grid;
       const size_t fixed2 = (size_t)per2 * 12 + 64;
       if (fixed2 + 256 * 8 > h->smem) { per_sm = std::max(1, got - 1); continue; }
-      P.rank_chunk = (int)std::min<size_t>((size_t)s.n_cand, (h->smem - fixed2) / 8);
+      P.rank_chunk = (int)std::min<size_t>((size_t)s.n_cand + 1, (h->smem - fixed2) / 8) & ~1;   // even: 16-byte chunk rows
       if (got == per_sm || round == 2) break;
       per_sm = got;
     }
@@ -609,6 +611,21 @@ int ssppcu_iterate(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters) {
   P.seed = seed; P.iter0 = iter0; P.n_inner = n_iters;
   CU(h, launch_iterate(h->view, P, h->variant, h->threads, h->smem + h->smem_model, h->grid, h->stream));
   return SSPPCU_OK;
+}
+
+int ssppcu_phase_probe(ssppcu_t* h, int enable, unsigned long long* stamps, int cap_ctas) {
+  if (int rc = check(h)) return rc;
+  if (!h->P.coop) return fail(h, SSPPCU_EINVAL, "the phase probe exists in the cooperative kernel only");
+  if (enable && !h->d_probe) {
+    CU(h, cudaMalloc(&h->d_probe, (size_t)h->grid * 6 * sizeof(unsigned long long)));
+    CU(h, cudaMemset(h->d_probe, 0, (size_t)h->grid * 6 * sizeof(unsigned long long)));
+  }
+  if (stamps && h->d_probe) {
+    CU(h, cudaStreamSynchronize(h->stream));
+    CU(h, cudaMemcpy(stamps, h->d_probe, (size_t)std::min(cap_ctas, h->grid) * 6 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  }
+  h->P.probe = enable ? h->d_probe : nullptr;
+  return h->grid;
 }
 
 int ssppcu_sync(ssppcu_t* h) {

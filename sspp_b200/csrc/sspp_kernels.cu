@@ -91,36 +91,46 @@ __device__ __forceinline__ Smem carve(unsigned char* raw, const ScoreConfig& c, 
 // record is a multiple of 16 bytes, copied as 128-bit words.  The staged view addresses them by 32-bit
 // offsets from the dynamic shared-memory base, so every access compiles to an LDS (warp-uniform index ->
 // one broadcast wavefront) instead of an indexed constant load through the ADU or a generic load.
-extern __shared__ __align__(16) unsigned char smem_all[];
+extern __shared__ uint4 smem_all4[];                    // the dynamic shared memory as 16-byte words
+#define smem_all (reinterpret_cast<unsigned char*>(smem_all4))
 template <class T>
-struct SmemTab {
-  unsigned off;
-  __device__ __forceinline__ const T& operator[](int i) const { return *reinterpret_cast<const T*>(smem_all + off + (unsigned)i * (unsigned)sizeof(T)); }
-};
+struct SmemTab { unsigned w16; };                       // first 16-byte word of the table
 struct SmemModel : ssppm::DevModelHead {
   SmemTab<DevBody> body; SmemTab<DevMGeom> mg; SmemTab<DevSGeom> sg; SmemTab<DevPair> pair; SmemTab<DevMMPair> mm; SmemTab<DevSphere> sph;
 };
-__device__ __forceinline__ unsigned stage_table(const void* src, unsigned bytes, unsigned& at, int tid, int T) {
+// overloads of the record accessors of sspp_math.h: one LDS.128 off the typed shared array
+template <class T>
+__device__ __forceinline__ ssppm::f4 rec_f4(const SmemTab<T>& t, int i, int w) {
+  const uint4 v = smem_all4[t.w16 + (unsigned)i * (unsigned)(sizeof(T) / 16) + (unsigned)(w >> 2)];
+  ssppm::f4 r; r.x = __uint_as_float(v.x); r.y = __uint_as_float(v.y); r.z = __uint_as_float(v.z); r.w = __uint_as_float(v.w);
+  return r;
+}
+template <class T>
+__device__ __forceinline__ ssppm::i4 rec_i4(const SmemTab<T>& t, int i, int w) {
+  const uint4 v = smem_all4[t.w16 + (unsigned)i * (unsigned)(sizeof(T) / 16) + (unsigned)(w >> 2)];
+  ssppm::i4 r; r.x = (int)v.x; r.y = (int)v.y; r.z = (int)v.z; r.w = (int)v.w;
+  return r;
+}
+__device__ __forceinline__ unsigned stage_table(const void* src, unsigned bytes, unsigned& at16, int tid, int T) {
   const uint4* s4 = reinterpret_cast<const uint4*>(src);
-  uint4* d4 = reinterpret_cast<uint4*>(smem_all + at);
-  for (int i = tid; i < (int)(bytes >> 4); i += T) d4[i] = __ldg(s4 + i);
-  const unsigned off = at;
-  at += bytes;
-  return off;
+  for (int i = tid; i < (int)(bytes >> 4); i += T) smem_all4[at16 + i] = __ldg(s4 + i);
+  const unsigned w16 = at16;
+  at16 += bytes >> 4;
+  return w16;
 }
 __device__ __forceinline__ SmemModel stage_model(const ModelView& G, int tid, int T) {
   SmemModel S;
   static_cast<ssppm::DevModelHead&>(S) = G;
   unsigned at = 0;
-  S.body.off = stage_table(G.body, G.n_mbody * (unsigned)sizeof(DevBody), at, tid, T);
-  S.mg.off = S.sg.off = S.pair.off = S.mm.off = S.sph.off = 0;
+  S.body.w16 = stage_table(G.body, G.n_mbody * (unsigned)sizeof(DevBody), at, tid, T);
+  S.mg.w16 = S.sg.w16 = S.pair.w16 = S.mm.w16 = S.sph.w16 = 0;
   if (G.sdf_mode) {
-    S.sph.off = stage_table(G.sph, G.n_sphere * (unsigned)sizeof(DevSphere), at, tid, T);
+    S.sph.w16 = stage_table(G.sph, G.n_sphere * (unsigned)sizeof(DevSphere), at, tid, T);
   } else {
-    S.mg.off = stage_table(G.mg, G.n_mgeom * (unsigned)sizeof(DevMGeom), at, tid, T);
-    S.sg.off = stage_table(G.sg, G.n_sgeom * (unsigned)sizeof(DevSGeom), at, tid, T);
-    S.pair.off = stage_table(G.pair, G.n_pair * (unsigned)sizeof(DevPair), at, tid, T);
-    S.mm.off = stage_table(G.mm, G.n_mmpair * (unsigned)sizeof(DevMMPair), at, tid, T);
+    S.mg.w16 = stage_table(G.mg, G.n_mgeom * (unsigned)sizeof(DevMGeom), at, tid, T);
+    S.sg.w16 = stage_table(G.sg, G.n_sgeom * (unsigned)sizeof(DevSGeom), at, tid, T);
+    S.pair.w16 = stage_table(G.pair, G.n_pair * (unsigned)sizeof(DevPair), at, tid, T);
+    S.mm.w16 = stage_table(G.mm, G.n_mmpair * (unsigned)sizeof(DevMMPair), at, tid, T);
   }
   return S;
 }
@@ -229,40 +239,69 @@ __device__ __forceinline__ void score_tile(const SmemModel& M, const IterParams&
 // CES log-weights w_j = (ln(k + 1/2) - ln(j + 1)) / sum (tsp_elites.h:24-32) are recomputed on the
 // fly: lane l owns j = l, l + 32, ... in every pass, partial sums meet in an xor butterfly.
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ float ces_weight_sum(int k, float lk, int lane) {
+// Wide sums.  The elite reductions are DEFINED over 256 virtual lanes = 8 groups of 32: virtual lane v sums its
+// terms j = v, v + 256, ... in ascending order; the 32 partials of a group meet in an xor butterfly; the group
+// sums are added in ascending group order, groups without terms (32 g >= k) skipped (adding +0 is exact).  One
+// warp can walk the groups serially (small k: the one-CTA-per-query kernel) or the warps of a CTA can take one
+// group each (coop phase C, merge kernel): the same bits either way, and what the replica oracle restates.
+template <class Term>
+__device__ __forceinline__ float group_partial(int g, int k, int lane, Term term) {
   float acc = 0.0f;
-  for (int j = lane; j < k; j += 32) acc += lk - log_poly((float)j + 1.0f);
+  for (int j = 32 * g + lane; j < k; j += 256) acc = term(j, acc);
   return warp_butterfly(acc);
 }
+template <class Term>
+__device__ __forceinline__ float wide_sum_warp(int k, int lane, Term term) {
+  float tot = group_partial(0, k, lane, term);
+  for (int g = 1; g < 8 && 32 * g < k; ++g) tot += group_partial(g, k, lane, term);
+  return tot;
+}
+// all threads of the CTA call this; s_part: 8 floats of shared scratch; two barriers inside
+template <class Term>
+__device__ __forceinline__ float wide_sum_cta(int k, Term term, float* s_part) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  for (int g = warp; g < 8; g += nwarp)
+    if (g == 0 || 32 * g < k) { const float pg = group_partial(g, k, lane, term); if (lane == 0) s_part[g] = pg; }
+  __syncthreads();
+  float tot = s_part[0];
+  for (int g = 1; g < 8 && 32 * g < k; ++g) tot += s_part[g];
+  __syncthreads();
+  return tot;
+}
+struct WarpSum { int lane; template <class Term> __device__ __forceinline__ float operator()(int k, Term term) const { return wide_sum_warp(k, lane, term); } };
+struct CtaSum { float* s_part; template <class Term> __device__ __forceinline__ float operator()(int k, Term term) const { return wide_sum_cta(k, term, s_part); } };
 
-template <class ParamGetter>
+template <class Sum>
+__device__ __forceinline__ float ces_weight_sum(int k, float lk, Sum sum) {
+  return sum(k, [&](int j, float acc) { return acc + (lk - log_poly((float)j + 1.0f)); });
+}
+
+// K7 for one distribution element t of one query.  `sum` is WarpSum (one warp executes this) or CtaSum (the whole
+// CTA does); `writer` is true in the thread that stores the result.
+template <class ParamGetter, class Sum>
 __device__ __forceinline__ void update_element(const ScoreConfig& c, const unsigned long long* keys, int k, float lk, float sumw,
-                                               int t, float* mean, float* sigma, ParamGetter get_param, int lane) {
+                                               int t, float* mean, float* sigma, ParamGetter get_param, Sum sum, bool writer) {
   const int d = t % c.D;
-  float acc = 0.0f;
-  for (int j = lane; j < k; j += 32) {
+  const float em = sum(k, [&](int j, float acc) {
     const float w = (lk - log_poly((float)j + 1.0f)) / sumw;
-    acc = fmaf(w, get_param((unsigned)(keys[j] & 0xFFFFFFFFu), t), acc);
-  }
-  const float em = warp_butterfly(acc);
+    return fmaf(w, get_param((unsigned)(keys[j] & 0xFFFFFFFFu), t), acc);
+  });
   const float m0 = mean[t];
   float nm = fmaf(c.mean_lr, em - m0, m0);
   if (c.mode == MODE_TASK && d == 2) nm = fmaxf(nm, c.dist_zmin);
   nm = fminf(fmaxf(nm, c.lo[d]), c.hi[d]);
   const bool wrap = (c.mode == MODE_TASK && d == 3 && c.lo[3] != c.hi[3]);
-  float vacc = 0.0f;
-  for (int j = lane; j < k; j += 32) {
+  const float var = sum(k, [&](int j, float acc) {
     const float w = (lk - log_poly((float)j + 1.0f)) / sumw;
     const float v = get_param((unsigned)(keys[j] & 0xFFFFFFFFu), t);
     const float df = wrap ? wrap_angle_diff(v, nm, c.lo[3], c.hi[3]) : v - nm;
-    vacc = fmaf(w, df * df, vacc);
-  }
-  const float var = warp_butterfly(vacc);
+    return fmaf(w, df * df, acc);
+  });
   const float s0 = sigma[t];
   const float blend = fmaf(c.var_beta, var, (1.0f - c.var_beta) * (s0 * s0));
   float sg = clamp_sigma(c, sqrtf(blend));
   sg = clamp_sigma(c, sg * c.dec);               // adapt(true)
-  if (lane == 0) { mean[t] = nm; sigma[t] = sg; }
+  if (writer) { mean[t] = nm; sigma[t] = sg; }
 }
 
 struct StoredParams {
@@ -328,12 +367,12 @@ __device__ void cta_elites_and_update(const ScoreConfig& c, unsigned long long* 
     return;
   }
   const float lk = log_poly((float)k + 0.5f);
-  const float sumw = ces_weight_sum(k, lk, lane);          // every warp computes the same number
+  const float sumw = ces_weight_sum(k, lk, WarpSum{lane});   // every warp computes the same number
   for (int j = tid; j < k; j += T) elite_w[j] = (lk - log_poly((float)j + 1.0f)) / sumw;
   // the best candidate is read before any element is updated (its rows are not state, but keep the order of v1)
   const unsigned bi = (unsigned)(keys[0] & 0xFFFFFFFFu);
   if (c.do_update)
-    for (int t = warp; t < nfd; t += nwarp) update_element(c, keys, k, lk, sumw, t, mean, sigma, get_param, lane);
+    for (int t = warp; t < nfd; t += nwarp) update_element(c, keys, k, lk, sumw, t, mean, sigma, get_param, WarpSum{lane}, lane == 0);
   for (int t = tid; t < nfd; t += T) best[t] = get_param(bi, t);
   if (tid == 0) *best_valid = 1;
   __syncthreads();
@@ -341,9 +380,10 @@ __device__ void cta_elites_and_update(const ScoreConfig& c, unsigned long long* 
 
 // ---- coop phase B: grid-wide counting rank -------------------------------------------------
 // Items are the (query, candidate) keys, split evenly over the CTAs.  For its keys of one query a CTA
-// stages the query's raw keys in shared memory, `chunk` at a time, and counts the smaller ones:
-// 4 owned keys per warp pass, lanes stride over the chunk.  rank = position in the sorted order
-// (keys are unique: they embed the candidate index).
+// stages the query's raw keys in shared memory, `chunk` at a time (128-bit loads), and counts the smaller
+// ones: every warp scans its own slice of the chunk for up to 8 owned keys at a time (counters in
+// registers), warp totals meet in shared-memory counters.  rank = position in the sorted order (keys are
+// unique: they embed the candidate index).
 __device__ void rank_phase(const IterParams& P, unsigned char* smem_raw) {
   const ScoreConfig& c = P.cfg;
   const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarp = T >> 5;
@@ -361,28 +401,34 @@ __device__ void rank_phase(const IterParams& P, unsigned char* smem_raw) {
     const int nmine = (int)min((long long)(N - i0), hi_item - item);
     const unsigned long long* raw = P.keys_raw + (size_t)query * P.n_pad;
     unsigned long long* sorted = P.keys + (size_t)query * P.n_pad;
-    for (int a = tid; a < nmine; a += T) { s_mine[a] = raw[i0 + a]; s_cnt[a] = 0; }
+    for (int a = tid; a < nmine; a += T) { s_mine[a] = __ldcg(raw + i0 + a); s_cnt[a] = 0; }
     if (tid == 0) s_succ = 0;
-    for (int cs = 0; cs < N; cs += P.rank_chunk) {
+    for (int cs = 0; cs < N; cs += P.rank_chunk) {          // rank_chunk is even and the rows are 16-byte aligned
       const int cn = min(P.rank_chunk, N - cs);
       __syncthreads();
-      for (int j = tid; j < cn; j += T) s_chunk[j] = __ldcg(raw + cs + j);
+      {
+        const ulonglong2* src = reinterpret_cast<const ulonglong2*>(raw + cs);
+        ulonglong2* dst = reinterpret_cast<ulonglong2*>(s_chunk);
+        for (int j = tid; j < (cn >> 1); j += T) dst[j] = __ldcg(src + j);
+        if ((cn & 1) && tid == 0) s_chunk[cn - 1] = __ldcg(raw + cs + cn - 1);
+      }
       __syncthreads();
-      for (int a0 = warp * 4; a0 < nmine; a0 += nwarp * 4) {
-        const unsigned long long k0 = s_mine[a0], k1 = (a0 + 1 < nmine) ? s_mine[a0 + 1] : 0ull,
-                                 k2 = (a0 + 2 < nmine) ? s_mine[a0 + 2] : 0ull, k3 = (a0 + 3 < nmine) ? s_mine[a0 + 3] : 0ull;
-        int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
-        for (int j = lane; j < cn; j += 32) {
+      const int slice = (cn + nwarp - 1) / nwarp;
+      const int j0 = warp * slice, j1 = min(cn, j0 + slice);
+      for (int a0 = 0; a0 < nmine; a0 += 8) {
+        unsigned long long key[8];
+        int cnt[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) { key[u] = (a0 + u < nmine) ? s_mine[a0 + u] : 0ull; cnt[u] = 0; }
+        for (int j = j0 + lane; j < j1; j += 32) {
           const unsigned long long x = s_chunk[j];
-          c0 += (x < k0); c1 += (x < k1); c2 += (x < k2); c3 += (x < k3);
+#pragma unroll
+          for (int u = 0; u < 8; ++u) cnt[u] += (x < key[u]);
         }
-        c0 = __reduce_add_sync(0xFFFFFFFFu, c0); c1 = __reduce_add_sync(0xFFFFFFFFu, c1);
-        c2 = __reduce_add_sync(0xFFFFFFFFu, c2); c3 = __reduce_add_sync(0xFFFFFFFFu, c3);
-        if (lane == 0) {
-          s_cnt[a0] += c0;
-          if (a0 + 1 < nmine) s_cnt[a0 + 1] += c1;
-          if (a0 + 2 < nmine) s_cnt[a0 + 2] += c2;
-          if (a0 + 3 < nmine) s_cnt[a0 + 3] += c3;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int tot = __reduce_add_sync(0xFFFFFFFFu, cnt[u]);
+          if (lane == 0 && tot && a0 + u < nmine) atomicAdd(&s_cnt[a0 + u], tot);
         }
       }
     }
@@ -412,14 +458,13 @@ __device__ void rank_phase(const IterParams& P, unsigned char* smem_raw) {
   }
 }
 
-// ---- coop phase C: one warp per (query, distribution element); element nfd = the query's scalars ----
-__device__ void update_phase(const IterParams& P) {
+// ---- coop phase C: one CTA per (query, distribution element); element nfd = the query's scalars ----
+__device__ void update_phase(const IterParams& P, float* s_part) {
   const ScoreConfig& c = P.cfg;
-  const int lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+  const int tid = threadIdx.x, T = blockDim.x;
   const int nfd = c.n_free * c.D, N = c.n_cand;
-  const int gw = blockIdx.x * nwarp + (threadIdx.x >> 5), gstride = gridDim.x * nwarp;
   const int n_items = P.n_query * (nfd + 1);
-  for (int item = gw; item < n_items; item += gstride) {
+  for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
     const int query = item / (nfd + 1), t = item - query * (nfd + 1);
     const int n_succ = __ldcg(P.succ_acc + query);
     const int k = elite_count(n_succ, c.elite_frac);
@@ -427,21 +472,21 @@ __device__ void update_phase(const IterParams& P) {
     float* mean = P.mean + (size_t)query * nfd;
     float* sigma = P.sigma + (size_t)query * nfd;
     if (t == nfd) {                     // scalars + elite weights of the query
-      if (lane == 0) { P.n_success[query] = n_succ; P.n_elite[query] = k; }
+      if (tid == 0) { P.n_success[query] = n_succ; P.n_elite[query] = k; }
       if (n_succ > 0) {
         const float lk = log_poly((float)k + 0.5f);
-        const float sumw = ces_weight_sum(k, lk, lane);
+        const float sumw = ces_weight_sum(k, lk, CtaSum{s_part});
         float* ew = P.elite_w + (size_t)query * P.n_pad;
-        for (int j = lane; j < k; j += 32) ew[j] = (lk - log_poly((float)j + 1.0f)) / sumw;
+        for (int j = tid; j < k; j += T) ew[j] = (lk - log_poly((float)j + 1.0f)) / sumw;
       }
       continue;
     }
     if (!c.do_update) continue;
-    if (n_succ == 0) { if (lane == 0) sigma[t] = clamp_sigma(c, sigma[t] * c.inc); continue; }   // adapt(false)
+    if (n_succ == 0) { if (tid == 0) sigma[t] = clamp_sigma(c, sigma[t] * c.inc); continue; }   // adapt(false)
     const float lk = log_poly((float)k + 0.5f);
-    const float sumw = ces_weight_sum(k, lk, lane);
+    const float sumw = ces_weight_sum(k, lk, CtaSum{s_part});
     StoredParams gp{P.params + (size_t)query * N * nfd, nfd, (unsigned)P.cand_offset};
-    update_element(c, keys, k, lk, sumw, t, mean, sigma, gp, lane);
+    update_element(c, keys, k, lk, sumw, t, mean, sigma, gp, CtaSum{s_part}, tid == 0);
   }
 }
 
@@ -451,6 +496,7 @@ template <bool COOP, int MAXT, int MINB>
 __global__ void __launch_bounds__(MAXT, MINB)
 sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant__ IterParams P) {
   __shared__ int s_int[4];
+  __shared__ float s_part[8];
   const ScoreConfig& c = P.cfg;
   const int tid = threadIdx.x, T = blockDim.x;
   const int nfd = c.n_free * c.D;
@@ -483,7 +529,17 @@ sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant_
     return;
   }
   cg::grid_group grid = cg::this_grid();
+  // optional phase probe (diagnostics): thread 0 of every CTA stamps %globaltimer at the phase boundaries of the
+  // launch's first iteration: [cta][0] start, [1] scored, [2] past barrier 1, [3] ranked, [4] past barrier 2, [5] updated
+  auto stamp = [&](int it, int slot) {
+    if (P.probe && it == 0 && tid == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      P.probe[(size_t)blockIdx.x * 6 + slot] = t;
+    }
+  };
   for (int it = 0; it < P.n_inner; ++it) {
+    stamp(it, 0);
     // ---- phase A: score the tiles ----
     load_basis(s, c, P, tid, T);                         // phase B reuses this shared memory
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
@@ -494,13 +550,18 @@ sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant_
       score_tile(M, P, s, query, c0, nc, P.iter0 + (uint32_t)it);
       __syncthreads();
     }
+    stamp(it, 1);
     grid.sync();
+    stamp(it, 2);
     // ---- phase B: order the keys ----
     rank_phase(P, smem_raw);
+    stamp(it, 3);
     if (P.sort_only) { if (it + 1 < P.n_inner) grid.sync(); continue; }
     grid.sync();
+    stamp(it, 4);
     // ---- phase C: distribution update ----
-    update_phase(P);
+    update_phase(P, s_part);
+    stamp(it, 5);
     if (it + 1 < P.n_inner) grid.sync();
   }
 }
@@ -546,33 +607,33 @@ sspp_merge_rank_kernel(const __grid_constant__ MergeParams P) {
 }
 
 __global__ void __launch_bounds__(256)
-sspp_merge_finish_kernel(const __grid_constant__ MergeParams P) {
+sspp_merge_finish_kernel(const __grid_constant__ MergeParams P) {     // one CTA per distribution element (+1: the scalars)
+  __shared__ float s_part[8];
   const ScoreConfig& c = P.cfg;
-  const int lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+  const int tid = threadIdx.x, T = blockDim.x;
   const int nfd = c.n_free * c.D;
-  const int gw = blockIdx.x * nwarp + (threadIdx.x >> 5), gstride = gridDim.x * nwarp;
   const int n_succ = *P.succ_acc;
   const int k = elite_count(n_succ, c.elite_frac);
   const int best_ok0 = c.include_best ? reinterpret_cast<const int*>(P.state0)[3 * nfd] : 0;
   RegenParams gp{&c, P.seed, P.iter, P.state0, P.state0 + nfd, P.state0 + 2 * nfd, best_ok0};
-  for (int t = gw; t <= nfd; t += gstride) {
+  for (int t = blockIdx.x; t <= nfd; t += gridDim.x) {
     if (t == nfd) {
-      if (lane == 0) { *P.n_success = n_succ; *P.n_elite = k; }
+      if (tid == 0) { *P.n_success = n_succ; *P.n_elite = k; }
       const unsigned long long k0 = P.keys[0];
       if (n_succ > 0) {
-        if (lane == 0) { *P.best_idx = (int)(unsigned)(k0 & 0xFFFFFFFFu); *P.best_cost = key_cost(k0); *P.any_success = 1; *P.best_valid = 1; }
-        for (int e = lane; e < nfd; e += 32) P.best[e] = gp((unsigned)(k0 & 0xFFFFFFFFu), e);
+        if (tid == 0) { *P.best_idx = (int)(unsigned)(k0 & 0xFFFFFFFFu); *P.best_cost = key_cost(k0); *P.any_success = 1; *P.best_valid = 1; }
+        for (int e = tid; e < nfd; e += T) P.best[e] = gp((unsigned)(k0 & 0xFFFFFFFFu), e);
         const float lk = log_poly((float)k + 0.5f);
-        const float sumw = ces_weight_sum(k, lk, lane);
-        for (int j = lane; j < k; j += 32) P.elite_w[j] = (lk - log_poly((float)j + 1.0f)) / sumw;
-      } else if (lane == 0) { *P.best_idx = -1; *P.best_cost = __int_as_float(0x7F800000); }
+        const float sumw = ces_weight_sum(k, lk, CtaSum{s_part});
+        for (int j = tid; j < k; j += T) P.elite_w[j] = (lk - log_poly((float)j + 1.0f)) / sumw;
+      } else if (tid == 0) { *P.best_idx = -1; *P.best_cost = __int_as_float(0x7F800000); }
       continue;
     }
     if (!c.do_update) continue;
-    if (n_succ == 0) { if (lane == 0) P.sigma[t] = clamp_sigma(c, P.sigma[t] * c.inc); continue; }
+    if (n_succ == 0) { if (tid == 0) P.sigma[t] = clamp_sigma(c, P.sigma[t] * c.inc); continue; }
     const float lk = log_poly((float)k + 0.5f);
-    const float sumw = ces_weight_sum(k, lk, lane);
-    update_element(c, P.keys, k, lk, sumw, t, P.mean, P.sigma, gp, lane);
+    const float sumw = ces_weight_sum(k, lk, CtaSum{s_part});
+    update_element(c, P.keys, k, lk, sumw, t, P.mean, P.sigma, gp, CtaSum{s_part}, tid == 0);
   }
 }
 
@@ -672,8 +733,13 @@ struct VariantFns { IterKernel coop, solo; };
 template <int MAXT, int MINB>
 constexpr VariantFns variant_fns() { return {sspp_iterate_kernel<true, MAXT, MINB>, sspp_iterate_kernel<false, MAXT, MINB>}; }
 // same order as kIterVariants
+#ifdef SSPP_FAST_BUILD   // kernel experiments: only the two default variants are compiled (the others alias them)
+const VariantFns kFns[kNumIterVariants] = {variant_fns<256, 2>(), variant_fns<256, 2>(), variant_fns<320, 2>(), variant_fns<320, 2>(),
+                                           variant_fns<320, 2>(), variant_fns<320, 2>(), variant_fns<256, 2>(), variant_fns<256, 2>()};
+#else
 const VariantFns kFns[kNumIterVariants] = {variant_fns<256, 2>(), variant_fns<256, 3>(), variant_fns<320, 2>(), variant_fns<320, 3>(),
                                            variant_fns<448, 2>(), variant_fns<384, 2>(), variant_fns<128, 6>(), variant_fns<192, 5>()};
+#endif
 cudaError_t set_smem(IterKernel k, size_t smem_bytes) {   // per device / context, so no caching across calls
   if (smem_bytes <= 48 * 1024) return cudaSuccess;
   return cudaFuncSetAttribute(reinterpret_cast<const void*>(k), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
@@ -721,7 +787,7 @@ cudaError_t launch_merge_update(const MergeParams& P, cudaStream_t stream) {
   sspp_merge_rank_kernel<<<(std::max(P.n_keys, 1) + 255) / 256, 256, 0, stream>>>(P);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
-  sspp_merge_finish_kernel<<<(nfd + 1 + 7) / 8, 256, 0, stream>>>(P);
+  sspp_merge_finish_kernel<<<nfd + 1, 256, 0, stream>>>(P);
   return cudaGetLastError();
 }
 

@@ -42,6 +42,7 @@ struct IterParams {
   int* n_success; int* n_elite; int* best_idx; int* any_success;   // [Q]
   float* best_cost;         // [Q]
   int* succ_acc;            // [Q] scratch: success count accumulated by the ranking phase
+  unsigned long long* probe; // diagnostics, NULL = off: [grid][6] %globaltimer stamps at the phase boundaries (coop kernel)
 };
 
 // shared-memory bytes of the staged scene tables, and of the scoring phase for the given tile shape (the

@@ -65,8 +65,10 @@ struct alignas(16) DevMGeom {
   float R[9];
   float size[3];    // sphere r | capsule,cylinder r,half-length | box half extents
   int type;
-  int pair_begin, pair_end;   // range in the pair table
+  int pair_begin, pair_end;   // range in the pair table: [pair_begin, pair_mid) plane partners, [pair_mid, pair_end) bounded ones
   int body;
+  int pair_mid;
+  int pad_[3];
 };
 struct alignas(16) DevSGeom {
   float pos[3];     // world frame
@@ -120,6 +122,9 @@ struct ModelView : DevModelHead {
   const DevMMPair* mm;
   const DevSphere* sph;
 };
+
+static_assert(sizeof(DevBody) == 128 && sizeof(DevMGeom) == 96 && sizeof(DevSGeom) == 80 && sizeof(DevPair) == 32 &&
+              sizeof(DevSphere) == 32 && sizeof(DevMMPair) == 16, "table records are whole 16-byte words");
 
 // ----------------------------------------------------------------------------------------
 // small vector helpers (explicit fmaf everywhere)
@@ -183,7 +188,6 @@ SSPP_HD i4 ld4i(const int* p) {
   i4 r; r.x = p[0]; r.y = p[1]; r.z = p[2]; r.w = p[3]; return r;
 #endif
 }
-// R[9] + 3 trailing words (size / axis) of a record as three 4-word loads
 SSPP_HD float word_as_float(int w) {
 #if defined(__CUDA_ARCH__)
   return __int_as_float(w);
@@ -191,14 +195,32 @@ SSPP_HD float word_as_float(int w) {
   union { int i; float f; } b; b.i = w; return b.f;
 #endif
 }
+// Record access.  Tables are arrays of 16-byte aligned records; rec_f4 / rec_i4(tab, i, w) read words
+// [w, w + 4) of record i (w a multiple of 4).  These overloads serve plain arrays (host container, global
+// memory); the kernels add overloads for their shared-memory staged tables.  Word offsets of the groups:
+enum { BW_POS = 0, BW_R0 = 4, BW_ANCHOR = 16, BW_JOINT = 20, BW_FLAGS = 24, BW_SPH = 28,     // DevBody
+       GW_POS = 0, GW_R = 4, GW_TYPE = 16, GW_MID = 20,                                    // DevMGeom / DevSGeom
+       PW_C = 0, PW_S = 4,                                                               // DevPair
+       SW_C = 0, SW_MARGIN = 4 };                                                        // DevSphere
+template <class T> SSPP_HD f4 rec_f4(const T* tab, int i, int w) { return ld4(reinterpret_cast<const float*>(tab + i) + w); }
+template <class T> SSPP_HD i4 rec_i4(const T* tab, int i, int w) { return ld4i(reinterpret_cast<const int*>(tab + i) + w); }
+// R[9] + 3 trailing words (size / axis) of record i, starting at word w, as three 4-word reads
 struct m3t { m3 R; v3 t; };
-SSPP_HD m3t ld_rot12(const float* R) {
-  const f4 a = ld4(R), b = ld4(R + 4), c = ld4(R + 8);
+template <class TAB>
+SSPP_HD m3t rec_rot12(const TAB& tab, int i, int w) {
+  const f4 a = rec_f4(tab, i, w), b = rec_f4(tab, i, w + 4), c = rec_f4(tab, i, w + 8);
   m3t o;
   o.R.a[0] = a.x; o.R.a[1] = a.y; o.R.a[2] = a.z; o.R.a[3] = a.w;
   o.R.a[4] = b.x; o.R.a[5] = b.y; o.R.a[6] = b.z; o.R.a[7] = b.w;
   o.R.a[8] = c.x; o.t.x = c.y; o.t.y = c.z; o.t.z = c.w;
   return o;
+}
+SSPP_HD int lowest_bit(uint32_t m) {   // index of the lowest set bit, m != 0
+#if defined(__CUDA_ARCH__)
+  return __ffs((int)m) - 1;
+#else
+  return __builtin_ctz(m);
+#endif
 }
 
 // ----------------------------------------------------------------------------------------
@@ -367,10 +389,9 @@ SSPP_HD void rot_axis(m3& R, float s, float c) {
 }
 
 // parent frame (Rp,pp) -> this body's frame (R,p) given planned coordinates q
-template <class QA>
-SSPP_HD void fk_body(const DevBody& B, bool has_parent, const m3& Rp, v3 pp, QA& q, m3* R, v3* p) {
-  const i4 jt = ld4i(&B.parent);        // parent, jtype, qidx, axis_kind
-  const int jtype = jt.y, qidx = jt.z, axis_kind = jt.w;
+template <class TAB, class QA>
+SSPP_HD void fk_body(const TAB& bodies, int b, i4 jt, bool has_parent, const m3& Rp, v3 pp, QA& q, m3* R, v3* p) {
+  const int jtype = jt.y, qidx = jt.z, axis_kind = jt.w;     // jt = (parent, jtype, qidx, axis_kind)
   if (jtype == JT_FREE4) {  // (x,y,z,yaw) -> pose; quaternion (cos y/2,0,0,sin y/2) == Rz(yaw)
     float s, c;
     sincos_poly(q.get(qidx + 3), &s, &c);
@@ -380,15 +401,16 @@ SSPP_HD void fk_body(const DevBody& B, bool has_parent, const m3& Rp, v3 pp, QA&
     *p = mk(q.get(qidx), q.get(qidx + 1), q.get(qidx + 2));
     return;
   }
-  const f4 ps = ld4(B.pos);             // pos, axis_sign
-  const int has_anchor = B.has_anchor, r0_identity = B.r0_identity;
+  const f4 ps = rec_f4(bodies, b, BW_POS);             // pos, axis_sign
+  const i4 fl = rec_i4(bodies, b, BW_FLAGS);           // has_anchor, r0_identity, geom_begin, geom_end
+  const int has_anchor = fl.x, r0_identity = fl.y;
   m3 Rw; v3 pw;
   v3 axis = mk(0.f, 0.f, 0.f);
   if (has_parent) {
-    if (r0_identity && axis_kind < 3) Rw = Rp;
-    else { const m3t ra = ld_rot12(B.R0); axis = ra.t; Rw = r0_identity ? Rp : mulm(Rp, ra.R.a); }
+    if (r0_identity && axis_kind < 3 && jtype == JT_HINGE) Rw = Rp;
+    else { const m3t ra = rec_rot12(bodies, b, BW_R0); axis = ra.t; Rw = r0_identity ? Rp : mulm(Rp, ra.R.a); }
     pw = add(pp, mulv(Rp, mk(ps.x, ps.y, ps.z)));
-  } else { const m3t ra = ld_rot12(B.R0); axis = ra.t; Rw = ra.R; pw = mk(ps.x, ps.y, ps.z); }
+  } else { const m3t ra = rec_rot12(bodies, b, BW_R0); axis = ra.t; Rw = ra.R; pw = mk(ps.x, ps.y, ps.z); }
   if (jtype == JT_HINGE) {
     m3 Rn;
     if (axis_kind < 3) {
@@ -403,10 +425,9 @@ SSPP_HD void fk_body(const DevBody& B, bool has_parent, const m3& Rp, v3 pp, QA&
       rodrigues(axis, q.get(qidx), Rj);
       Rn = mulm(Rw, Rj);
     }
-    if (has_anchor) { const f4 an4 = ld4(B.anchor); const v3 an = mk(an4.x, an4.y, an4.z); pw = add(pw, sub(mulv(Rw, an), mulv(Rn, an))); }
+    if (has_anchor) { const f4 an4 = rec_f4(bodies, b, BW_ANCHOR); const v3 an = mk(an4.x, an4.y, an4.z); pw = add(pw, sub(mulv(Rw, an), mulv(Rn, an))); }
     Rw = Rn;
   } else if (jtype == JT_SLIDE) {
-    if (r0_identity && axis_kind < 3 && has_parent) axis = ld3(B.axis);
     pw = madd(mulv(Rw, axis), q.get(qidx), pw);
   }
   *R = Rw; *p = pw;
@@ -763,36 +784,49 @@ SSPP_HD float contact_cost(int rule, float d, float margin, v3 ca, v3 cb) {
   return 0.0f;
 }
 
-SSPP_HD Prim place(const DevMGeom& g, const m3& R, v3 p) {
+// moving geom g of table `mg` under the body frame (R, p)
+template <class TAB>
+SSPP_HD Prim place(const TAB& mg, int g, const m3& R, v3 p) {
   Prim P;
-  P.p = add(p, mulv(R, ld3(g.pos)));
-  P.R = mulm(R, g.R);
-  P.s = ld3(g.size);
-  P.type = g.type;
+  const f4 gp = rec_f4(mg, g, GW_POS);
+  const m3t rs = rec_rot12(mg, g, GW_R);
+  P.p = add(p, mulv(R, mk(gp.x, gp.y, gp.z)));
+  P.R = mulm(R, rs.R.a);
+  P.s = rs.t;
+  P.type = rec_i4(mg, g, GW_TYPE).x;
   return P;
 }
-// orientation part of a placement, as little as the type needs: capsules and cylinders only use their
+// orientation and size of a placement, as little as the type needs: capsules and cylinders only use their
 // axis (column 2), spheres nothing; element formulas are those of mulm
-SSPP_HD void place_rotation(const DevMGeom& g, const m3& R, Prim* P) {
-  if (g.type == GT_BOX) { const m3t rs = ld_rot12(g.R); P->R = mulm(R, rs.R.a); return; }
-  if (g.type == GT_SPHERE) return;
+template <class TAB>
+SSPP_HD void place_rotation(const TAB& mg, int g, int type, const m3& R, Prim* P) {
+  if (type == GT_BOX) { const m3t rs = rec_rot12(mg, g, GW_R); P->s = rs.t; P->R = mulm(R, rs.R.a); return; }
+  const f4 a = rec_f4(mg, g, GW_R), b = rec_f4(mg, g, GW_R + 4), c = rec_f4(mg, g, GW_R + 8);   // R0..3 | R4..7 | R8, size
+  P->s = mk(c.y, c.z, c.w);
+  if (type == GT_SPHERE) return;
+  const float g2 = a.z, g5 = b.y, g8 = c.x;
 #pragma unroll
   for (int i = 0; i < 3; ++i)
-    P->R.a[3 * i + 2] = fmaf(R.a[3 * i + 2], g.R[8], fmaf(R.a[3 * i + 1], g.R[5], R.a[3 * i] * g.R[2]));
+    P->R.a[3 * i + 2] = fmaf(R.a[3 * i + 2], g8, fmaf(R.a[3 * i + 1], g5, R.a[3 * i] * g2));
 }
-SSPP_HD Prim static_prim(const DevSGeom& g) {
+template <class TAB>
+SSPP_HD Prim static_prim(const TAB& sg, int i) {
   Prim P;
-  const f4 a = ld4(g.pos);
-  const m3t rs = ld_rot12(g.R);
-  P.p = mk(a.x, a.y, a.z); P.R = rs.R; P.s = rs.t; P.type = g.type;
+  const f4 a = rec_f4(sg, i, GW_POS);
+  const m3t rs = rec_rot12(sg, i, GW_R);
+  P.p = mk(a.x, a.y, a.z); P.R = rs.R; P.s = rs.t; P.type = rec_i4(sg, i, GW_TYPE).x;
   return P;
 }
+SSPP_HD Prim static_prim(const DevSGeom& g) { return static_prim(&g, 0); }
 
 // Collision cost of one configuration q: FK of every moving body, placement of its geoms,
 // bounding-sphere cull, narrow phase, contact rule.  XF is a transform store with
 // put(body, k, value) / get(body, k), k in 0..11 (R row-major then p) — shared memory on the
 // GPU, a plain array in the replica; unused when model.chain is set.
 // QA exposes the planned coordinates as q.get(i).
+// The broad phase of a geom runs branch-free over its pair records, 32 at a time, into a bit mask (plane
+// partners first, then bounded ones); the narrow phase then visits the set bits in ascending order, so the
+// contact costs are summed in pair-table order.
 template <class MT, class XF, class QA>
 SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf) {
   float cost = M.static_cost;
@@ -801,74 +835,92 @@ SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf) {
   for (int k = 0; k < 9; ++k) R.a[k] = 0.0f;
 #pragma unroll 1
   for (int b = 0; b < M.n_mbody; ++b) {
-    const DevBody& B = M.body[b];
+    const i4 jt = rec_i4(M.body, b, BW_JOINT);               // parent, jtype, qidx, axis_kind
     m3 Rp; v3 pp;
-    const bool hp = B.parent >= 0;
+    const bool hp = jt.x >= 0;
     if (hp) {
       if (M.chain) { Rp = R; pp = p; }
       else {
 #pragma unroll
-        for (int k = 0; k < 9; ++k) Rp.a[k] = xf.get(B.parent, k);
-        pp = mk(xf.get(B.parent, 9), xf.get(B.parent, 10), xf.get(B.parent, 11));
+        for (int k = 0; k < 9; ++k) Rp.a[k] = xf.get(jt.x, k);
+        pp = mk(xf.get(jt.x, 9), xf.get(jt.x, 10), xf.get(jt.x, 11));
       }
     } else { pp = mk(0.f, 0.f, 0.f); Rp = R; }
-    fk_body(B, hp, Rp, pp, q, &R, &p);
+    fk_body(M.body, b, jt, hp, Rp, pp, q, &R, &p);
     if (!M.chain) {
 #pragma unroll
       for (int k = 0; k < 9; ++k) xf.put(b, k, R.a[k]);
       xf.put(b, 9, p.x); xf.put(b, 10, p.y); xf.put(b, 11, p.z);
     }
     if (M.sdf_mode) {                                        // sphere samples of this body against the grid
+      const i4 sp = rec_i4(M.body, b, BW_SPH);          // sph_begin, sph_end
 #pragma unroll 1
-      for (int k = B.sph_begin; k < B.sph_end; ++k) {
-        const DevSphere& S = M.sph[k];
-        const float d = sdf_sample(M.grid, add(p, mulv(R, ld3(S.c)))) - S.r;
-        cost += sphere_contact_cost(M.rule, d, S.margin);
+      for (int k = sp.x; k < sp.y; ++k) {
+        const f4 sc = rec_f4(M.sph, k, SW_C);                // centre, radius
+        const float margin = word_as_float(rec_i4(M.sph, k, SW_MARGIN).x);
+        const float d = sdf_sample(M.grid, add(p, mulv(R, mk(sc.x, sc.y, sc.z)))) - sc.w;
+        cost += sphere_contact_cost(M.rule, d, margin);
       }
       continue;
     }
+    const i4 fl = rec_i4(M.body, b, BW_FLAGS);               // has_anchor, r0_identity, geom_begin, geom_end
 #pragma unroll 1
-    for (int g = B.geom_begin; g < B.geom_end; ++g) {
-      const DevMGeom& G = M.mg[g];
-      const f4 gp = ld4(G.pos);                              // pos, rbound
-      const i4 gi = ld4i(&G.type);                           // type, pair_begin, pair_end, body
+    for (int g = fl.z; g < fl.w; ++g) {
+      const f4 gp = rec_f4(M.mg, g, GW_POS);                 // pos, rbound
+      const i4 gi = rec_i4(M.mg, g, GW_TYPE);                // type, pair_begin, pair_end, body
+      const int pair_mid = rec_i4(M.mg, g, GW_MID).x;
       Prim P;
       P.p = add(p, mulv(R, mk(gp.x, gp.y, gp.z)));
       P.type = gi.x;
       bool rotated = false;
 #pragma unroll 1
-      for (int k = gi.y; k < gi.z; ++k) {
-        const DevPair& pr = M.pair[k];
-        const f4 c4 = ld4(pr.c);
-        const i4 t4 = ld4i(&pr.s);                           // s, margin, thr, plane (floats as raw words)
-        const v3 pc = mk(c4.x, c4.y, c4.z);
-        if (t4.w) { if (dot(pc, P.p) > c4.w) continue; }     // bounding sphere beyond the half space
-        else { const v3 w = sub(P.p, pc); if (dot(w, w) > c4.w) continue; }   // bounding spheres apart
-        const DevSGeom& S = M.sg[t4.x];
-        const float margin = word_as_float(t4.y), thr = word_as_float(t4.z);
-        if (!rotated) { P.s = ld3(G.size); place_rotation(G, R, &P); rotated = true; }
-        const Prim Q = static_prim(S);
-        const float d = moving_static_sd(P, Q, thr);
-        cost += contact_cost(M.rule, d, margin, P.p, Q.p);
+      for (int k0 = gi.y; k0 < gi.z; k0 += 32) {
+        const int k1 = (gi.z - k0 < 32) ? gi.z : k0 + 32;
+        uint32_t near_mask = 0u;
+        int k = k0;
+        const int km = (pair_mid < k1) ? pair_mid : k1;
+#pragma unroll 1
+        for (; k < km; ++k) {                // plane partners: bounding sphere beyond the half space?
+          const f4 c4 = rec_f4(M.pair, k, PW_C);
+          if (!(dot(mk(c4.x, c4.y, c4.z), P.p) > c4.w)) near_mask |= 1u << (k - k0);
+        }
+#pragma unroll 1
+        for (; k < k1; ++k) {                                // bounded partners: bounding spheres apart?
+          const f4 c4 = rec_f4(M.pair, k, PW_C);
+          const v3 w = sub(P.p, mk(c4.x, c4.y, c4.z));
+          if (!(dot(w, w) > c4.w)) near_mask |= 1u << (k - k0);
+        }
+        while (near_mask) {
+          const int j = lowest_bit(near_mask);
+          near_mask &= near_mask - 1u;
+          const i4 t4 = rec_i4(M.pair, k0 + j, PW_S);        // s, margin, thr, plane (floats as raw words)
+          const float margin = word_as_float(t4.y), thr = word_as_float(t4.z);
+          if (!rotated) { place_rotation(M.mg, g, gi.x, R, &P); rotated = true; }
+          const Prim Q = static_prim(M.sg, t4.x);
+          const float d = moving_static_sd(P, Q, thr);
+          cost += contact_cost(M.rule, d, margin, P.p, Q.p);
+        }
       }
     }
   }
 #pragma unroll 1
   for (int k = 0; k < M.n_mmpair; ++k) {   // pairs of geoms that move relative to each other
-    const DevMGeom& Ga = M.mg[M.mm[k].a];
-    const DevMGeom& Gb = M.mg[M.mm[k].b];
+    const i4 mp = rec_i4(M.mm, k, 0);      // a, b, margin
+    const float margin = word_as_float(mp.z);
+    const int ba = rec_i4(M.mg, mp.x, GW_TYPE).w, bb = rec_i4(M.mg, mp.y, GW_TYPE).w;
+    const float ra = rec_f4(M.mg, mp.x, GW_POS).w, rb = rec_f4(M.mg, mp.y, GW_POS).w;
     m3 Ra, Rb; v3 pa, pb;
 #pragma unroll
-    for (int e = 0; e < 9; ++e) { Ra.a[e] = xf.get(Ga.body, e); Rb.a[e] = xf.get(Gb.body, e); }
-    pa = mk(xf.get(Ga.body, 9), xf.get(Ga.body, 10), xf.get(Ga.body, 11));
-    pb = mk(xf.get(Gb.body, 9), xf.get(Gb.body, 10), xf.get(Gb.body, 11));
-    const Prim P = place(Ga, Ra, pa), Q = place(Gb, Rb, pb);
+    for (int e = 0; e < 9; ++e) { Ra.a[e] = xf.get(ba, e); Rb.a[e] = xf.get(bb, e); }
+    pa = mk(xf.get(ba, 9), xf.get(ba, 10), xf.get(ba, 11));
+    pb = mk(xf.get(bb, 9), xf.get(bb, 10), xf.get(bb, 11));
+    const Prim P = place(M.mg, mp.x, Ra, pa), Q = place(M.mg, mp.y, Rb, pb);
     const v3 w = sub(P.p, Q.p);
-    const float rr = Ga.rbound + Gb.rbound + fmaxf(M.mm[k].margin, 0.0f) + 1e-4f;
+    const float rr = ra + rb + fmaxf(margin, 0.0f) + 1e-4f;
     if (dot(w, w) > rr * rr) continue;
     bool ok;
     const float d = prim_sd(P, Q, &ok);
-    cost += contact_cost(M.rule, d, M.mm[k].margin, P.p, Q.p);
+    cost += contact_cost(M.rule, d, margin, P.p, Q.p);
   }
   return cost;
 }
@@ -879,7 +931,7 @@ SSPP_HD float sdf_node_value(const MT& M, int i, int j, int k) {
   const SdfGrid& g = M.grid;
   const v3 x = mk(fmaf((float)i, g.h[0], g.lo[0]), fmaf((float)j, g.h[1], g.lo[1]), fmaf((float)k, g.h[2], g.lo[2]));
   float best = 3.0e38f;
-  for (int s = 0; s < M.n_sgeom; ++s) best = fminf(best, point_prim_sd(x, static_prim(M.sg[s])));
+  for (int s = 0; s < M.n_sgeom; ++s) best = fminf(best, point_prim_sd(x, static_prim(M.sg, s)));
   return best;
 }
 

@@ -592,6 +592,11 @@ ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const 
       ++D.n_pair;
     }
     D.mg[ig].pair_end = D.n_pair;
+    // plane partners first (the kernel's broad phase runs the two kinds in separate branch-free loops)
+    std::stable_partition(D.pair + D.mg[ig].pair_begin, D.pair + D.mg[ig].pair_end,
+                          [&](const DevPair& pr) { return D.sg[pr.s].rbound < 0.0f; });
+    D.mg[ig].pair_mid = D.mg[ig].pair_begin;
+    while (D.mg[ig].pair_mid < D.mg[ig].pair_end && D.sg[D.pair[D.mg[ig].pair_mid].s].rbound < 0.0f) ++D.mg[ig].pair_mid;
   }
   // broad-phase test of every pair, precomputed in FP32 (see DevPair)
   for (int ig = 0; ig < D.n_mgeom; ++ig)
