@@ -93,21 +93,29 @@ __device__ __forceinline__ Smem carve(unsigned char* raw, const ScoreConfig& c, 
 // one broadcast wavefront) instead of an indexed constant load through the ADU or a generic load.
 extern __shared__ uint4 smem_all4[];                    // the dynamic shared memory as 16-byte words
 #define smem_all (reinterpret_cast<unsigned char*>(smem_all4))
+// A staged table is addressed by its 32-bit shared-window byte address, formed ONCE per thread; every record
+// read is one explicit ld.shared.v4 (the compiler's own shared addressing re-derives the window base from
+// SR_CgaCtaId at every use inside these loops).
 template <class T>
-struct SmemTab { unsigned w16; };                       // first 16-byte word of the table
+struct SmemTab { unsigned addr; };
 struct SmemModel : ssppm::DevModelHead {
   SmemTab<DevBody> body; SmemTab<DevMGeom> mg; SmemTab<DevSGeom> sg; SmemTab<DevPair> pair; SmemTab<DevMMPair> mm; SmemTab<DevSphere> sph;
 };
-// overloads of the record accessors of sspp_math.h: one LDS.128 off the typed shared array
+__device__ __forceinline__ uint4 lds128(unsigned addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+// overloads of the record accessors of sspp_math.h
 template <class T>
 __device__ __forceinline__ ssppm::f4 rec_f4(const SmemTab<T>& t, int i, int w) {
-  const uint4 v = smem_all4[t.w16 + (unsigned)i * (unsigned)(sizeof(T) / 16) + (unsigned)(w >> 2)];
+  const uint4 v = lds128(t.addr + (unsigned)i * (unsigned)sizeof(T) + (unsigned)(w << 2));
   ssppm::f4 r; r.x = __uint_as_float(v.x); r.y = __uint_as_float(v.y); r.z = __uint_as_float(v.z); r.w = __uint_as_float(v.w);
   return r;
 }
 template <class T>
 __device__ __forceinline__ ssppm::i4 rec_i4(const SmemTab<T>& t, int i, int w) {
-  const uint4 v = smem_all4[t.w16 + (unsigned)i * (unsigned)(sizeof(T) / 16) + (unsigned)(w >> 2)];
+  const uint4 v = lds128(t.addr + (unsigned)i * (unsigned)sizeof(T) + (unsigned)(w << 2));
   ssppm::i4 r; r.x = (int)v.x; r.y = (int)v.y; r.z = (int)v.z; r.w = (int)v.w;
   return r;
 }
@@ -116,21 +124,22 @@ __device__ __forceinline__ unsigned stage_table(const void* src, unsigned bytes,
   for (int i = tid; i < (int)(bytes >> 4); i += T) smem_all4[at16 + i] = __ldg(s4 + i);
   const unsigned w16 = at16;
   at16 += bytes >> 4;
-  return w16;
+  return w16 << 4;
 }
 __device__ __forceinline__ SmemModel stage_model(const ModelView& G, int tid, int T) {
   SmemModel S;
   static_cast<ssppm::DevModelHead&>(S) = G;
+  const unsigned base = (unsigned)__cvta_generic_to_shared(smem_all4);
   unsigned at = 0;
-  S.body.w16 = stage_table(G.body, G.n_mbody * (unsigned)sizeof(DevBody), at, tid, T);
-  S.mg.w16 = S.sg.w16 = S.pair.w16 = S.mm.w16 = S.sph.w16 = 0;
+  S.body.addr = base + stage_table(G.body, G.n_mbody * (unsigned)sizeof(DevBody), at, tid, T);
+  S.mg.addr = S.sg.addr = S.pair.addr = S.mm.addr = S.sph.addr = base;
   if (G.sdf_mode) {
-    S.sph.w16 = stage_table(G.sph, G.n_sphere * (unsigned)sizeof(DevSphere), at, tid, T);
+    S.sph.addr = base + stage_table(G.sph, G.n_sphere * (unsigned)sizeof(DevSphere), at, tid, T);
   } else {
-    S.mg.w16 = stage_table(G.mg, G.n_mgeom * (unsigned)sizeof(DevMGeom), at, tid, T);
-    S.sg.w16 = stage_table(G.sg, G.n_sgeom * (unsigned)sizeof(DevSGeom), at, tid, T);
-    S.pair.w16 = stage_table(G.pair, G.n_pair * (unsigned)sizeof(DevPair), at, tid, T);
-    S.mm.w16 = stage_table(G.mm, G.n_mmpair * (unsigned)sizeof(DevMMPair), at, tid, T);
+    S.mg.addr = base + stage_table(G.mg, G.n_mgeom * (unsigned)sizeof(DevMGeom), at, tid, T);
+    S.sg.addr = base + stage_table(G.sg, G.n_sgeom * (unsigned)sizeof(DevSGeom), at, tid, T);
+    S.pair.addr = base + stage_table(G.pair, G.n_pair * (unsigned)sizeof(DevPair), at, tid, T);
+    S.mm.addr = base + stage_table(G.mm, G.n_mmpair * (unsigned)sizeof(DevMMPair), at, tid, T);
   }
   return S;
 }

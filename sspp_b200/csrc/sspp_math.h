@@ -31,7 +31,7 @@ namespace ssppm {
 // ----------------------------------------------------------------------------------------
 // limits of the flattened model
 // ----------------------------------------------------------------------------------------
-enum { MAX_MBODY = 16, MAX_MGEOM = 32, MAX_SGEOM = 112, MAX_PAIR = 1024, MAX_MMPAIR = 64,
+enum { MAX_MBODY = 16, MAX_MGEOM = 64, MAX_GEOM_PAIRS = 32, MAX_SGEOM = 112, MAX_PAIR = 1024, MAX_MMPAIR = 64,
        MAX_DOF = 9, MAX_K = 16, MAX_SPHERE = 256 };
 
 enum GeomType { GT_PLANE = 0, GT_SPHERE = 2, GT_CAPSULE = 3, GT_CYLINDER = 5, GT_BOX = 6 };
@@ -65,9 +65,8 @@ struct alignas(16) DevMGeom {
   float R[9];
   float size[3];    // sphere r | capsule,cylinder r,half-length | box half extents
   int type;
-  int pair_begin, pair_end;   // range in the pair table: [pair_begin, pair_mid) plane partners, [pair_mid, pair_end) bounded ones
+  int pair_begin, pair_mid, pair_end;   // <= 32 pairs: [pair_begin, pair_mid) plane partners, [pair_mid, pair_end) bounded ones
   int body;
-  int pair_mid;
   int pad_[3];
 };
 struct alignas(16) DevSGeom {
@@ -199,7 +198,7 @@ SSPP_HD float word_as_float(int w) {
 // [w, w + 4) of record i (w a multiple of 4).  These overloads serve plain arrays (host container, global
 // memory); the kernels add overloads for their shared-memory staged tables.  Word offsets of the groups:
 enum { BW_POS = 0, BW_R0 = 4, BW_ANCHOR = 16, BW_JOINT = 20, BW_FLAGS = 24, BW_SPH = 28,     // DevBody
-       GW_POS = 0, GW_R = 4, GW_TYPE = 16, GW_MID = 20,                                    // DevMGeom / DevSGeom
+       GW_POS = 0, GW_R = 4, GW_TYPE = 16, GW_BODY = 20,                                   // DevMGeom / DevSGeom
        PW_C = 0, PW_S = 4,                                                               // DevPair
        SW_C = 0, SW_MARGIN = 4 };                                                        // DevSphere
 template <class T> SSPP_HD f4 rec_f4(const T* tab, int i, int w) { return ld4(reinterpret_cast<const float*>(tab + i) + w); }
@@ -867,25 +866,21 @@ SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf) {
 #pragma unroll 1
     for (int g = fl.z; g < fl.w; ++g) {
       const f4 gp = rec_f4(M.mg, g, GW_POS);                 // pos, rbound
-      const i4 gi = rec_i4(M.mg, g, GW_TYPE);                // type, pair_begin, pair_end, body
-      const int pair_mid = rec_i4(M.mg, g, GW_MID).x;
+      const i4 gi = rec_i4(M.mg, g, GW_TYPE);                // type, pair_begin, pair_mid, pair_end (<= 32 pairs)
       Prim P;
       P.p = add(p, mulv(R, mk(gp.x, gp.y, gp.z)));
       P.type = gi.x;
       bool rotated = false;
-#pragma unroll 1
-      for (int k0 = gi.y; k0 < gi.z; k0 += 32) {
-        const int k1 = (gi.z - k0 < 32) ? gi.z : k0 + 32;
+      {
+        const int k0 = gi.y;
         uint32_t near_mask = 0u;
-        int k = k0;
-        const int km = (pair_mid < k1) ? pair_mid : k1;
 #pragma unroll 1
-        for (; k < km; ++k) {                // plane partners: bounding sphere beyond the half space?
+        for (int k = k0; k < gi.z; ++k) {                    // plane partners: bounding sphere beyond the half space?
           const f4 c4 = rec_f4(M.pair, k, PW_C);
           if (!(dot(mk(c4.x, c4.y, c4.z), P.p) > c4.w)) near_mask |= 1u << (k - k0);
         }
 #pragma unroll 1
-        for (; k < k1; ++k) {                                // bounded partners: bounding spheres apart?
+        for (int k = gi.z; k < gi.w; ++k) {                  // bounded partners: bounding spheres apart?
           const f4 c4 = rec_f4(M.pair, k, PW_C);
           const v3 w = sub(P.p, mk(c4.x, c4.y, c4.z));
           if (!(dot(w, w) > c4.w)) near_mask |= 1u << (k - k0);
@@ -907,7 +902,7 @@ SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf) {
   for (int k = 0; k < M.n_mmpair; ++k) {   // pairs of geoms that move relative to each other
     const i4 mp = rec_i4(M.mm, k, 0);      // a, b, margin
     const float margin = word_as_float(mp.z);
-    const int ba = rec_i4(M.mg, mp.x, GW_TYPE).w, bb = rec_i4(M.mg, mp.y, GW_TYPE).w;
+    const int ba = rec_i4(M.mg, mp.x, GW_BODY).x, bb = rec_i4(M.mg, mp.y, GW_BODY).x;
     const float ra = rec_f4(M.mg, mp.x, GW_POS).w, rb = rec_f4(M.mg, mp.y, GW_POS).w;
     m3 Ra, Rb; v3 pa, pb;
 #pragma unroll

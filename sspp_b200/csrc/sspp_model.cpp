@@ -624,6 +624,34 @@ ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const 
       D.mm[D.n_mmpair].margin = (float)std::max(m.geom_margin[g], m.geom_margin[h]);
       ++D.n_mmpair;
     }
+  // a moving geom carries at most MAX_GEOM_PAIRS pair records (one mask word in the kernel's broad phase): geoms
+  // with more partners are emitted again with the next slice of their pairs
+  bool oversize = false;
+  for (int ig = 0; ig < D.n_mgeom; ++ig) if (D.mg[ig].pair_end - D.mg[ig].pair_begin > MAX_GEOM_PAIRS) oversize = true;
+  if (oversize && !opt.sdf) {
+    std::vector<DevMGeom> out;
+    std::vector<int> src_out, first_of(D.n_mgeom, 0);
+    for (int mb = 0; mb < D.n_mbody; ++mb) {
+      const int gb = D.body[mb].geom_begin, ge = D.body[mb].geom_end;
+      D.body[mb].geom_begin = (int)out.size();
+      for (int ig = gb; ig < ge; ++ig) {
+        first_of[ig] = (int)out.size();
+        const DevMGeom& G = D.mg[ig];
+        for (int k = G.pair_begin; k < G.pair_end || k == G.pair_begin; k += MAX_GEOM_PAIRS) {
+          DevMGeom c = G;
+          c.pair_begin = k; c.pair_end = std::min(k + (int)MAX_GEOM_PAIRS, G.pair_end);
+          c.pair_mid = std::min(std::max(G.pair_mid, c.pair_begin), c.pair_end);
+          out.push_back(c); src_out.push_back(mgeom_src[ig]);
+        }
+      }
+      D.body[mb].geom_end = (int)out.size();
+    }
+    if ((int)out.size() > MAX_MGEOM) throw std::runtime_error("too many moving geoms after splitting their pair lists");
+    for (int k = 0; k < D.n_mmpair; ++k) { D.mm[k].a = first_of[D.mm[k].a]; D.mm[k].b = first_of[D.mm[k].b]; }
+    std::copy(out.begin(), out.end(), D.mg);
+    D.n_mgeom = (int)out.size();
+    mgeom_src = src_out;
+  }
   if (opt.sdf) {
     // The grid is the union of the static partners; it cannot express a per-geom collision mask, so every
     // sampled moving geom must see exactly the same static geoms, and nothing may collide moving-vs-moving.
