@@ -64,27 +64,36 @@ __device__ __forceinline__ float key_cost(unsigned long long key) {
 }
 __device__ __forceinline__ bool key_success(unsigned long long key) { return (unsigned)(key >> 32) != 0xFFFFFFFFu; }
 
-// shared memory carve-up of the scoring phase (all 4-byte words)
+// shared memory carve-up of the scoring phase (all 4-byte words; every segment starts on a 16-byte boundary).
+// Banded collocation rows have a pitch of 4 floats when the band fits (degree <= 3), control-point rows a pitch
+// of dp = D rounded up to 4 with zero padding, so a row is one / dp/4 128-bit reads.
+__host__ __device__ __forceinline__ int row_pitch(int w) { return w <= 4 ? 4 : (w | 1); }
+__host__ __device__ __forceinline__ int up4(int n) { return (n + 3) & ~3; }
 struct Smem {
   unsigned long long* keys;   // coop == 0 only: n_pad sort keys
   float *psi_col, *psi_arc, *X, *cc, *cw, *seg, *qs, *xf;
   int *first_col, *first_arc;
+  unsigned a_psi_col, a_psi_arc, a_X;   // shared-window byte addresses of the same segments
 };
 __device__ __forceinline__ Smem carve(unsigned char* raw, const ScoreConfig& c, const IterParams& P, int T) {
   Smem s;
   s.keys = reinterpret_cast<unsigned long long*>(raw);
-  float* sm = reinterpret_cast<float*>(raw) + (P.coop ? 0 : 2 * P.n_pad);
-  const int CT = P.cand_per_cta, wc = P.w_col | 1, wa = P.w_arc | 1;
-  s.psi_col = sm;   sm += c.Mc * wc;
-  s.psi_arc = sm;   sm += c.arc_same ? 0 : c.Ma * wa;
-  s.first_col = reinterpret_cast<int*>(sm); sm += c.Mc;
-  s.first_arc = reinterpret_cast<int*>(sm); sm += c.arc_same ? 0 : c.Ma;
-  s.X = sm;         sm += CT * c.K * c.D;
+  float* const sm0 = reinterpret_cast<float*>(raw);
+  float* sm = sm0 + (P.coop ? 0 : 2 * P.n_pad);
+  const int CT = P.cand_per_cta, wc = row_pitch(P.w_col), wa = row_pitch(P.w_arc), dp = up4(c.D);
+  s.psi_col = sm;   sm += up4(c.Mc * wc);
+  s.psi_arc = sm;   sm += c.arc_same ? 0 : up4(c.Ma * wa);
+  s.first_col = reinterpret_cast<int*>(sm); sm += up4(c.Mc);
+  s.first_arc = reinterpret_cast<int*>(sm); sm += c.arc_same ? 0 : up4(c.Ma);
+  s.X = sm;         sm += CT * c.K * dp;
   s.cc = sm;        sm += CT * c.Mc;     // collision cost per point
   s.cw = sm;        sm += CT * c.Mc;     // collision cost + penalty per point
   s.seg = sm;       sm += CT * P.mq;     // segment lengths
   s.qs = sm;        sm += c.D * T;       // coordinates of the point in flight
   s.xf = sm;                              // link frames (only when !chain)
+  const unsigned a0 = (unsigned)__cvta_generic_to_shared(raw);
+  s.a_psi_col = a0 + (unsigned)((s.psi_col - sm0) * 4); s.a_psi_arc = a0 + (unsigned)((s.psi_arc - sm0) * 4);
+  s.a_X = a0 + (unsigned)((s.X - sm0) * 4);
   return s;
 }
 // Scene tables staged at the front of dynamic shared memory (they stay there for the whole launch): every
@@ -145,13 +154,45 @@ __device__ __forceinline__ SmemModel stage_model(const ModelView& G, int tid, in
 }
 
 __device__ __forceinline__ void load_basis(const Smem& s, const ScoreConfig& c, const IterParams& P, int tid, int T) {
-  const int wc = P.w_col | 1, wa = P.w_arc | 1;
-  for (int e = tid; e < c.Mc * P.w_col; e += T) s.psi_col[(e / P.w_col) * wc + (e % P.w_col)] = P.psi_col[e];
+  const int wc = row_pitch(P.w_col), wa = row_pitch(P.w_arc);
+  for (int e = tid; e < c.Mc * wc; e += T) { const int r = e / wc, k = e - r * wc; s.psi_col[e] = (k < P.w_col) ? P.psi_col[r * P.w_col + k] : 0.0f; }
   for (int e = tid; e < c.Mc; e += T) s.first_col[e] = P.first_col[e];
   if (!c.arc_same) {
-    for (int e = tid; e < c.Ma * P.w_arc; e += T) s.psi_arc[(e / P.w_arc) * wa + (e % P.w_arc)] = P.psi_arc[e];
+    for (int e = tid; e < c.Ma * wa; e += T) { const int r = e / wa, k = e - r * wa; s.psi_arc[e] = (k < P.w_arc) ? P.psi_arc[r * P.w_arc + k] : 0.0f; }
     for (int e = tid; e < c.Ma; e += T) s.first_arc[e] = P.first_arc[e];
   }
+}
+
+// One spline point from 128-bit shared reads: q[d] = sum_k row[k] * X[first + k][d], k ascending from +0 — the
+// chain of ssppm::spline_coord, so the same bits.  W: band width (<= 4, row pitch 4); NV: 4-float words per
+// control-point row (pitch 4 NV, zero padded).
+template <int W, int NV>
+__device__ __forceinline__ void spline_point(unsigned a_rows, int m, int first, unsigned a_X, float* q) {
+  const uint4 rv = lds128(a_rows + (unsigned)m * 16u);
+  const float rc[4] = {__uint_as_float(rv.x), __uint_as_float(rv.y), __uint_as_float(rv.z), __uint_as_float(rv.w)};
+#pragma unroll
+  for (int d = 0; d < 4 * NV; ++d) q[d] = 0.0f;
+#pragma unroll
+  for (int k = 0; k < W; ++k)
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      const uint4 x = lds128(a_X + (unsigned)((first + k) * NV + v) * 16u);
+      q[4 * v + 0] = fmaf(rc[k], __uint_as_float(x.x), q[4 * v + 0]);
+      q[4 * v + 1] = fmaf(rc[k], __uint_as_float(x.y), q[4 * v + 1]);
+      q[4 * v + 2] = fmaf(rc[k], __uint_as_float(x.z), q[4 * v + 2]);
+      q[4 * v + 3] = fmaf(rc[k], __uint_as_float(x.w), q[4 * v + 3]);
+    }
+}
+// dispatch on the (band width, row words) of the problem; false: shape not covered, use the generic loop
+__device__ __forceinline__ bool spline_point_any(int W, int NV, unsigned a_rows, int m, int first, unsigned a_X, float* q) {
+  if (NV == 2) {
+    if (W == 4) { spline_point<4, 2>(a_rows, m, first, a_X, q); return true; }
+    if (W == 3) { spline_point<3, 2>(a_rows, m, first, a_X, q); return true; }
+  } else if (NV == 1) {
+    if (W == 3) { spline_point<3, 1>(a_rows, m, first, a_X, q); return true; }
+    if (W == 4) { spline_point<4, 1>(a_rows, m, first, a_X, q); return true; }
+  }
+  return false;
 }
 
 // Phase A for one tile: candidates [c0, c0 + nc) of `query`.  Ends with the per-candidate outputs
@@ -163,7 +204,9 @@ __device__ __forceinline__ void score_tile(const SmemModel& M, const IterParams&
   const int D = c.D, K = c.K, Mc = c.Mc, Ma = c.Ma, Mq = P.mq;
   const int nfd = c.n_free * D;
   const int Marc = c.arc_same ? Mc : Ma;
-  const int wc = P.w_col | 1, wa = P.w_arc | 1;
+  const int wc = row_pitch(P.w_col), wa = row_pitch(P.w_arc), dp = up4(D), NV = dp >> 2;
+  const bool fast_col = NV <= 2 && (P.w_col == 3 || P.w_col == 4);   // shapes spline_point_any covers
+  const bool fast_arc = NV <= 2 && (P.w_arc == 3 || P.w_arc == 4);
   const float* mean = P.mean + (size_t)query * nfd;
   const float* sigma = P.sigma + (size_t)query * nfd;
   const float* best = P.best + (size_t)query * nfd;
@@ -172,34 +215,47 @@ __device__ __forceinline__ void score_tile(const SmemModel& M, const IterParams&
   SmemXF xf{s.xf, T, tid};
   SmemQ qa{s.qs, T, tid};
   const int best_ok = c.include_best ? P.best_valid[query] : 0;
-  // ---- K1: candidate point matrices ----
-  for (int e = tid; e < nc * K * D; e += T) s.X[e] = base[e % (K * D)];
+  // ---- K1: candidate point matrices (rows padded to dp floats with zeros) ----
+  for (int e = tid; e < nc * K * dp; e += T) { const int r = e / dp, d = e - r * dp; s.X[e] = (d < D) ? base[(r % K) * D + d] : 0.0f; }
   __syncthreads();
   for (int e = tid; e < nc * nfd; e += T) {
     const int cl = e / nfd, t = e - cl * nfd;
     const int cand = c0 + cl, gcand = P.cand_offset + cand;
     const int kind = candidate_kind(c, gcand, best_ok);
     const float v = candidate_param(c, P.seed, iter, (uint32_t)query, gcand, kind, t, mean, sigma, best);
-    s.X[(cl * K + c.free_begin) * D + t] = v;
+    const int fr = t / D;
+    s.X[(cl * K + c.free_begin + fr) * dp + (t - fr * D)] = v;
     P.params[(qn + cand) * nfd + t] = v;
   }
   __syncthreads();
   // ---- K2-K4: spline point, kinematics, collision per (candidate, point) item ----
-  // Segment lengths (K5) are formed by the thread that owns the segment's end point, which evaluates
-  // the start point a second time instead of reading it from a staging buffer (a banded row is <= 4 FMA
-  // per coordinate): no per-point buffer, and the same bits as any other evaluation of that point.
+  // When the arc-length grid is the collision grid (arc_same) the thread that owns a segment's end point
+  // evaluates the start point a second time instead of reading it from a staging buffer: no per-point buffer,
+  // and the same bits as any other evaluation of that point.
   for (int w = tid; w < nc * Mc; w += T) {
     const int cl = w / Mc, m = w - cl * Mc;
-    const float* row = s.psi_col + m * wc;
     const int first = s.first_col[m];
-    const float* X = s.X + cl * K * D;
     float s2 = 0.0f;
-    for (int d = 0; d < D; ++d) {
-      const float acc = spline_coord(row, first, P.w_col, X, D, d);
-      s.qs[d * T + tid] = acc;
+    float q[8];
+    if (fast_col && spline_point_any(P.w_col, NV, s.a_psi_col, m, first, s.a_X + (unsigned)(cl * K * dp) * 4u, q)) {
+#pragma unroll
+      for (int d = 0; d < 8; ++d) if (d < D) s.qs[d * T + tid] = q[d];
       if (c.arc_same && m > 0) {
-        const float df = acc - spline_coord(row - wc, s.first_col[m - 1], P.w_col, X, D, d);
-        s2 = fmaf(df, df, s2);
+        float q0[8];
+        spline_point_any(P.w_col, NV, s.a_psi_col, m - 1, s.first_col[m - 1], s.a_X + (unsigned)(cl * K * dp) * 4u, q0);
+#pragma unroll
+        for (int d = 0; d < 8; ++d) if (d < D) { const float df = q[d] - q0[d]; s2 = fmaf(df, df, s2); }
+      }
+    } else {
+      const float* row = s.psi_col + m * wc;
+      const float* X = s.X + cl * K * dp;
+      for (int d = 0; d < D; ++d) {
+        const float acc = spline_coord(row, first, P.w_col, X, dp, d);
+        s.qs[d * T + tid] = acc;
+        if (c.arc_same && m > 0) {
+          const float df = acc - spline_coord(row - wc, s.first_col[m - 1], P.w_col, X, dp, d);
+          s2 = fmaf(df, df, s2);
+        }
       }
     }
     if (c.arc_same && m > 0) s.seg[cl * Mq + m - 1] = sqrtf(s2);
@@ -212,17 +268,37 @@ __device__ __forceinline__ void score_tile(const SmemModel& M, const IterParams&
     s.cw[cl * Mc + m] = cw;
   }
   if (!c.arc_same) {
-    for (int w = tid; w < nc * (Ma - 1); w += T) {
-      const int cl = w / (Ma - 1), m = 1 + (w - cl * (Ma - 1));
-      const float* row = s.psi_arc + m * wa;
-      const float* X = s.X + cl * K * D;
-      const int f1 = s.first_arc[m], f0 = s.first_arc[m - 1];
-      float s2 = 0.0f;
-      for (int d = 0; d < D; ++d) {
-        const float df = spline_coord(row, f1, P.w_arc, X, D, d) - spline_coord(row - wa, f0, P.w_arc, X, D, d);
-        s2 = fmaf(df, df, s2);
+    if (fast_arc) {
+      // arc-length grid: a warp round takes 32 consecutive points of the flattened (candidate, arc point) list and
+      // advances by 31, so every lane but 0 finds the start point of its segment in the lane below (shuffle): each
+      // point is evaluated once
+      const int total = nc * Ma;
+      for (int pb = warp * 31; pb < total - 1; pb += nwarp * 31) {
+        const int pt = min(pb + lane, total - 1);
+        const int cl = pt / Ma, m = pt - cl * Ma;
+        float q[8];
+        spline_point_any(P.w_arc, NV, s.a_psi_arc, m, s.first_arc[m], s.a_X + (unsigned)(cl * K * dp) * 4u, q);
+        float s2 = 0.0f;
+#pragma unroll
+        for (int d = 0; d < 8; ++d) {
+          const float prev = __shfl_up_sync(0xFFFFFFFFu, q[d], 1);
+          if (d < D) { const float df = q[d] - prev; s2 = fmaf(df, df, s2); }
+        }
+        if (lane > 0 && pb + lane < total && m > 0) s.seg[cl * Mq + m - 1] = sqrtf(s2);
       }
-      s.seg[cl * Mq + m - 1] = sqrtf(s2);
+    } else {
+      for (int w = tid; w < nc * (Ma - 1); w += T) {
+        const int cl = w / (Ma - 1), m = 1 + (w - cl * (Ma - 1));
+        const float* row = s.psi_arc + m * wa;
+        const float* X = s.X + cl * K * dp;
+        const int f1 = s.first_arc[m], f0 = s.first_arc[m - 1];
+        float s2 = 0.0f;
+        for (int d = 0; d < D; ++d) {
+          const float df = spline_coord(row, f1, P.w_arc, X, dp, d) - spline_coord(row - wa, f0, P.w_arc, X, dp, d);
+          s2 = fmaf(df, df, s2);
+        }
+        s.seg[cl * Mq + m - 1] = sqrtf(s2);
+      }
     }
   }
   __syncthreads();
@@ -725,9 +801,9 @@ size_t model_smem_bytes(const ssppm::DevModelHead& M) {
 
 size_t iterate_smem_bytes(const ssppm::DevModelHead& M, const IterParams& P, int threads) {
   const ScoreConfig& c = P.cfg;
-  const int wc = P.w_col | 1, wa = P.w_arc | 1;
-  size_t f = (size_t)c.Mc * (wc + 1) + (c.arc_same ? 0 : (size_t)c.Ma * (wa + 1));
-  f += (size_t)P.cand_per_cta * c.K * c.D;
+  const int wc = row_pitch(P.w_col), wa = row_pitch(P.w_arc), dp = up4(c.D);
+  size_t f = (size_t)up4(c.Mc * wc) + up4(c.Mc) + (c.arc_same ? 0 : (size_t)up4(c.Ma * wa) + up4(c.Ma));
+  f += (size_t)P.cand_per_cta * c.K * dp;
   f += (size_t)P.cand_per_cta * c.Mc * 2;
   f += (size_t)P.cand_per_cta * P.mq;
   f += (size_t)c.D * threads;

@@ -2,6 +2,7 @@
 #include "sspp_model.h"
 
 #include <algorithm>
+#include <array>
 #include <cmath>
 #include <cstring>
 #include <fstream>
@@ -577,7 +578,48 @@ ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const 
     sgeom_src.push_back(g);
     return sg_of[g] = D.n_sgeom++;
   };
-  int n_static_pairs = 0;
+  // Workspace bound of every moving body: its frame origin stays within reach[b] of the world point centre[b]
+  // whatever the planned coordinates are (hinges turn about their own anchor, slides move by at most their
+  // range, a free body is unbounded).  A pair whose static partner lies beyond that bound can never generate a
+  // contact and is dropped here, once, instead of being culled per collocation point.
+  const double kInf = 1e30;
+  std::vector<double> reach(D.n_mbody, kInf);
+  std::vector<std::array<double, 3>> centre(D.n_mbody, std::array<double, 3>{0, 0, 0});
+  for (int mb = 0; mb < D.n_mbody; ++mb) {
+    const DevBody& B = D.body[mb];
+    const double plen = std::sqrt((double)B.pos[0] * B.pos[0] + (double)B.pos[1] * B.pos[1] + (double)B.pos[2] * B.pos[2]);
+    const double alen = std::sqrt((double)B.anchor[0] * B.anchor[0] + (double)B.anchor[1] * B.anchor[1] + (double)B.anchor[2] * B.anchor[2]);
+    double own = kInf;
+    if (B.jtype == JT_HINGE) own = 2.0 * alen;
+    else if (B.jtype == JT_SLIDE) {
+      int src = -1;
+      for (int b = 1; b < m.nbody; ++b) if (mb_of[b] == mb) src = b;
+      const double lo = m.jnt_range[2 * src], hi = m.jnt_range[2 * src + 1];
+      if (lo < hi) own = std::max(std::fabs(lo), std::fabs(hi));
+    }
+    if (B.parent < 0) { centre[mb] = {B.pos[0], B.pos[1], B.pos[2]}; reach[mb] = own; }
+    else { centre[mb] = centre[B.parent]; reach[mb] = std::min(kInf, reach[B.parent] + plen + own); }
+  }
+  auto unreachable = [&](int ig, int h) {     // moving geom ig can never come within the margin of model geom h
+    if (opt.sdf) return false;                // the grid needs the same static set for every moving geom
+    const DevMGeom& G = D.mg[ig];
+    const double r = reach[G.body];
+    if (r >= kInf) return false;
+    const double glen = std::sqrt((double)G.pos[0] * G.pos[0] + (double)G.pos[1] * G.pos[1] + (double)G.pos[2] * G.pos[2]);
+    const int hb = m.geom_body[h];
+    double Rg[9], Rw[9], pw[3];
+    quat_to_mat(&m.geom_quat[4 * h], Rg);
+    mat_mul(xw[hb].R, Rg, Rw);
+    mat_vec(xw[hb].R, &m.geom_pos[3 * h], pw);
+    for (int k = 0; k < 3; ++k) pw[k] += xw[hb].p[k];
+    const double margin = std::max(0.0, std::max(m.geom_margin[mgeom_src[ig]], m.geom_margin[h]));
+    const double need = r + glen + G.rbound + margin + 2e-3;      // 2 mm of slack over every FP32 rounding in the kernel
+    const double dx = centre[G.body][0] - pw[0], dy = centre[G.body][1] - pw[1], dz = centre[G.body][2] - pw[2];
+    if (m.geom_type[h] == GT_PLANE) return Rw[2] * dx + Rw[5] * dy + Rw[8] * dz > need;
+    const double rb = bound_radius(m.geom_type[h], &m.geom_size[3 * h]);
+    return rb >= 0 && std::sqrt(dx * dx + dy * dy + dz * dz) > need + rb;
+  };
+  int n_static_pairs = 0, n_unreachable = 0;
   for (int ig = 0; ig < D.n_mgeom; ++ig) {
     const int g = mgeom_src[ig];
     D.mg[ig].pair_begin = D.n_pair;
@@ -586,6 +628,7 @@ ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const 
       if (!pair_active(m, std::min(g, h), std::max(g, h))) continue;
       if (!pair_supported(m.geom_type[g], m.geom_type[h]))
         throw std::runtime_error("collision between geoms '" + m.geom_name[g] + "' and '" + m.geom_name[h] + "' is of an unsupported type pairing");
+      if (unreachable(ig, h)) { ++n_unreachable; continue; }
       if (D.n_pair >= MAX_PAIR) throw std::runtime_error("too many geom pairs");
       D.pair[D.n_pair].s = static_geom(h);
       D.pair[D.n_pair].margin = (float)std::max(m.geom_margin[g], m.geom_margin[h]);
@@ -626,31 +669,39 @@ ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const 
     }
   // a moving geom carries at most MAX_GEOM_PAIRS pair records (one mask word in the kernel's broad phase): geoms
   // with more partners are emitted again with the next slice of their pairs
-  bool oversize = false;
-  for (int ig = 0; ig < D.n_mgeom; ++ig) if (D.mg[ig].pair_end - D.mg[ig].pair_begin > MAX_GEOM_PAIRS) oversize = true;
-  if (oversize && !opt.sdf) {
-    std::vector<DevMGeom> out;
-    std::vector<int> src_out, first_of(D.n_mgeom, 0);
-    for (int mb = 0; mb < D.n_mbody; ++mb) {
-      const int gb = D.body[mb].geom_begin, ge = D.body[mb].geom_end;
-      D.body[mb].geom_begin = (int)out.size();
-      for (int ig = gb; ig < ge; ++ig) {
-        first_of[ig] = (int)out.size();
-        const DevMGeom& G = D.mg[ig];
-        for (int k = G.pair_begin; k < G.pair_end || k == G.pair_begin; k += MAX_GEOM_PAIRS) {
-          DevMGeom c = G;
-          c.pair_begin = k; c.pair_end = std::min(k + (int)MAX_GEOM_PAIRS, G.pair_end);
-          c.pair_mid = std::min(std::max(G.pair_mid, c.pair_begin), c.pair_end);
-          out.push_back(c); src_out.push_back(mgeom_src[ig]);
-        }
-      }
-      D.body[mb].geom_end = (int)out.size();
+  {
+    std::vector<char> in_mm(D.n_mgeom, 0);
+    for (int k = 0; k < D.n_mmpair; ++k) in_mm[D.mm[k].a] = in_mm[D.mm[k].b] = 1;
+    bool rebuild = false;
+    for (int ig = 0; ig < D.n_mgeom; ++ig) {
+      const int np = D.mg[ig].pair_end - D.mg[ig].pair_begin;
+      if (np > MAX_GEOM_PAIRS || (np == 0 && !in_mm[ig])) rebuild = true;
     }
-    if ((int)out.size() > MAX_MGEOM) throw std::runtime_error("too many moving geoms after splitting their pair lists");
-    for (int k = 0; k < D.n_mmpair; ++k) { D.mm[k].a = first_of[D.mm[k].a]; D.mm[k].b = first_of[D.mm[k].b]; }
-    std::copy(out.begin(), out.end(), D.mg);
-    D.n_mgeom = (int)out.size();
-    mgeom_src = src_out;
+    if (rebuild && !opt.sdf) {
+      std::vector<DevMGeom> out;
+      std::vector<int> src_out, first_of(D.n_mgeom, 0);
+      for (int mb = 0; mb < D.n_mbody; ++mb) {
+        const int gb = D.body[mb].geom_begin, ge = D.body[mb].geom_end;
+        D.body[mb].geom_begin = (int)out.size();
+        for (int ig = gb; ig < ge; ++ig) {
+          first_of[ig] = (int)out.size();
+          const DevMGeom& G = D.mg[ig];
+          if (G.pair_end == G.pair_begin && !in_mm[ig]) continue;      // every partner is out of reach
+          for (int k = G.pair_begin; k < G.pair_end || k == G.pair_begin; k += MAX_GEOM_PAIRS) {
+            DevMGeom c = G;
+            c.pair_begin = k; c.pair_end = std::min(k + (int)MAX_GEOM_PAIRS, G.pair_end);
+            c.pair_mid = std::min(std::max(G.pair_mid, c.pair_begin), c.pair_end);
+            out.push_back(c); src_out.push_back(mgeom_src[ig]);
+          }
+        }
+        D.body[mb].geom_end = (int)out.size();
+      }
+      if ((int)out.size() > MAX_MGEOM) throw std::runtime_error("too many moving geoms after splitting their pair lists");
+      for (int k = 0; k < D.n_mmpair; ++k) { D.mm[k].a = first_of[D.mm[k].a]; D.mm[k].b = first_of[D.mm[k].b]; }
+      std::copy(out.begin(), out.end(), D.mg);
+      D.n_mgeom = (int)out.size();
+      mgeom_src = src_out;
+    }
   }
   if (opt.sdf) {
     // The grid is the union of the static partners; it cannot express a per-geom collision mask, so every
@@ -718,6 +769,7 @@ ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const 
   if (info) {
     info->n_static_pairs = n_static_pairs;
     info->n_active_pairs = D.n_pair;
+    info->n_unreachable_pairs = n_unreachable;
     info->mgeom_src = mgeom_src;
     info->sgeom_src = sgeom_src;
   }

@@ -43,6 +43,7 @@ enum PlanMode { PLAN_JOINT = 0,   // planner A: q = first `dof` scalar coordinat
 struct CompileInfo {
   int n_static_pairs = 0;     // pairs between geoms that never move (folded into static_cost)
   int n_active_pairs = 0;     // moving-vs-static pairs
+  int n_unreachable_pairs = 0; // moving-vs-static pairs dropped because the workspace bound proves them contact-free
   std::vector<int> mgeom_src, sgeom_src;   // FlatModel geom ids behind DevModel::mg / ::sg
 };
 
