@@ -33,7 +33,13 @@ hint = int(os.environ.get("SSPP_TILE_HINT", "0"), 0)
 case = joint_case(n_samples=4096, check_points=64, do_update=True); case.cfg.tile_hint = hint
 h = capi.Handle(case.model, case.cfg); case.prepare(h)
 out["cfg2_us"] = round(t_us(h, 1, 200), 1); out["cfg2_gpts"] = round(4096 * 64 / out["cfg2_us"] * 1e-3, 3)
-r = h.results(); out["cfg2_succ"] = int(r["n_success"][0]); h.close()
+r = h.results(); out["cfg2_succ"] = int(r["n_success"][0])
+import time
+for i in range(5): case.prepare(h); h.iterate(SEED, i, 1); h.results(); h.best()
+t0 = time.perf_counter()
+for i in range(200): case.prepare(h); h.iterate(SEED, 10 + i, 1); r = h.results(); b = h.best()
+out["cfg2_e2e_us"] = round((time.perf_counter() - t0) / 200 * 1e6, 1); out["cfg2_e2e_succ"] = int(r["n_success"][0])
+h.close()
 Q = 1024; rng = np.random.default_rng(1000)
 s = np.column_stack([rng.uniform(0.2, 0.6, Q), rng.uniform(-0.4, 0.4, Q), rng.uniform(0.14, 0.4, Q), rng.uniform(-1.5, 1.5, Q)])
 e = np.column_stack([rng.uniform(0.2, 0.6, Q), rng.uniform(-0.4, 0.4, Q), rng.uniform(0.14, 0.4, Q), rng.uniform(-1.5, 1.5, Q)])

@@ -7,7 +7,7 @@ import numpy as np, torch
 from sspp_b200 import capi
 from tests.helpers import joint_case, task_case, SEED
 
-VARIANTS = [(256, 2), (256, 3), (320, 2), (320, 3), (448, 2), (384, 2), (128, 6), (192, 5)]
+VARIANTS = [(256, 2), (256, 3), (320, 2), (320, 3), (448, 2), (384, 2), (128, 7), (192, 5)]
 which = sys.argv[1] if len(sys.argv) > 1 else "cfg2"
 
 def hint(variant, cpc, threads): return (variant + 1) | (cpc << 8) | (threads << 20)

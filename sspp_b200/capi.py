@@ -360,10 +360,10 @@ class Handle:
     def results(self) -> dict:
         d = self.dims
         Q, N = d.n_queries, d.n_cand
-        out = dict(L=np.zeros((Q, N), np.float32), Cnf=np.zeros((Q, N), np.float32), Cwf=np.zeros((Q, N), np.float32),
-                   cost=np.zeros((Q, N), np.float32), status=np.zeros((Q, N), np.uint8),
-                   n_success=np.zeros(Q, np.int32), n_elite=np.zeros(Q, np.int32), best_idx=np.zeros(Q, np.int32),
-                   best_cost=np.zeros(Q, np.float32), any_success=np.zeros(Q, np.int32))
+        out = dict(L=np.empty((Q, N), np.float32), Cnf=np.empty((Q, N), np.float32), Cwf=np.empty((Q, N), np.float32),
+                   cost=np.empty((Q, N), np.float32), status=np.empty((Q, N), np.uint8),
+                   n_success=np.empty(Q, np.int32), n_elite=np.empty(Q, np.int32), best_idx=np.empty(Q, np.int32),
+                   best_cost=np.empty(Q, np.float32), any_success=np.empty(Q, np.int32))
         self._ck(lib.ssppcu_get_results(self._h, *[_ptr(out[k]) for k in (
             "L", "Cnf", "Cwf", "cost", "status", "n_success", "n_elite", "best_idx", "best_cost", "any_success")]))
         return out

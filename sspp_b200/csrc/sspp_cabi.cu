@@ -47,6 +47,11 @@ struct ssppcu_planner {
   float* d_state = nullptr;      // snapshot of d_live
   size_t state_words = 0; bool state_saved = false;
   unsigned long long* d_probe = nullptr;   // phase probe stamps [grid][6], allocated on demand
+  // host transfers: every per-candidate / per-query result lives in ONE device block mirrored by a pinned host
+  // block (one D2H copy per read-back), and host inputs go through a pinned staging ring (asynchronous H2D)
+  unsigned char* d_res = nullptr; unsigned char* h_res = nullptr; size_t res_bytes = 0;
+  size_t o_L = 0, o_Cnf = 0, o_Cwf = 0, o_cost = 0, o_status = 0, o_nsucc = 0, o_nelite = 0, o_bidx = 0, o_bcost = 0, o_extra = 0;
+  unsigned char* h_stage = nullptr; size_t stage_bytes = 0, stage_at = 0;
 };
 
 namespace {
@@ -185,6 +190,9 @@ void ssppcu_destroy(ssppcu_t* h) {
   if (h->d_eval_out) cudaFree(h->d_eval_out);
   if (h->d_merge_keys) cudaFree(h->d_merge_keys);
   if (h->d_probe) cudaFree(h->d_probe);
+  if (h->d_res) cudaFree(h->d_res);
+  if (h->h_res) cudaFreeHost(h->h_res);
+  if (h->h_stage) cudaFreeHost(h->h_stage);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
 }
@@ -306,7 +314,8 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
   }
   h->variant = hint_variant >= 0 ? hint_variant : 0;
   const bool auto_shape = hint_variant < 0 && !hint_threads;
-  h->threads = ((long)s.n_cand * s.Mc <= 1024) ? 128 : 256;
+  h->threads = ((long)s.n_cand * s.Mc <= 512) ? 128 : 256;
+  if (auto_shape && h->threads == 256) h->variant = 1;   // one CTA per query: 3 x 256 threads per SM at <= 80 registers (measured, profiles/)
   if (hint_threads) h->threads = hint_threads;
   if (h->threads > kIterVariants[h->variant].max_threads) { set_err(err, errlen, "tile_hint: threads exceed the variant's launch bound"); delete h; return SSPPCU_EINVAL; }
   P.coop = 0; P.cand_per_cta = s.n_cand; P.ctas_per_query = 1;
@@ -377,12 +386,31 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
     P.best_valid = reinterpret_cast<int*>(P.best + Q * nfd); P.any_success = P.best_valid + Q;
   }
   rc |= dalloc(h, &P.params, Q * N * nfd);
-  rc |= dalloc(h, &P.L, Q * N); rc |= dalloc(h, &P.Cnf, Q * N); rc |= dalloc(h, &P.Cwf, Q * N); rc |= dalloc(h, &P.cost, Q * N);
-  rc |= dalloc(h, &P.status, Q * N);
   rc |= dalloc(h, &P.keys, Q * P.n_pad); rc |= dalloc(h, &P.keys_raw, Q * P.n_pad); rc |= dalloc(h, &P.elite_w, Q * P.n_pad);
   rc |= dalloc(h, &P.succ_acc, Q);
-  rc |= dalloc(h, &P.n_success, Q); rc |= dalloc(h, &P.n_elite, Q); rc |= dalloc(h, &P.best_idx, Q);
-  rc |= dalloc(h, &P.best_cost, Q);
+  {
+    size_t off = 0;
+    auto take = [&](size_t bytes) { const size_t o = off; off += (bytes + 15) & ~(size_t)15; return o; };
+    h->o_L = take(Q * N * 4); h->o_Cnf = take(Q * N * 4); h->o_Cwf = take(Q * N * 4); h->o_cost = take(Q * N * 4);
+    h->o_status = take(Q * N); h->o_nsucc = take(Q * 4); h->o_nelite = take(Q * 4); h->o_bidx = take(Q * 4); h->o_bcost = take(Q * 4);
+    h->res_bytes = off;
+    h->o_extra = take(Q * nfd * 4 + 2 * Q * 4);    // host mirror only: best | best_valid | any_success (they live in the state block)
+    if (!rc) {
+      cudaError_t e1 = cudaMalloc(&h->d_res, h->res_bytes);
+      if (e1 == cudaSuccess) e1 = cudaMemset(h->d_res, 0, h->res_bytes);
+      if (e1 == cudaSuccess) e1 = cudaMallocHost(&h->h_res, off);
+      h->stage_bytes = std::max<size_t>(64 * 1024, 4 * (Q * s.K * s.D + 2 * Q * nfd) * sizeof(float));
+      if (e1 == cudaSuccess) e1 = cudaMallocHost(&h->h_stage, h->stage_bytes);
+      if (e1 != cudaSuccess) rc |= cuda_fail(h, e1, "result / staging blocks");
+      else {
+        P.L = reinterpret_cast<float*>(h->d_res + h->o_L); P.Cnf = reinterpret_cast<float*>(h->d_res + h->o_Cnf);
+        P.Cwf = reinterpret_cast<float*>(h->d_res + h->o_Cwf); P.cost = reinterpret_cast<float*>(h->d_res + h->o_cost);
+        P.status = h->d_res + h->o_status;
+        P.n_success = reinterpret_cast<int*>(h->d_res + h->o_nsucc); P.n_elite = reinterpret_cast<int*>(h->d_res + h->o_nelite);
+        P.best_idx = reinterpret_cast<int*>(h->d_res + h->o_bidx); P.best_cost = reinterpret_cast<float*>(h->d_res + h->o_bcost);
+      }
+    }
+  }
   if (rc) { set_err(err, errlen, h->err); ssppcu_destroy(h); return SSPPCU_ECUDA; }
   P.psi_col = d_psi_col; P.psi_arc = d_psi_arc; P.base = d_base; P.first_col = d_first_col; P.first_arc = d_first_arc;
   ce = cudaMemcpy(d_psi_col, band_col.data(), band_col.size() * sizeof(float), cudaMemcpyHostToDevice);
@@ -446,12 +474,28 @@ int d2h(ssppcu_t* h, T* dst, const T* src, size_t n) {
   if (e != cudaSuccess) return cuda_fail(h, e, "cudaMemcpyAsync D2H");
   return 0;
 }
+// host -> device through the pinned staging ring: asynchronous on the handle's stream; the ring is drained
+// (one stream synchronisation) only when it wraps
 template <class T>
 int h2d(ssppcu_t* h, T* dst, const T* src, size_t n) {
-  cudaError_t e = cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyHostToDevice, h->stream);
+  const size_t bytes = n * sizeof(T);
+  if (bytes == 0) return 0;
+  if (bytes > h->stage_bytes) {                       // larger than the ring: plain synchronous copy
+    cudaError_t e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    if (e != cudaSuccess) return cuda_fail(h, e, "cudaMemcpyAsync H2D");
+    return 0;
+  }
+  if (h->stage_at + bytes > h->stage_bytes) {
+    cudaError_t e = cudaStreamSynchronize(h->stream);
+    if (e != cudaSuccess) return cuda_fail(h, e, "cudaStreamSynchronize");
+    h->stage_at = 0;
+  }
+  unsigned char* slot = h->h_stage + h->stage_at;
+  std::memcpy(slot, src, bytes);
+  h->stage_at += (bytes + 15) & ~(size_t)15;
+  cudaError_t e = cudaMemcpyAsync(dst, slot, bytes, cudaMemcpyHostToDevice, h->stream);
   if (e != cudaSuccess) return cuda_fail(h, e, "cudaMemcpyAsync H2D");
-  e = cudaStreamSynchronize(h->stream);   // the source is a host temporary
-  if (e != cudaSuccess) return cuda_fail(h, e, "cudaStreamSynchronize");
   return 0;
 }
 
@@ -474,6 +518,7 @@ int ssppcu_dims(const ssppcu_t* h, SsppDims* o) {
 
 int ssppcu_set_stream(ssppcu_t* h, void* s) {
   if (!h) return SSPPCU_EINVAL;
+  if (h->stage_at) { cudaSetDevice(h->cfg.device); cudaStreamSynchronize(h->stream); h->stage_at = 0; }   // staged copies of the old stream
   h->stream = s ? static_cast<cudaStream_t>(s) : h->own_stream;
   return SSPPCU_OK;
 }
@@ -638,14 +683,23 @@ int ssppcu_get_results(ssppcu_t* h, float* L, float* Cnf, float* Cwf, float* cos
                        int32_t* n_elite, int32_t* best_idx, float* best_cost, int32_t* any_success) {
   if (int rc = check(h)) return rc;
   const size_t Q = h->P.n_query, QN = Q * h->P.cfg.n_cand;
-  int rc = 0;
-  rc |= d2h(h, L, h->P.L, QN); rc |= d2h(h, Cnf, h->P.Cnf, QN); rc |= d2h(h, Cwf, h->P.Cwf, QN);
-  rc |= d2h(h, cost, h->P.cost, QN); rc |= d2h(h, status, h->P.status, QN);
-  rc |= d2h(h, n_success, h->P.n_success, Q); rc |= d2h(h, n_elite, h->P.n_elite, Q);
-  rc |= d2h(h, best_idx, h->P.best_idx, Q); rc |= d2h(h, best_cost, h->P.best_cost, Q);
-  rc |= d2h(h, any_success, h->P.any_success, Q);
-  if (rc) return SSPPCU_ECUDA;
+  // one copy of the result block into its pinned mirror (per-candidate arrays only when somebody wants them)
+  const bool per_cand = L || Cnf || Cwf || cost || status;
+  const size_t from = per_cand ? 0 : h->o_nsucc;
+  CU(h, cudaMemcpyAsync(h->h_res + from, h->d_res + from, h->res_bytes - from, cudaMemcpyDeviceToHost, h->stream));
+  int32_t* h_any = reinterpret_cast<int32_t*>(h->h_res + h->o_extra);
+  if (any_success) CU(h, cudaMemcpyAsync(h_any, h->P.any_success, Q * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
   CU(h, cudaStreamSynchronize(h->stream));
+  if (L) std::memcpy(L, h->h_res + h->o_L, QN * 4);
+  if (Cnf) std::memcpy(Cnf, h->h_res + h->o_Cnf, QN * 4);
+  if (Cwf) std::memcpy(Cwf, h->h_res + h->o_Cwf, QN * 4);
+  if (cost) std::memcpy(cost, h->h_res + h->o_cost, QN * 4);
+  if (status) std::memcpy(status, h->h_res + h->o_status, QN);
+  if (n_success) std::memcpy(n_success, h->h_res + h->o_nsucc, Q * 4);
+  if (n_elite) std::memcpy(n_elite, h->h_res + h->o_nelite, Q * 4);
+  if (best_idx) std::memcpy(best_idx, h->h_res + h->o_bidx, Q * 4);
+  if (best_cost) std::memcpy(best_cost, h->h_res + h->o_bcost, Q * 4);
+  if (any_success) std::memcpy(any_success, h_any, Q * 4);
   return SSPPCU_OK;
 }
 
@@ -661,9 +715,11 @@ int ssppcu_get_params(ssppcu_t* h, float* params) {
 int ssppcu_get_best(ssppcu_t* h, float* best, int32_t* valid) {
   if (int rc = check(h)) return rc;
   const size_t Q = h->P.n_query, nfd = (size_t)h->P.cfg.n_free * h->P.cfg.D;
-  if (int rc = d2h(h, best, h->P.best, Q * nfd)) return rc;
-  if (int rc = d2h(h, valid, h->P.best_valid, Q)) return rc;
+  unsigned char* m = h->h_res + h->o_extra + Q * 4;          // after the any_success mirror
+  CU(h, cudaMemcpyAsync(m, h->P.best, Q * nfd * 4 + Q * 4, cudaMemcpyDeviceToHost, h->stream));   // best | best_valid
   CU(h, cudaStreamSynchronize(h->stream));
+  if (best) std::memcpy(best, m, Q * nfd * 4);
+  if (valid) std::memcpy(valid, m + Q * nfd * 4, Q * 4);
   return SSPPCU_OK;
 }
 

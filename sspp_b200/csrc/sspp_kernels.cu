@@ -823,7 +823,7 @@ const VariantFns kFns[kNumIterVariants] = {variant_fns<256, 2>(), variant_fns<25
                                            variant_fns<320, 2>(), variant_fns<320, 2>(), variant_fns<256, 2>(), variant_fns<256, 2>()};
 #else
 const VariantFns kFns[kNumIterVariants] = {variant_fns<256, 2>(), variant_fns<256, 3>(), variant_fns<320, 2>(), variant_fns<320, 3>(),
-                                           variant_fns<448, 2>(), variant_fns<384, 2>(), variant_fns<128, 6>(), variant_fns<192, 5>()};
+                                           variant_fns<448, 2>(), variant_fns<384, 2>(), variant_fns<128, 7>(), variant_fns<192, 5>()};
 #endif
 cudaError_t set_smem(IterKernel k, size_t smem_bytes) {   // per device / context, so no caching across calls
   if (smem_bytes <= 48 * 1024) return cudaSuccess;

@@ -54,7 +54,7 @@ size_t iterate_smem_bytes(const ssppm::DevModelHead& M, const IterParams& P, int
 // budget (65536 / (max_threads * min_ctas), rounded down to 8) and with it the resident warps per SM.
 struct IterVariant { int max_threads, min_ctas; };
 constexpr int kNumIterVariants = 8;
-constexpr IterVariant kIterVariants[kNumIterVariants] = {{256, 2}, {256, 3}, {320, 2}, {320, 3}, {448, 2}, {384, 2}, {128, 6}, {192, 5}};
+constexpr IterVariant kIterVariants[kNumIterVariants] = {{256, 2}, {256, 3}, {320, 2}, {320, 3}, {448, 2}, {384, 2}, {128, 7}, {192, 5}};
 
 // grid size: n_tiles CTAs (coop == 0) or `grid` co-resident CTAs looping over the tiles (coop == 1)
 cudaError_t launch_iterate(const ssppm::ModelView& M, const IterParams& P, int variant, int threads, size_t smem_bytes, int grid,
