@@ -158,10 +158,15 @@ int ssppcu_restore_state(ssppcu_t* h);
 
 /* n_iters fused iterations, asynchronous on the handle's stream; Philox counters (seed, iter0+i) */
 int ssppcu_iterate(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters);
+/* ssppcu_restore_state + ssppcu_iterate in ONE launch: the first iteration samples from the snapshot and re-arms
+ * the live state with it (a planner that is reset before every plan(), tsp_planner.h:54-69, needs no separate
+ * device-to-device copy) */
+int ssppcu_iterate_restored(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters);
 int ssppcu_sync(ssppcu_t* h);
 /* Diagnostics of the cooperative kernel: with enable != 0 every CTA stamps %globaltimer (ns) at the phase
- * boundaries of each launch's first iteration: start, scored, past grid barrier 1, ranked, past grid barrier 2,
- * updated.  stamps (may be NULL) receives [min(cap_ctas, grid)][6] values of the last launch.  Returns the grid
+ * boundaries of each launch's first iteration: [0] start, [1] scored, [2] past grid barrier 1, [3] ranked, [4] past
+ * grid barrier 2, [5] updated, [6] rank keys staged, [7] rank counted.  stamps (may be NULL) receives
+ * [min(cap_ctas, grid)][8] values of the last launch.  Returns the grid
  * size or a negative error. */
 int ssppcu_phase_probe(ssppcu_t* h, int enable, unsigned long long* stamps, int cap_ctas);
 

@@ -18,7 +18,7 @@ for r in range(20):
 A = np.stack(acc)                      # [rep][cta][6]
 t0 = A[:, :, 0].min(axis=1)[:, None, None]
 R = (A - t0) * 1e-3                    # us since the first CTA started
-names = ["start", "scored", "past_bar1", "ranked", "past_bar2", "updated"]
+names = ["start", "scored", "past_bar1", "ranked", "past_bar2", "updated", "rank_staged", "rank_counted"]
 out = {n: dict(min=round(float(R[:, :, i].min(axis=1).mean()), 1), med=round(float(np.median(R[:, :, i], axis=1).mean()), 1),
                max=round(float(R[:, :, i].max(axis=1).mean()), 1)) for i, n in enumerate(names)}
 print(json.dumps(dict(grid=int(A.shape[1]), phases_us=out)))

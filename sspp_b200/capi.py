@@ -90,7 +90,7 @@ SYMBOLS = [
     "ssppcu_get_params", "ssppcu_get_best", "ssppcu_get_elites", "ssppcu_device_view", "ssppcu_eval_points",
     "ssppcu_get_collocation", "ssppcu_get_base", "ssppcu_shard_keys", "ssppcu_merge_update", "ssppcu_version",
     "ssppcu_spline_setup", "ssppcu_collocation_matrix", "ssppcu_save_state", "ssppcu_restore_state",
-    "ssppcu_fp32_peak", "ssppcu_get_merged", "ssppcu_get_sdf", "ssppcu_get_spheres", "ssppcu_phase_probe",
+    "ssppcu_fp32_peak", "ssppcu_get_merged", "ssppcu_get_sdf", "ssppcu_get_spheres", "ssppcu_phase_probe", "ssppcu_iterate_restored",
 ]
 
 lib = _load()
@@ -121,6 +121,7 @@ lib.ssppcu_set_distribution.argtypes = [C.c_void_p, _dp, _dp]
 lib.ssppcu_get_distribution.argtypes = [C.c_void_p, _dp, _dp]
 lib.ssppcu_set_joint_noise.argtypes = [C.c_void_p, C.c_double, _dp]
 lib.ssppcu_iterate.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_int]
+lib.ssppcu_iterate_restored.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_int]
 lib.ssppcu_sync.argtypes = [C.c_void_p]
 lib.ssppcu_get_results.argtypes = [C.c_void_p] + [C.c_void_p] * 10
 lib.ssppcu_get_params.argtypes = [C.c_void_p, C.c_void_p]
@@ -332,22 +333,24 @@ class Handle:
         lim = np.ascontiguousarray(np.asarray(limits, np.float64).reshape(self.dims.dof))
         self._ck(lib.ssppcu_set_joint_noise(self._h, float(sigma), _dptr(lim)))
 
-    def iterate(self, seed: int, iter0: int = 0, n_iters: int = 1):
-        self._ck(lib.ssppcu_iterate(self._h, C.c_uint64(seed), C.c_uint32(iter0), int(n_iters)))
+    def iterate(self, seed: int, iter0: int = 0, n_iters: int = 1, restored: bool = False):
+        """n_iters fused iterations; restored=True: restore_state() folded into the same launch"""
+        fn = lib.ssppcu_iterate_restored if restored else lib.ssppcu_iterate
+        self._ck(fn(self._h, C.c_uint64(seed), C.c_uint32(iter0), int(n_iters)))
 
     def sync(self):
         self._ck(lib.ssppcu_sync(self._h))
 
     def phase_probe(self, enable: bool = True, read: bool = False):
-        """diagnostics of the cooperative kernel: per-CTA %globaltimer stamps [grid][6] of the last launch's first
-        iteration (start, scored, past barrier 1, ranked, past barrier 2, updated); None unless `read`"""
+        """diagnostics of the cooperative kernel: per-CTA %globaltimer stamps [grid][8] of the last launch's first
+        iteration (start, scored, past barrier 1, ranked, past barrier 2, updated, rank keys staged, rank counted); None unless `read`"""
         lib.ssppcu_phase_probe.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
         grid = lib.ssppcu_phase_probe(self._h, int(enable), None, 0)
         if grid < 0:
             self._ck(grid)
         if not read:
             return None
-        out = np.zeros((grid, 6), np.uint64)
+        out = np.zeros((grid, 8), np.uint64)
         self._ck(min(0, lib.ssppcu_phase_probe(self._h, int(enable), out.ctypes.data_as(C.c_void_p), grid)))
         return out
 

@@ -345,7 +345,7 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
       const long long total = (long long)c.n_queries * s.n_cand;
       const int grid_guess = std::min(P.n_tiles, per_sm * h->n_sm);
       const long long per = (total + grid_guess - 1) / grid_guess;
-      const size_t fixed = (size_t)per * 12 + 64;
+      const size_t fixed = (size_t)per * 16 + 64;
       if (fixed + 256 * 8 > smem_cap) { set_err(err, errlen, "population too large for the ranking scratch"); delete h; return SSPPCU_ELIMIT; }
       h->smem = std::max(h->smem, std::min<size_t>(std::min<size_t>((size_t)s.n_cand + 1, 8192) * 8 + fixed, smem_cap));
       int got = 0;
@@ -354,7 +354,7 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
       }
       h->grid = std::min(P.n_tiles, got * h->n_sm);
       const long long per2 = (total + h->grid - 1) / h->grid;
-      const size_t fixed2 = (size_t)per2 * 12 + 64;
+      const size_t fixed2 = (size_t)per2 * 16 + 64;
       if (fixed2 + 256 * 8 > h->smem) { per_sm = std::max(1, got - 1); continue; }
       P.rank_chunk = (int)std::min<size_t>((size_t)s.n_cand + 1, (h->smem - fixed2) / 8) & ~1;   // even: 16-byte chunk rows
       if (got == per_sm || round == 2) break;
@@ -365,6 +365,7 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
     P.n_tiles = c.n_queries;
     h->grid = P.n_tiles;
   }
+  P.smem_words = (int)(h->smem / 4);
   if ((ce = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking)) != cudaSuccess) { set_err(err, errlen, std::string("cudaStreamCreate: ") + cudaGetErrorString(ce)); delete h; return SSPPCU_ECUDA; }
   h->stream = h->own_stream;
   // ---- device buffers ----
@@ -649,11 +650,13 @@ int ssppcu_fp32_peak(int device, double* tflops, double* sm_clock_mhz) {
   return SSPPCU_OK;
 }
 
-int ssppcu_iterate(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters) {
+static int iterate_impl(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters, bool restored) {
   if (int rc = check(h)) return rc;
   if (n_iters < 1) return fail(h, SSPPCU_EINVAL, "n_iters must be positive");
+  if (restored && !h->state_saved) return fail(h, SSPPCU_EINVAL, "no saved state");
   IterParams P = h->P;
   P.seed = seed; P.iter0 = iter0; P.n_inner = n_iters;
+  P.state_in = restored ? h->d_state : nullptr;
   CU(h, launch_iterate(h->view, P, h->variant, h->threads, h->smem + h->smem_model, h->grid, h->stream));
   return SSPPCU_OK;
 }
@@ -662,16 +665,19 @@ int ssppcu_phase_probe(ssppcu_t* h, int enable, unsigned long long* stamps, int 
   if (int rc = check(h)) return rc;
   if (!h->P.coop) return fail(h, SSPPCU_EINVAL, "the phase probe exists in the cooperative kernel only");
   if (enable && !h->d_probe) {
-    CU(h, cudaMalloc(&h->d_probe, (size_t)h->grid * 6 * sizeof(unsigned long long)));
-    CU(h, cudaMemset(h->d_probe, 0, (size_t)h->grid * 6 * sizeof(unsigned long long)));
+    CU(h, cudaMalloc(&h->d_probe, (size_t)h->grid * kProbeSlots * sizeof(unsigned long long)));
+    CU(h, cudaMemset(h->d_probe, 0, (size_t)h->grid * kProbeSlots * sizeof(unsigned long long)));
   }
   if (stamps && h->d_probe) {
     CU(h, cudaStreamSynchronize(h->stream));
-    CU(h, cudaMemcpy(stamps, h->d_probe, (size_t)std::min(cap_ctas, h->grid) * 6 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    CU(h, cudaMemcpy(stamps, h->d_probe, (size_t)std::min(cap_ctas, h->grid) * kProbeSlots * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
   }
   h->P.probe = enable ? h->d_probe : nullptr;
   return h->grid;
 }
+
+int ssppcu_iterate(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters) { return iterate_impl(h, seed, iter0, n_iters, false); }
+int ssppcu_iterate_restored(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters) { return iterate_impl(h, seed, iter0, n_iters, true); }
 
 int ssppcu_sync(ssppcu_t* h) {
   if (int rc = check(h)) return rc;

@@ -198,7 +198,7 @@ __device__ __forceinline__ bool spline_point_any(int W, int NV, unsigned a_rows,
 // Phase A for one tile: candidates [c0, c0 + nc) of `query`.  Ends with the per-candidate outputs
 // and raw keys in global memory; no trailing barrier.
 __device__ __forceinline__ void score_tile(const SmemModel& M, const IterParams& P, const Smem& s, int query, int c0, int nc,
-                                           uint32_t iter) {
+                                           uint32_t iter, bool from_saved) {
   const ScoreConfig& c = P.cfg;
   const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarp = T >> 5;
   const int D = c.D, K = c.K, Mc = c.Mc, Ma = c.Ma, Mq = P.mq;
@@ -207,14 +207,17 @@ __device__ __forceinline__ void score_tile(const SmemModel& M, const IterParams&
   const int wc = row_pitch(P.w_col), wa = row_pitch(P.w_arc), dp = up4(D), NV = dp >> 2;
   const bool fast_col = NV <= 2 && (P.w_col == 3 || P.w_col == 4);   // shapes spline_point_any covers
   const bool fast_arc = NV <= 2 && (P.w_arc == 3 || P.w_arc == 4);
-  const float* mean = P.mean + (size_t)query * nfd;
-  const float* sigma = P.sigma + (size_t)query * nfd;
-  const float* best = P.best + (size_t)query * nfd;
+  // sampling state: the live block, or (first iteration of a restoring launch) the snapshot it is being re-armed from
+  const float* st_base = from_saved ? P.state_in : P.mean;
+  const size_t st_q = (size_t)P.n_query * nfd;
+  const float* mean = st_base + (size_t)query * nfd;
+  const float* sigma = st_base + st_q + (size_t)query * nfd;
+  const float* best = st_base + 2 * st_q + (size_t)query * nfd;
   const float* base = P.base + (size_t)query * K * D;
   const size_t qn = (size_t)query * c.n_cand;
   SmemXF xf{s.xf, T, tid};
   SmemQ qa{s.qs, T, tid};
-  const int best_ok = c.include_best ? P.best_valid[query] : 0;
+  const int best_ok = c.include_best ? reinterpret_cast<const int*>(st_base + 3 * st_q)[query] : 0;
   // ---- K1: candidate point matrices (rows padded to dp floats with zeros) ----
   for (int e = tid; e < nc * K * dp; e += T) { const int r = e / dp, d = e - r * dp; s.X[e] = (d < D) ? base[(r % K) * D + d] : 0.0f; }
   __syncthreads();
@@ -361,15 +364,16 @@ __device__ __forceinline__ float ces_weight_sum(int k, float lk, Sum sum) {
   return sum(k, [&](int j, float acc) { return acc + (lk - log_poly((float)j + 1.0f)); });
 }
 
-// K7 for one distribution element t of one query.  `sum` is WarpSum (one warp executes this) or CtaSum (the whole
-// CTA does); `writer` is true in the thread that stores the result.
-template <class ParamGetter, class Sum>
-__device__ __forceinline__ void update_element(const ScoreConfig& c, const unsigned long long* keys, int k, float lk, float sumw,
-                                               int t, float* mean, float* sigma, ParamGetter get_param, Sum sum, bool writer) {
+// K7 for one distribution element t of one query.  value_of(j): the element's value in the j-th best candidate.
+// `sum` is WarpSum (one warp executes this) or CtaSum (the whole CTA does); `writer` is true in the thread that
+// stores the result.
+template <class ValueOf, class Sum>
+__device__ __forceinline__ void update_element(const ScoreConfig& c, int k, float lk, float sumw, int t, float* mean, float* sigma,
+                                               ValueOf value_of, Sum sum, bool writer) {
   const int d = t % c.D;
   const float em = sum(k, [&](int j, float acc) {
     const float w = (lk - log_poly((float)j + 1.0f)) / sumw;
-    return fmaf(w, get_param((unsigned)(keys[j] & 0xFFFFFFFFu), t), acc);
+    return fmaf(w, value_of(j), acc);
   });
   const float m0 = mean[t];
   float nm = fmaf(c.mean_lr, em - m0, m0);
@@ -378,7 +382,7 @@ __device__ __forceinline__ void update_element(const ScoreConfig& c, const unsig
   const bool wrap = (c.mode == MODE_TASK && d == 3 && c.lo[3] != c.hi[3]);
   const float var = sum(k, [&](int j, float acc) {
     const float w = (lk - log_poly((float)j + 1.0f)) / sumw;
-    const float v = get_param((unsigned)(keys[j] & 0xFFFFFFFFu), t);
+    const float v = value_of(j);
     const float df = wrap ? wrap_angle_diff(v, nm, c.lo[3], c.hi[3]) : v - nm;
     return fmaf(w, df * df, acc);
   });
@@ -457,19 +461,50 @@ __device__ void cta_elites_and_update(const ScoreConfig& c, unsigned long long* 
   // the best candidate is read before any element is updated (its rows are not state, but keep the order of v1)
   const unsigned bi = (unsigned)(keys[0] & 0xFFFFFFFFu);
   if (c.do_update)
-    for (int t = warp; t < nfd; t += nwarp) update_element(c, keys, k, lk, sumw, t, mean, sigma, get_param, WarpSum{lane}, lane == 0);
+    for (int t = warp; t < nfd; t += nwarp)
+      update_element(c, k, lk, sumw, t, mean, sigma, [&](int j) { return get_param((unsigned)(keys[j] & 0xFFFFFFFFu), t); }, WarpSum{lane}, lane == 0);
   for (int t = tid; t < nfd; t += T) best[t] = get_param(bi, t);
   if (tid == 0) *best_valid = 1;
   __syncthreads();
 }
 
 // ---- coop phase B: grid-wide counting rank -------------------------------------------------
-// Items are the (query, candidate) keys, split evenly over the CTAs.  For its keys of one query a CTA
-// stages the query's raw keys in shared memory, `chunk` at a time (128-bit loads), and counts the smaller
-// ones: every warp scans its own slice of the chunk for up to 8 owned keys at a time (counters in
-// registers), warp totals meet in shared-memory counters.  rank = position in the sorted order (keys are
-// unique: they embed the candidate index).
-__device__ void rank_phase(const IterParams& P, unsigned char* smem_raw) {
+// Items are the (query, candidate) keys, split evenly over the CTAs.  For its keys of one query a CTA stages the
+// query's raw keys in shared memory, `chunk` at a time, with ONE bulk asynchronous copy (TMA, completion on an
+// mbarrier), and ranks its own keys:
+//   successful key: rank = number of smaller keys, counted against the staged keys — every warp scans its own slice
+//                   of the chunk for up to 8 owned keys at a time (counters in registers);
+//   failed key:     all failed keys share the top 32 bits and order by candidate index, so
+//                   rank = n_success + failed keys at lower indices, two counters of the same scan.
+// rank = position in the sorted order (keys are unique: they embed the candidate index).
+__device__ __forceinline__ void tma_stage(unsigned long long* dst, const unsigned long long* src, int n, unsigned long long* mbar,
+                                          unsigned& phase) {
+  // all threads call; dst/src 16-byte aligned; n keys (8 bytes each)
+  const unsigned bytes = (unsigned)(n & ~1) * 8u;
+  if (threadIdx.x == 0) {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // earlier generic-proxy accesses of dst are done
+    if (bytes) {
+      const unsigned d = (unsigned)__cvta_generic_to_shared(dst), m = (unsigned)__cvta_generic_to_shared(mbar);
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(m), "r"(bytes) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   :: "r"(d), "l"(src), "r"(bytes), "r"(m) : "memory");
+    }
+    if (n & 1) dst[n - 1] = __ldcg(src + n - 1);
+  }
+  if (bytes) {
+    const unsigned m = (unsigned)__cvta_generic_to_shared(mbar);
+    unsigned done = 0;
+    while (!done) {
+      asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                   : "=r"(done) : "r"(m), "r"(phase) : "memory");
+    }
+    phase ^= 1u;
+  }
+  __syncthreads();                                                   // the odd tail element, and a common point to go on from
+}
+
+template <class Stamp>
+__device__ void rank_phase(const IterParams& P, unsigned char* smem_raw, unsigned long long* mbar, unsigned& mbar_phase, Stamp stamp) {
   const ScoreConfig& c = P.cfg;
   const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarp = T >> 5;
   const int N = c.n_cand, nfd = c.n_free * c.D;
@@ -478,52 +513,69 @@ __device__ void rank_phase(const IterParams& P, unsigned char* smem_raw) {
   const long long lo_item = per * blockIdx.x, hi_item = min(total, lo_item + per);
   unsigned long long* s_chunk = reinterpret_cast<unsigned long long*>(smem_raw);
   unsigned long long* s_mine = s_chunk + P.rank_chunk;
-  int* s_cnt = reinterpret_cast<int*>(s_mine + per);
-  __shared__ int s_succ;
+  int* s_cnt = reinterpret_cast<int*>(s_mine + per);       // smaller keys found (successful own keys)
+  int* s_oidx = s_cnt + per;                                // own successful keys, compacted: local index
+  __shared__ int s_nos, s_fb, s_tf;                         // own successes; failed keys before this CTA's first key; failed keys
   for (long long item = lo_item; item < hi_item;) {
     const int query = (int)(item / N);
     const int i0 = (int)(item - (long long)query * N);
     const int nmine = (int)min((long long)(N - i0), hi_item - item);
     const unsigned long long* raw = P.keys_raw + (size_t)query * P.n_pad;
     unsigned long long* sorted = P.keys + (size_t)query * P.n_pad;
+    __syncthreads();
+    if (tid == 0) { s_nos = 0; s_fb = 0; s_tf = 0; }
     for (int a = tid; a < nmine; a += T) { s_mine[a] = __ldcg(raw + i0 + a); s_cnt[a] = 0; }
-    if (tid == 0) s_succ = 0;
+    __syncthreads();
+    for (int a0 = warp * 32; a0 < nmine; a0 += nwarp * 32) {   // compact the successful own keys (any order)
+      const int a = a0 + lane;
+      const bool ok = a < nmine && key_success(s_mine[a]);
+      const unsigned b = __ballot_sync(0xFFFFFFFFu, ok);
+      int base = 0;
+      if (lane == 0 && b) base = atomicAdd(&s_nos, __popc(b));
+      base = __shfl_sync(0xFFFFFFFFu, base, 0);
+      if (ok) s_oidx[base + __popc(b & ((1u << lane) - 1u))] = a;
+    }
     for (int cs = 0; cs < N; cs += P.rank_chunk) {          // rank_chunk is even and the rows are 16-byte aligned
       const int cn = min(P.rank_chunk, N - cs);
-      __syncthreads();
-      {
-        const ulonglong2* src = reinterpret_cast<const ulonglong2*>(raw + cs);
-        ulonglong2* dst = reinterpret_cast<ulonglong2*>(s_chunk);
-        for (int j = tid; j < (cn >> 1); j += T) dst[j] = __ldcg(src + j);
-        if ((cn & 1) && tid == 0) s_chunk[cn - 1] = __ldcg(raw + cs + cn - 1);
-      }
-      __syncthreads();
+      __syncthreads();                                       // the previous chunk has been consumed; s_nos / s_oidx are final
+      tma_stage(s_chunk, raw + cs, cn, mbar, mbar_phase);
+      stamp(6);                                              // chunk staged
+      const int n_os = s_nos;
       const int slice = (cn + nwarp - 1) / nwarp;
       const int j0 = warp * slice, j1 = min(cn, j0 + slice);
-      for (int a0 = 0; a0 < nmine; a0 += 8) {
+      for (int u0 = 0; u0 < max(n_os, 1); u0 += 8) {
         unsigned long long key[8];
         int cnt[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) { key[u] = (a0 + u < nmine) ? s_mine[a0 + u] : 0ull; cnt[u] = 0; }
+        for (int u = 0; u < 8; ++u) { key[u] = (u0 + u < n_os) ? s_mine[s_oidx[u0 + u]] : 0ull; cnt[u] = 0; }
+        int fb = 0, tf = 0;
         for (int j = j0 + lane; j < j1; j += 32) {
           const unsigned long long x = s_chunk[j];
 #pragma unroll
-          for (int u = 0; u < 8; ++u) cnt[u] += (x < key[u]);
+          for (int u = 0; u < 8; ++u)      // cnt += (x < key): compare, compare-extended, predicated add
+            asm("{ .reg .pred p; setp.lt.u64 p, %1, %2; @p add.s32 %0, %0, 1; }" : "+r"(cnt[u]) : "l"(x), "l"(key[u]));
+          if (u0 == 0) { const bool failed = !key_success(x); tf += failed; fb += failed && (cs + j < i0); }
         }
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
           const int tot = __reduce_add_sync(0xFFFFFFFFu, cnt[u]);
-          if (lane == 0 && tot && a0 + u < nmine) atomicAdd(&s_cnt[a0 + u], tot);
+          if (lane == 0 && tot && u0 + u < n_os) atomicAdd(&s_cnt[s_oidx[u0 + u]], tot);
+        }
+        if (u0 == 0) {
+          fb = __reduce_add_sync(0xFFFFFFFFu, fb); tf = __reduce_add_sync(0xFFFFFFFFu, tf);
+          if (lane == 0) { if (fb) atomicAdd(&s_fb, fb); if (tf) atomicAdd(&s_tf, tf); }
         }
       }
     }
     __syncthreads();
-    int succ_hi = 0;
+    stamp(7);                                                // counted
+    const int n_succ = N - s_tf;
     for (int a = tid; a < nmine; a += T) {
       const unsigned long long key = s_mine[a];
-      const int r = s_cnt[a];
+      int r;
+      if (key_success(key)) r = s_cnt[a];
+      else { r = n_succ + s_fb; for (int b = 0; b < a; ++b) r += !key_success(s_mine[b]); }
       sorted[r] = key;
-      if (key_success(key)) succ_hi = max(succ_hi, r + 1);
       if (r == 0 && !P.sort_only) {                       // best candidate of the query (last_best_, tsp_planner.h:131-138)
         write_best(P, query, key);
         if (key_success(key)) {
@@ -534,17 +586,16 @@ __device__ void rank_phase(const IterParams& P, unsigned char* smem_raw) {
         }
       }
     }
-    if (i0 == 0) for (int i = N + tid; i < P.n_pad; i += T) sorted[i] = ~0ull;
-    succ_hi = __reduce_max_sync(0xFFFFFFFFu, succ_hi);
-    if (lane == 0 && succ_hi) atomicMax(&s_succ, succ_hi);
-    __syncthreads();
-    if (tid == 0 && s_succ) atomicMax(&P.succ_acc[query], s_succ);   // n_success = rank of the last success + 1
+    if (i0 == 0) {
+      for (int i = N + tid; i < P.n_pad; i += T) sorted[i] = ~0ull;
+      if (tid == 0) P.succ_acc[query] = n_succ;            // read by phase C after the grid barrier
+    }
     item += nmine;
   }
 }
 
 // ---- coop phase C: one CTA per (query, distribution element); element nfd = the query's scalars ----
-__device__ void update_phase(const IterParams& P, float* s_part) {
+__device__ void update_phase(const IterParams& P, float* s_part, float* s_val, int s_val_cap) {
   const ScoreConfig& c = P.cfg;
   const int tid = threadIdx.x, T = blockDim.x;
   const int nfd = c.n_free * c.D, N = c.n_cand;
@@ -571,7 +622,14 @@ __device__ void update_phase(const IterParams& P, float* s_part) {
     const float lk = log_poly((float)k + 0.5f);
     const float sumw = ces_weight_sum(k, lk, CtaSum{s_part});
     StoredParams gp{P.params + (size_t)query * N * nfd, nfd, (unsigned)P.cand_offset};
-    update_element(c, keys, k, lk, sumw, t, mean, sigma, gp, CtaSum{s_part}, tid == 0);
+    if (k <= s_val_cap) {           // gather the element's elite values once (keys -> sampled rows: two dependent reads)
+      __syncthreads();
+      for (int j = tid; j < k; j += T) s_val[j] = gp((unsigned)(__ldcg(keys + j) & 0xFFFFFFFFu), t);
+      __syncthreads();
+      update_element(c, k, lk, sumw, t, mean, sigma, [&](int j) { return s_val[j]; }, CtaSum{s_part}, tid == 0);
+    } else {
+      update_element(c, k, lk, sumw, t, mean, sigma, [&](int j) { return gp((unsigned)(keys[j] & 0xFFFFFFFFu), t); }, CtaSum{s_part}, tid == 0);
+    }
   }
 }
 
@@ -582,9 +640,16 @@ __global__ void __launch_bounds__(MAXT, MINB)
 sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant__ IterParams P) {
   __shared__ int s_int[4];
   __shared__ float s_part[8];
+  __shared__ __align__(8) unsigned long long s_mbar;    // completion barrier of the bulk copies (rank phase)
   const ScoreConfig& c = P.cfg;
   const int tid = threadIdx.x, T = blockDim.x;
   const int nfd = c.n_free * c.D;
+  unsigned mbar_phase = 0;
+  if (COOP && tid == 0) {
+    const unsigned m = (unsigned)__cvta_generic_to_shared(&s_mbar);
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(m) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
   const SmemModel M = stage_model(MG, tid, T);      // visible after the first barrier below (load_basis / score_tile)
   unsigned char* smem_raw = smem_all + P.model_bytes;
   const Smem s = carve(smem_raw, c, P, T);
@@ -593,7 +658,17 @@ sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant_
     const int query = blockIdx.x;
     load_basis(s, c, P, tid, T);
     for (int it = 0; it < P.n_inner; ++it) {
-      score_tile(M, P, s, query, 0, c.n_cand, P.iter0 + (uint32_t)it);
+      const bool from_saved = P.state_in != nullptr && it == 0;
+      score_tile(M, P, s, query, 0, c.n_cand, P.iter0 + (uint32_t)it, from_saved);
+      if (from_saved) {               // re-arm this query's live state from the snapshot (nobody else touches it)
+        const size_t sq = (size_t)P.n_query * nfd;
+        for (int t = tid; t < nfd; t += T)
+          for (int b = 0; b < 3; ++b) P.mean[b * sq + (size_t)query * nfd + t] = P.state_in[b * sq + (size_t)query * nfd + t];
+        if (tid == 0) {
+          const int* si = reinterpret_cast<const int*>(P.state_in + 3 * sq);
+          P.best_valid[query] = si[query]; P.any_success[query] = si[P.n_query + query];
+        }
+      }
       __syncthreads();                                   // raw keys were written by this CTA: visible after the barrier
       unsigned long long* keys = s.keys;
       const unsigned long long* raw = P.keys_raw + (size_t)query * P.n_pad;
@@ -620,32 +695,36 @@ sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant_
     if (P.probe && it == 0 && tid == 0) {
       unsigned long long t;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-      P.probe[(size_t)blockIdx.x * 6 + slot] = t;
+      P.probe[(size_t)blockIdx.x * kProbeSlots + slot] = t;
     }
   };
   for (int it = 0; it < P.n_inner; ++it) {
     stamp(it, 0);
+    const bool from_saved = P.state_in != nullptr && it == 0;
+    if (from_saved) {                 // re-arm the live state from the snapshot; phase A reads the snapshot itself
+      const size_t words = (size_t)P.n_query * (3 * nfd + 2);
+      for (size_t e = (size_t)blockIdx.x * T + tid; e < words; e += (size_t)gridDim.x * T) P.mean[e] = P.state_in[e];
+    }
     // ---- phase A: score the tiles ----
     load_basis(s, c, P, tid, T);                         // phase B reuses this shared memory
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
       const int query = tile / P.ctas_per_query;
       const int c0 = (tile - query * P.ctas_per_query) * P.cand_per_cta;
       const int nc = min(P.cand_per_cta, c.n_cand - c0);
-      if (c0 == 0 && tid == 0) P.succ_acc[query] = 0;
-      score_tile(M, P, s, query, c0, nc, P.iter0 + (uint32_t)it);
+      score_tile(M, P, s, query, c0, nc, P.iter0 + (uint32_t)it, from_saved);
       __syncthreads();
     }
     stamp(it, 1);
     grid.sync();
     stamp(it, 2);
     // ---- phase B: order the keys ----
-    rank_phase(P, smem_raw);
+    rank_phase(P, smem_raw, &s_mbar, mbar_phase, [&](int slot) { stamp(it, slot); });
     stamp(it, 3);
     if (P.sort_only) { if (it + 1 < P.n_inner) grid.sync(); continue; }
     grid.sync();
     stamp(it, 4);
     // ---- phase C: distribution update ----
-    update_phase(P, s_part);
+    update_phase(P, s_part, reinterpret_cast<float*>(smem_raw), P.smem_words);
     stamp(it, 5);
     if (it + 1 < P.n_inner) grid.sync();
   }
@@ -718,7 +797,7 @@ sspp_merge_finish_kernel(const __grid_constant__ MergeParams P) {     // one CTA
     if (n_succ == 0) { if (tid == 0) P.sigma[t] = clamp_sigma(c, P.sigma[t] * c.inc); continue; }
     const float lk = log_poly((float)k + 0.5f);
     const float sumw = ces_weight_sum(k, lk, CtaSum{s_part});
-    update_element(c, P.keys, k, lk, sumw, t, P.mean, P.sigma, gp, CtaSum{s_part}, tid == 0);
+    update_element(c, k, lk, sumw, t, P.mean, P.sigma, [&](int j) { return gp((unsigned)(P.keys[j] & 0xFFFFFFFFu), t); }, CtaSum{s_part}, tid == 0);
   }
 }
 

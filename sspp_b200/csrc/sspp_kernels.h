@@ -21,6 +21,7 @@ struct IterParams {
   int rank_chunk;           // keys staged in shared memory per ranking pass (coop)
   int w_col, w_arc;         // band widths of the collocation matrices
   int mq;                   // pitch (rows) of the per-candidate point buffer: max(Mc, Ma)
+  int smem_words;           // 4-byte words of dynamic shared memory behind the scene tables (phase scratch)
   int model_bytes;          // scene tables staged at the front of dynamic shared memory (model_smem_bytes)
   uint32_t iter0;           // iteration counter of the first inner iteration (Philox counter word)
   uint64_t seed;
@@ -33,6 +34,8 @@ struct IterParams {
   float* sigma;             // [Q][n_free*D]
   float* best;              // [Q][n_free*D]  forwarded best candidate (last_best_, tsp_planner.h:134)
   int* best_valid;          // [Q]
+  const float* state_in;    // NULL, or a snapshot of the live block mean|sigma|best|best_valid|any_success: the launch's first
+                            // iteration samples from it and re-arms the live block with it (fused restore)
   float* params;            // [Q][N][n_free*D] sampled rows of every candidate
   float* L; float* Cnf; float* Cwf; float* cost;   // [Q][N]
   uint8_t* status;          // [Q][N]
@@ -42,7 +45,7 @@ struct IterParams {
   int* n_success; int* n_elite; int* best_idx; int* any_success;   // [Q]
   float* best_cost;         // [Q]
   int* succ_acc;            // [Q] scratch: success count accumulated by the ranking phase
-  unsigned long long* probe; // diagnostics, NULL = off: [grid][6] %globaltimer stamps at the phase boundaries (coop kernel)
+  unsigned long long* probe; // diagnostics, NULL = off: [grid][kProbeSlots] %globaltimer stamps at the phase boundaries (coop kernel)
 };
 
 // shared-memory bytes of the staged scene tables, and of the scoring phase for the given tile shape (the
@@ -52,6 +55,7 @@ size_t iterate_smem_bytes(const ssppm::DevModelHead& M, const IterParams& P, int
 
 // Launch-bound variants of the iteration kernel: __launch_bounds__(max_threads, min_ctas) sets the register
 // budget (65536 / (max_threads * min_ctas), rounded down to 8) and with it the resident warps per SM.
+constexpr int kProbeSlots = 8;   // phase-probe stamps per CTA
 struct IterVariant { int max_threads, min_ctas; };
 constexpr int kNumIterVariants = 8;
 constexpr IterVariant kIterVariants[kNumIterVariants] = {{256, 2}, {256, 3}, {320, 2}, {320, 3}, {448, 2}, {384, 2}, {128, 7}, {192, 5}};
