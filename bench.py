@@ -6,8 +6,8 @@
 
 Workload at N = 1 (BASELINE.json configs[1]): robocrane 7-DoF fixture, one planning query,
 4096 candidates x 64 collocation points x 10 control points.  One STEP = one planner iteration of
-that query from its initial sampling state: re-arm the state (one device-to-device copy), then ONE
-fused launch: Philox perturb -> spline -> kinematics -> collision -> cost reduce -> elites -> update.
+that query from its initial sampling state, ONE fused launch (ssppcu_iterate_restored): re-arm the
+state from its snapshot -> Philox perturb -> spline -> kinematics -> collision -> cost reduce -> elites -> update.
 The state is re-armed every step so that every step scores the same statistical workload (about half
 of the candidates collide); Philox counters differ per step.
 N > 1: independent planning queries shard across GPUs (no data-path collective): every rank runs
@@ -230,8 +230,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     launches_per_step = 1 if d.ctas_per_query == 1 else inner
 
     def step(i: int):
-        h.restore_state()
-        h.iterate(SEED, i * inner, inner)
+        h.iterate(SEED, i * inner, inner, restored=True)      # re-arm from the snapshot + iterate: ONE launch
 
     clocks = ClockSampler(local_rank)
     for i in range(max(args.warmup, 3)):
@@ -250,8 +249,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     nk = min(args.steps, 100)
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(nk)]
     for i, (a, b) in enumerate(evs):
-        h.restore_state()
-        a.record(stream); h.iterate(SEED, (args.warmup + i) * inner, inner); b.record(stream)
+        a.record(stream); h.iterate(SEED, (args.warmup + i) * inner, inner, restored=True); b.record(stream)
     torch.cuda.synchronize()
     k_ms = float(np.mean([a.elapsed_time(b) for a, b in evs]))
     # ---- e2e: through the host API, host buffers in, every candidate's result out ----
@@ -270,7 +268,8 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     h2d = d.n_queries * (d.n_points * d.dof + 2 * nfd) * 4
     d2h = d.n_queries * (d.n_cand * (4 * 4 + 1) + 5 * 4 + nfd * 4 + 4)
     e2e = dict(value=pts_per_step * world * n_e2e / e2e_s, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h,
-               steps=n_e2e, api="sspp_b200.capi (ctypes over the C ABI): set_queries + set_joint_noise/reset_distribution + iterate + get_results + get_best")
+               steps=n_e2e, api="sspp_b200.capi (ctypes over the C ABI): set_queries + set_joint_noise/reset_distribution + iterate + get_results + get_best; "
+                   "host arrays are pageable numpy buffers, the library stages them through its pinned ring / pinned result mirror")
     if rank != 0:
         h.close()
         return
@@ -284,7 +283,11 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     ach = pts_per_step * wm["flop_per_point"] / (k_ms * 1e-3) * 1e-12
     hbm_bytes = d.n_queries * d.n_cand * inner * roofline.BYTES_PER_CANDIDATE
     hbm_ach = hbm_bytes / (k_ms * 1e-3) * 1e-9
-    roof = dict(bound="fp32", achieved=ach, peak=fp32_peak, unit="TFLOP/s", frac=ach / fp32_peak, traffic=None,
+    traffic = None                                  # DRAM bytes per launch of the kernel, from the committed ncu --set full capture
+    tf = ROOT / "profiles" / "roofline_traffic.json"
+    if tf.exists():
+        traffic = json.loads(tf.read_text()).get(args.workload, {}).get("dram_bytes_per_launch")
+    roof = dict(bound="fp32", achieved=ach, peak=fp32_peak, unit="TFLOP/s", frac=ach / fp32_peak, traffic=traffic,
                 kernel="sspp_iterate_kernel", kernel_ms=k_ms, flop_per_point=wm["flop_per_point"],
                 note="nominal FLOP model of sspp_b200/roofline.py (every filtered pair charged its full narrow phase; the kernel culls "
                      "most by bounding spheres) over the FMA peak measured live by ssppcu_fp32_peak; MEASURED_PEAKS.json has no FP32 entry",

@@ -479,8 +479,8 @@ SSPP_HD float point_box_sd(v3 x, v3 h) {
 
 // distance (>= 0) from the segment p0 + t d (box frame, t in [0,1]) to a box.  The squared
 // distance g(t) is convex, C1 and piecewise quadratic, so g'(t) is monotone piecewise linear:
-// bracket its root on [0,1], then 6 Newton steps that fall back to bisection when they leave
-// the bracket (fixed trip count: identical work in every lane and in the oracles).
+// bracket its root on [0,1], then at most 6 Newton steps that fall back to bisection when they leave
+// the bracket, stopping at a fixed point.
 SSPP_HD void seg_box_grad(float t, v3 p0, v3 d, v3 h, float* g, float* hs) {
   const float x = fmaf(t, d.x, p0.x), y = fmaf(t, d.y, p0.y), z = fmaf(t, d.z, p0.z);
   const float ex = x - clampf(x, -h.x, h.x), ey = y - clampf(y, -h.y, h.y), ez = z - clampf(z, -h.z, h.z);
@@ -495,14 +495,17 @@ SSPP_HD float seg_box_dist(v3 p0, v3 d, v3 h) {
   seg_box_grad(0.0f, p0, d, h, &g0, &hs);
   seg_box_grad(1.0f, p0, d, h, &g1, &hs);
   float lo = 0.0f, hi = 1.0f, t = 0.5f;
+  if (g0 < 0.0f && g1 > 0.0f) {        // interior minimum; otherwise an end point is the answer and the loop is moot
 #pragma unroll 1
-  for (int it = 0; it < 6; ++it) {
-    float g;
-    seg_box_grad(t, p0, d, h, &g, &hs);
-    if (g > 0.0f) hi = t; else if (g < 0.0f) lo = t;
-    float tn = (hs > 0.0f && g != 0.0f) ? t - g / hs : t;
-    if (g != 0.0f && !(tn > lo && tn < hi)) tn = 0.5f * (lo + hi);
-    t = tn;
+    for (int it = 0; it < 6; ++it) {
+      float g;
+      seg_box_grad(t, p0, d, h, &g, &hs);
+      if (g > 0.0f) hi = t; else if (g < 0.0f) lo = t;
+      float tn = (hs > 0.0f && g != 0.0f) ? t - g / hs : t;
+      if (g != 0.0f && !(tn > lo && tn < hi)) tn = 0.5f * (lo + hi);
+      if (tn == t) break;              // fixed point: every further step would reproduce it
+      t = tn;
+    }
   }
   t = (g0 >= 0.0f) ? 0.0f : ((g1 <= 0.0f) ? 1.0f : t);
   const float x = fmaf(t, d.x, p0.x), y = fmaf(t, d.y, p0.y), z = fmaf(t, d.z, p0.z);

@@ -199,3 +199,65 @@ def test_sdf_mode_matches_oracles():
     from sspp_b200 import capi
     with pytest.raises(capi.SsppError, match="uniform collision mask"):
         capi.Handle(bad.model, bad.cfg)
+
+
+@pytest.mark.parametrize("kind", ["joint", "task"])
+def test_iterate_restored_equals_restore_then_iterate(kind):
+    """ssppcu_iterate_restored = ssppcu_restore_state + ssppcu_iterate, bit for bit, in both kernel shapes"""
+    from sspp_b200 import capi
+    if kind == "joint":
+        case = joint_case(n_samples=1000, check_points=32, do_update=True)
+    else:
+        rng = np.random.default_rng(3)
+        Q = 160
+        s = np.column_stack([rng.uniform(0.2, 0.6, Q), rng.uniform(-0.4, 0.4, Q), rng.uniform(0.14, 0.4, Q), rng.uniform(-1.5, 1.5, Q)])
+        e = np.column_stack([rng.uniform(0.2, 0.6, Q), rng.uniform(-0.4, 0.4, Q), rng.uniform(0.14, 0.4, Q), rng.uniform(-1.5, 1.5, Q)])
+        case = task_case(n_queries=Q, start=s, end=e)
+    out = []
+    for fused in (False, True):
+        h = _handle(case)
+        h.iterate(SEED, 0, 2)
+        h.save_state()
+        h.iterate(SEED, 2, 3)                       # move the live state away from the snapshot
+        if fused:
+            h.iterate(SEED, 7, 2, restored=True)
+        else:
+            h.restore_state(); h.iterate(SEED, 7, 2)
+        r = h.results(); m, sg = h.get_distribution(); b, bv = h.best()
+        out.append((r, m, sg, b, bv))
+        h.close()
+    (r0, m0, s0, b0, v0), (r1, m1, s1, b1, v1) = out
+    for k in r0:
+        assert np.array_equal(r0[k], r1[k]), k
+    assert np.array_equal(m0, m1) and np.array_equal(s0, s1) and np.array_equal(b0, b1) and np.array_equal(v0, v1)
+
+
+def test_tile_shapes_and_kernel_variants_agree_bitwise():
+    """the launch-bound variant, threads per CTA and candidates per CTA are pure tuning knobs"""
+    ref = None
+    for hint in (0, (0 + 1) | (14 << 8) | (256 << 20), (2 + 1) | (9 << 8) | (320 << 20), (1 + 1) | (31 << 8) | (256 << 20),
+                 (5 + 1) | (20 << 8) | (384 << 20)):
+        case = joint_case(n_samples=2000, check_points=24, do_update=True)
+        case.cfg.tile_hint = hint
+        h = _handle(case)
+        h.iterate(SEED, 0, 2)
+        r = h.results(); m, sg = h.get_distribution(); idx, cost, w = h.elites(0)
+        cur = (r["cost"].copy(), r["status"].copy(), m, sg, idx, w)
+        if ref is None:
+            ref = cur
+        else:
+            for a, b in zip(ref, cur):
+                assert np.array_equal(a, b), hex(hint)
+        h.close()
+
+
+def test_phase_probe_stamps_are_ordered():
+    case = joint_case(n_samples=2048, check_points=32, do_update=True)
+    h = _handle(case)
+    h.phase_probe(True)
+    h.iterate(SEED, 0, 1)
+    st = h.phase_probe(True, read=True).astype(np.int64)
+    assert st.shape[1] == 8 and (st[:, :6] > 0).all()
+    assert (np.diff(st[:, :6], axis=1) >= 0).all()              # start <= scored <= barrier 1 <= ranked <= barrier 2 <= updated
+    assert st[:, 2].min() >= st[:, 1].max() - 2000              # nobody passes barrier 1 before everybody has scored (timer granularity)
+    h.close()
