@@ -77,10 +77,12 @@ struct alignas(16) DevSGeom {
   int type;
   int pad_[3];
 };
-// One filtered (moving geom, static geom) pair with its broad-phase test precomputed by compile_model:
-//   bounded partner: culled when |p - c[0..2]|^2 > c[3],  c = (S.pos, (G.rbound + S.rbound + thr)^2)
-//   plane partner:   culled when n . p > c[3],            c = (n, n . S.pos + G.rbound + thr)
-// with p the moving geom's centre and thr = max(margin, 0) + 1e-4 (conservative: margin + slack).
+// One filtered (moving geom, static geom) pair with its broad-phase test precomputed by compile_model as ONE
+// affine form of the moving geom's centre p:  f(p) = c[0] p.x + c[1] p.y + c[2] p.z + c[3]
+//   plane partner:   c = (n, -(n . S.pos + G.rbound + thr));      culled when f(p) > 0
+//   bounded partner: c = (-2 S.pos, |S.pos|^2 - (G.rbound + S.rbound + thr)^2);  culled when f(p) > -|p|^2
+//                    (|p - S.pos|^2 > rr^2 expanded; |p|^2 is formed once per moving geom)
+// thr = max(margin, 0) + 1e-4 (conservative: margin + slack; the expansion's rounding, ~1e-6 m, is far inside it).
 struct alignas(16) DevPair { float c[4]; int s; float margin; float thr; int plane; };
 // SDF mode: a moving geom is sampled by spheres (centre in the frame of moving body `body`)
 struct alignas(16) DevSphere { float c[3]; float r; float margin; int body; int pad_[2]; };
@@ -877,16 +879,16 @@ SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf) {
       {
         const int k0 = gi.y;
         uint32_t near_mask = 0u;
+        const float npp = -dot(P.p, P.p);
 #pragma unroll 1
         for (int k = k0; k < gi.z; ++k) {                    // plane partners: bounding sphere beyond the half space?
           const f4 c4 = rec_f4(M.pair, k, PW_C);
-          if (!(dot(mk(c4.x, c4.y, c4.z), P.p) > c4.w)) near_mask |= 1u << (k - k0);
+          if (!(fmaf(c4.z, P.p.z, fmaf(c4.y, P.p.y, fmaf(c4.x, P.p.x, c4.w))) > 0.0f)) near_mask |= 1u << (k - k0);
         }
 #pragma unroll 1
         for (int k = gi.z; k < gi.w; ++k) {                  // bounded partners: bounding spheres apart?
           const f4 c4 = rec_f4(M.pair, k, PW_C);
-          const v3 w = sub(P.p, mk(c4.x, c4.y, c4.z));
-          if (!(dot(w, w) > c4.w)) near_mask |= 1u << (k - k0);
+          if (!(fmaf(c4.z, P.p.z, fmaf(c4.y, P.p.y, fmaf(c4.x, P.p.x, c4.w))) > npp)) near_mask |= 1u << (k - k0);
         }
         while (near_mask) {
           const int j = lowest_bit(near_mask);

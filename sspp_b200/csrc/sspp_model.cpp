@@ -648,11 +648,20 @@ ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const 
       const DevSGeom& S = D.sg[pr.s];
       pr.thr = std::max(pr.margin, 0.0f) + 1e-4f;
       if (S.rbound >= 0.0f) {
-        const float rr = D.mg[ig].rbound + S.rbound + pr.thr;
-        pr.plane = 0; pr.c[0] = S.pos[0]; pr.c[1] = S.pos[1]; pr.c[2] = S.pos[2]; pr.c[3] = rr * rr;
+        // FP64 here, rounded once.  The kernel's FP32 expansion of |p - c|^2 errs by a few ulp of |p|^2 + |c|^2: the
+        // squared radius is widened by 16 ulp of that magnitude (|p| bounded by the workspace bound, else 4 m)
+        const DevMGeom& G = D.mg[ig];
+        const double rr = (double)G.rbound + S.rbound + pr.thr;
+        const double c2 = (double)S.pos[0] * S.pos[0] + (double)S.pos[1] * S.pos[1] + (double)S.pos[2] * S.pos[2];
+        const double cen = std::sqrt(centre[G.body][0] * centre[G.body][0] + centre[G.body][1] * centre[G.body][1] + centre[G.body][2] * centre[G.body][2]);
+        const double glen = std::sqrt((double)G.pos[0] * G.pos[0] + (double)G.pos[1] * G.pos[1] + (double)G.pos[2] * G.pos[2]);
+        const double pmax = reach[G.body] < kInf ? cen + reach[G.body] + glen : 4.0;
+        const double widen = 16.0 * 1.1920929e-7 * (pmax * pmax + c2);
+        pr.plane = 0; pr.c[0] = -2.0f * S.pos[0]; pr.c[1] = -2.0f * S.pos[1]; pr.c[2] = -2.0f * S.pos[2];
+        pr.c[3] = (float)(c2 - (rr * rr + widen));
       } else {
         const v3 n = mk(S.R[2], S.R[5], S.R[8]);
-        pr.plane = 1; pr.c[0] = n.x; pr.c[1] = n.y; pr.c[2] = n.z; pr.c[3] = dot(n, ld3(S.pos)) + D.mg[ig].rbound + pr.thr;
+        pr.plane = 1; pr.c[0] = n.x; pr.c[1] = n.y; pr.c[2] = n.z; pr.c[3] = -(dot(n, ld3(S.pos)) + D.mg[ig].rbound + pr.thr);
       }
     }
   for (int ig = 0; ig < D.n_mgeom; ++ig)
