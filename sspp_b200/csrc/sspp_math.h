@@ -674,19 +674,28 @@ SSPP_HD float sdf_sample_nodes(const SdfGrid& g, v3 x) {
     v[c] = g.nodes[((size_t)(k + (c >> 2)) * g.ny + (j + ((c >> 1) & 1))) * g.nx + (i + (c & 1))];
   return trilerp(v, fx, fy, fz);
 }
-// kernel read: the 8 corners of a cell are one 32-byte sector, fetched as two 16-byte read-only loads
+// kernel read: the 8 corners of a cell are one 32-byte sector, fetched with one 256-bit read-only load
+// (a warp's 32 scattered cells then cost one pass through the L1 tag stage instead of two)
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ void sdf_load_cell(const float* c, float v[8]) {
+  asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]) : "l"(c));
+}
+#endif
 SSPP_HD float sdf_sample(const SdfGrid& g, v3 x) {
 #if defined(__CUDA_ARCH__)
   int i, j, k; float fx, fy, fz;
   sdf_locate(g, x, &i, &j, &k, &fx, &fy, &fz);
-  const float4* c = reinterpret_cast<const float4*>(g.cells) + 2 * (((size_t)k * (g.ny - 1) + j) * (g.nx - 1) + i);
-  const float4 a = __ldg(c), b = __ldg(c + 1);
-  const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+  float v[8];
+  sdf_load_cell(g.cells + 8 * (((size_t)k * (g.ny - 1) + j) * (g.nx - 1) + i), v);
   return trilerp(v, fx, fy, fz);
 #else
   return sdf_sample_nodes(g, x);
 #endif
 }
+#ifndef SDF_BATCH
+#define SDF_BATCH 2   // cell reads in flight per thread (costs are still added in sample order)
+#endif
 // contribution of one sphere sample at signed distance d
 SSPP_HD float sphere_contact_cost(int rule, float d, float margin) {
   if (rule == CR_COUNT) return (d < margin) ? 1.0f : 0.0f;
@@ -858,6 +867,29 @@ SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf) {
     }
     if (M.sdf_mode) {                                        // sphere samples of this body against the grid
       const i4 sp = rec_i4(M.body, b, BW_SPH);          // sph_begin, sph_end
+#if defined(__CUDA_ARCH__) && SDF_BATCH > 1
+#pragma unroll 1
+      for (int k0 = sp.x; k0 < sp.y; k0 += SDF_BATCH) {
+        float v[SDF_BATCH][8];
+        float fx[SDF_BATCH], fy[SDF_BATCH], fz[SDF_BATCH];
+#pragma unroll
+        for (int u = 0; u < SDF_BATCH; ++u) {
+          const int k = (k0 + u < sp.y) ? k0 + u : sp.y - 1;
+          const f4 sc = rec_f4(M.sph, k, SW_C);
+          int i, j, l;
+          sdf_locate(M.grid, add(p, mulv(R, mk(sc.x, sc.y, sc.z))), &i, &j, &l, &fx[u], &fy[u], &fz[u]);
+          sdf_load_cell(M.grid.cells + 8 * (((size_t)l * (M.grid.ny - 1) + j) * (M.grid.nx - 1) + i), v[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < SDF_BATCH; ++u) {
+          if (k0 + u < sp.y) {
+            const i4 rm = rec_i4(M.sph, k0 + u, SW_C);
+            const float margin = word_as_float(rec_i4(M.sph, k0 + u, SW_MARGIN).x);
+            cost += sphere_contact_cost(M.rule, trilerp(v[u], fx[u], fy[u], fz[u]) - word_as_float(rm.w), margin);
+          }
+        }
+      }
+#else
 #pragma unroll 1
       for (int k = sp.x; k < sp.y; ++k) {
         const f4 sc = rec_f4(M.sph, k, SW_C);                // centre, radius
@@ -865,6 +897,7 @@ SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf) {
         const float d = sdf_sample(M.grid, add(p, mulv(R, mk(sc.x, sc.y, sc.z)))) - sc.w;
         cost += sphere_contact_cost(M.rule, d, margin);
       }
+#endif
       continue;
     }
     const i4 fl = rec_i4(M.body, b, BW_FLAGS);               // has_anchor, r0_identity, geom_begin, geom_end
