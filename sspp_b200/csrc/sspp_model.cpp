@@ -13,6 +13,8 @@
 
 namespace sspp {
 
+void quat_to_mat(const double* qi, double* R);
+
 // ------------------------------------------------------------------------------------------
 // minimal XML reader: elements, attributes, comments, declarations; character data ignored
 // ------------------------------------------------------------------------------------------
@@ -42,10 +44,23 @@ struct XmlReader {
       while (i < s.size() && s[i] != '<') ++i;   // character data
       if (i >= s.size()) return;
       if (starts("<!--")) { size_t e = s.find("-->", i + 4); if (e == std::string::npos) fail("unterminated comment"); i = e + 3; }
+      else if (starts("<![CDATA[")) { size_t e = s.find("]]>", i + 9); if (e == std::string::npos) fail("unterminated CDATA"); i = e + 3; }
       else if (starts("<?")) { size_t e = s.find("?>", i + 2); if (e == std::string::npos) fail("unterminated declaration"); i = e + 2; }
       else if (starts("<!")) { size_t e = s.find('>', i); if (e == std::string::npos) fail("unterminated <!"); i = e + 1; }
       else return;
     }
+  }
+  std::string decode_entities(const std::string& v) const {
+    if (v.find('&') == std::string::npos) return v;
+    static const std::pair<const char*, char> ent[] = {{"&lt;", '<'}, {"&gt;", '>'}, {"&amp;", '&'}, {"&quot;", '"'}, {"&apos;", '\''}};
+    std::string o;
+    for (size_t k = 0; k < v.size();) {
+      bool hit = false;
+      if (v[k] == '&')
+        for (auto& e : ent) { const size_t n = std::strlen(e.first); if (v.compare(k, n, e.first) == 0) { o += e.second; k += n; hit = true; break; } }
+      if (!hit) o += v[k++];
+    }
+    return o;
   }
   std::string name() {
     size_t b = i;
@@ -71,7 +86,7 @@ struct XmlReader {
       char q = s[i++];
       size_t e = s.find(q, i);
       if (e == std::string::npos) fail("unterminated attribute value");
-      n->attr.emplace_back(k, s.substr(i, e - i));
+      n->attr.emplace_back(k, decode_entities(s.substr(i, e - i)));
       i = e + 1;
     }
     for (;;) {
@@ -132,6 +147,33 @@ void zaxis_to_quat(const double* zin, double* q) {   // minimal rotation taking 
 }
 
 struct Compiler { bool degree = true; std::string eulerseq = "xyz"; };
+
+// rigid transform of a <frame> (or the identity); composed onto the bodies and geoms it wraps
+struct Pose {
+  double pos[3] = {0, 0, 0}, quat[4] = {1, 0, 0, 0};
+  bool identity = true;
+};
+void quat_mul(const double* a, const double* b, double* o) {
+  o[0] = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3];
+  o[1] = a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2];
+  o[2] = a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1];
+  o[3] = a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0];
+}
+void quat_rotate(const double* q, const double* v, double* o) {
+  double R[9];
+  quat_to_mat(q, R);
+  mat_vec(R, v, o);
+}
+// child pose (pos, quat) expressed in the frame's parent: outer o inner
+void compose(const Pose& outer, double* pos, double* quat) {
+  if (outer.identity) return;
+  double rp[3], q[4];
+  quat_rotate(outer.quat, pos, rp);
+  for (int k = 0; k < 3; ++k) pos[k] = outer.pos[k] + rp[k];
+  quat_mul(outer.quat, quat, q);
+  const double n = std::sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+  for (int k = 0; k < 4; ++k) quat[k] = q[k] / n;
+}
 
 // orientation attributes of body / geom elements -> quaternion
 void orientation(const AttrMap& a, const Compiler& c, double* q) {
@@ -233,7 +275,7 @@ struct Builder {
     return a;
   }
 
-  void add_geom(const XmlNode& e, int body, const std::string& childclass) {
+  void add_geom(const XmlNode& e, int body, const std::string& childclass, const Pose& frame) {
     AttrMap a = resolve(e, childclass, true);
     auto geti = [&](const char* k, int dflt) { auto it = a.find(k); return it == a.end() ? dflt : (int)std::lround(nums(it->second).at(0)); };
     const int contype = geti("contype", 1), conaff = geti("conaffinity", 1);
@@ -258,31 +300,49 @@ struct Builder {
       zaxis_to_quat(d, quat);
       if (type == ssppm::GT_BOX) size[2] = 0.5 * len; else size[1] = 0.5 * len;
     }
+    compose(frame, pos, quat);
     const bool ok = (type == ssppm::GT_PLANE) || (type == ssppm::GT_SPHERE && size[0] > 0) ||
                     ((type == ssppm::GT_CAPSULE || type == ssppm::GT_CYLINDER) && size[0] > 0 && size[1] > 0) ||
                     (type == ssppm::GT_BOX && size[0] > 0 && size[1] > 0 && size[2] > 0);
     if (!ok) throw std::runtime_error("geom '" + gname + "': size is incomplete for type " + tname);
+    if (type == ssppm::GT_PLANE && body != 0 && m.body_weld[body] != 0)
+      throw std::runtime_error("geom '" + gname + "': planes must belong to a static body");
+    const double margin = a.count("margin") ? nums(a["margin"]).at(0) : 0.0;
+    if (!(margin >= 0.0)) throw std::runtime_error("geom '" + gname + "': margin must be non-negative");
     m.geom_name.push_back(gname);
     m.geom_body.push_back(body);
     m.geom_type.push_back(type);
     m.geom_contype.push_back(contype);
     m.geom_conaffinity.push_back(conaff);
-    m.geom_margin.push_back(a.count("margin") ? nums(a["margin"]).at(0) : 0.0);
+    m.geom_margin.push_back(margin);
     for (int k = 0; k < 3; ++k) { m.geom_size.push_back(size[k]); m.geom_pos.push_back(pos[k]); }
     for (int k = 0; k < 4; ++k) m.geom_quat.push_back(quat[k]);
     ++m.ngeom;
   }
 
-  int add_body(const XmlNode* e, int parent, std::string childclass) {
+  // children of a body (or of the world), <frame> wrappers flattened in document order
+  struct Item { const XmlNode* node; Pose frame; std::string childclass; };
+  void collect(const XmlNode& e, const Pose& frame, const std::string& childclass, std::vector<Item>* out) const {
+    for (auto& ch : e.child) {
+      if (ch->tag == "frame") {
+        AttrMap fa;
+        for (auto& kv : ch->attr) fa[kv.first] = kv.second;
+        Pose inner;
+        if (fa.count("pos")) { auto v = nums(fa["pos"]); if (v.size() != 3) throw std::runtime_error("frame pos needs 3 numbers"); for (int k = 0; k < 3; ++k) inner.pos[k] = v[k]; }
+        orientation(fa, comp, inner.quat);
+        compose(frame, inner.pos, inner.quat);
+        inner.identity = false;
+        collect(*ch, inner, fa.count("childclass") ? fa["childclass"] : childclass, out);
+      } else if (ch->tag == "geom" || ch->tag == "body" || ch->tag == "joint" || ch->tag == "freejoint") {
+        out->push_back(Item{ch.get(), frame, childclass});
+      }
+    }
+  }
+
+  int push_body(const std::string& name, int parent, const double* pos, const double* quat) {
     const int id = m.nbody++;
-    AttrMap a;
-    if (e) for (auto& kv : e->attr) a[kv.first] = kv.second;
-    if (a.count("childclass")) childclass = a["childclass"];
-    m.body_name.push_back(a.count("name") ? a["name"] : (id == 0 ? "world" : ""));
+    m.body_name.push_back(name);
     m.body_parent.push_back(parent < 0 ? 0 : parent);
-    double pos[3] = {0, 0, 0}, quat[4] = {1, 0, 0, 0};
-    if (a.count("pos")) { auto v = nums(a["pos"]); if (v.size() != 3) throw std::runtime_error("body pos needs 3 numbers"); for (int k = 0; k < 3; ++k) pos[k] = v[k]; }
-    orientation(a, comp, quat);
     for (int k = 0; k < 3; ++k) m.body_pos.push_back(pos[k]);
     for (int k = 0; k < 4; ++k) m.body_quat.push_back(quat[k]);
     m.body_jtype.push_back(MJ_NONE);
@@ -290,38 +350,105 @@ struct Builder {
     for (int k = 0; k < 3; ++k) { m.jnt_axis.push_back(k == 2 ? 1.0 : 0.0); m.jnt_pos.push_back(0.0); }
     m.jnt_range.push_back(0.0); m.jnt_range.push_back(0.0);
     m.body_weld.push_back(0);
-    if (!e) return id;
-    int njoint = 0;
-    for (auto& ch : e->child) {
-      if (ch->tag != "joint" && ch->tag != "freejoint") continue;
-      if (++njoint > 1) throw std::runtime_error("body '" + m.body_name[id] + "': more than one joint per body is not supported");
-      if (id == 0) throw std::runtime_error("joint in the world body");
-      if (ch->tag == "freejoint") { m.body_jtype[id] = MJ_FREE; }
-      else {
-        AttrMap ja = resolve(*ch, childclass, false);
-        const std::string t = ja.count("type") ? ja["type"] : "hinge";
-        if (t == "hinge") m.body_jtype[id] = MJ_HINGE;
-        else if (t == "slide") m.body_jtype[id] = MJ_SLIDE;
-        else if (t == "free") m.body_jtype[id] = MJ_FREE;
-        else throw std::runtime_error("joint type '" + t + "' is not supported");
-        if (ja.count("axis")) { auto v = nums(ja["axis"]); if (v.size() != 3) throw std::runtime_error("joint axis needs 3 numbers"); normalize3(v.data()); for (int k = 0; k < 3; ++k) m.jnt_axis[3 * id + k] = v[k]; }
-        if (ja.count("pos")) { auto v = nums(ja["pos"]); if (v.size() != 3) throw std::runtime_error("joint pos needs 3 numbers"); for (int k = 0; k < 3; ++k) m.jnt_pos[3 * id + k] = v[k]; }
-        if (ja.count("range")) { auto v = nums(ja["range"]); if (v.size() == 2) { const double sc = (comp.degree && m.body_jtype[id] == MJ_HINGE) ? M_PI / 180.0 : 1.0; m.jnt_range[2 * id] = v[0] * sc; m.jnt_range[2 * id + 1] = v[1] * sc; } }
+    return id;
+  }
+
+  void set_joint(int id, int parent, const Item& it, const std::string& owner) {
+    const XmlNode& j = *it.node;
+    if (j.tag == "freejoint") { m.body_jtype[id] = MJ_FREE; }
+    else {
+      AttrMap ja = resolve(j, it.childclass, false);
+      const std::string t = ja.count("type") ? ja["type"] : "hinge";
+      if (t == "hinge") m.body_jtype[id] = MJ_HINGE;
+      else if (t == "slide") m.body_jtype[id] = MJ_SLIDE;
+      else if (t == "free") m.body_jtype[id] = MJ_FREE;
+      else throw std::runtime_error("body '" + owner + "': joint type '" + t + "' is not supported");
+      double axis[3] = {0, 0, 1}, jpos[3] = {0, 0, 0};
+      if (ja.count("axis")) { auto v = nums(ja["axis"]); if (v.size() != 3) throw std::runtime_error("joint axis needs 3 numbers"); for (int k = 0; k < 3; ++k) axis[k] = v[k]; }
+      if (ja.count("pos")) { auto v = nums(ja["pos"]); if (v.size() != 3) throw std::runtime_error("joint pos needs 3 numbers"); for (int k = 0; k < 3; ++k) jpos[k] = v[k]; }
+      normalize3(axis);
+      if (!it.frame.identity) {   // joint declared inside a <frame>: anchor and axis are given in that frame
+        double t3[3];
+        quat_rotate(it.frame.quat, axis, t3); for (int k = 0; k < 3; ++k) axis[k] = t3[k];
+        quat_rotate(it.frame.quat, jpos, t3); for (int k = 0; k < 3; ++k) jpos[k] = it.frame.pos[k] + t3[k];
       }
-      m.body_qadr[id] = m.nq;
-      if (m.body_jtype[id] == MJ_FREE) {
-        if (parent != 0) throw std::runtime_error("free joint below a non-world body");
-        for (int k = 0; k < 3; ++k) m.qpos0.push_back(pos[k]);
-        for (int k = 0; k < 4; ++k) m.qpos0.push_back(quat[k]);
-        m.nq += 7;
-      } else { m.qpos0.push_back(0.0); m.nq += 1; }
+      for (int k = 0; k < 3; ++k) { m.jnt_axis[3 * id + k] = axis[k]; m.jnt_pos[3 * id + k] = jpos[k]; }
+      if (ja.count("range")) { auto v = nums(ja["range"]); if (v.size() == 2) { const double sc = (comp.degree && m.body_jtype[id] == MJ_HINGE) ? M_PI / 180.0 : 1.0; m.jnt_range[2 * id] = v[0] * sc; m.jnt_range[2 * id + 1] = v[1] * sc; } }
+      // qpos is used as the joint displacement itself; a reference offset would shift every planned coordinate
+      if (ja.count("ref") && m.body_jtype[id] != MJ_FREE && nums(ja["ref"]).at(0) != 0.0)
+        throw std::runtime_error("body '" + owner + "': joint ref other than 0 is not supported");
     }
-    m.body_weld[id] = (m.body_jtype[id] != MJ_NONE) ? id : m.body_weld[parent];
-    for (auto& ch : e->child) if (ch->tag == "geom") add_geom(*ch, id, childclass);
-    for (auto& ch : e->child) if (ch->tag == "body") add_body(ch.get(), id, childclass);
+    m.body_qadr[id] = m.nq;
+    if (m.body_jtype[id] == MJ_FREE) {
+      if (parent != 0) throw std::runtime_error("free joint below a non-world body");
+      for (int k = 0; k < 3; ++k) m.qpos0.push_back(m.body_pos[3 * id + k]);
+      for (int k = 0; k < 4; ++k) m.qpos0.push_back(m.body_quat[4 * id + k]);
+      m.nq += 7;
+    } else { m.qpos0.push_back(0.0); m.nq += 1; }
+  }
+
+  // One MJCF body.  A body with several hinge / slide joints becomes a chain of bodies with one
+  // joint each (MuJoCo applies a body's joints in order, each in the frame the earlier ones left,
+  // which is what the chain does); the links of the chain share one weld id, so the collision
+  // filters (same body, parent-child) see them as the single body they stand for.
+  int add_body(const XmlNode* e, int parent, std::string childclass, const Pose& frame) {
+    AttrMap a;
+    if (e) for (auto& kv : e->attr) a[kv.first] = kv.second;
+    if (a.count("childclass")) childclass = a["childclass"];
+    double pos[3] = {0, 0, 0}, quat[4] = {1, 0, 0, 0};
+    if (a.count("pos")) { auto v = nums(a["pos"]); if (v.size() != 3) throw std::runtime_error("body pos needs 3 numbers"); for (int k = 0; k < 3; ++k) pos[k] = v[k]; }
+    orientation(a, comp, quat);
+    compose(frame, pos, quat);
+    const std::string name = a.count("name") ? a["name"] : (m.nbody == 0 ? "world" : "");
+    if (!name.empty() && m.body_id(name) >= 0) throw std::runtime_error("repeated body name '" + name + "'");
+    std::vector<Item> items;
+    if (e) collect(*e, Pose(), childclass, &items);
+    std::vector<const Item*> joints;
+    for (auto& it : items) if (it.node->tag == "joint" || it.node->tag == "freejoint") joints.push_back(&it);
+    if (!joints.empty() && m.nbody == 0) throw std::runtime_error("joint in the world body");
+    const double zero[3] = {0, 0, 0}, ident[4] = {1, 0, 0, 0};
+    int id = -1, top = -1;
+    const size_t nlinks = joints.empty() ? 1 : joints.size();
+    for (size_t l = 0; l < nlinks; ++l) {
+      const bool last = l + 1 == nlinks;
+      id = push_body(last ? name : std::string(), l == 0 ? parent : id, l == 0 ? pos : zero, l == 0 ? quat : ident);
+      if (l == 0) top = id;
+      if (!joints.empty()) {
+        set_joint(id, parent, *joints[l], name);
+        if (nlinks > 1 && m.body_jtype[id] == MJ_FREE) throw std::runtime_error("body '" + name + "': a free joint cannot be combined with other joints");
+      }
+      m.body_weld[id] = (m.body_jtype[id] != MJ_NONE) ? top : m.body_weld[m.body_parent[id]];
+    }
+    for (auto& it : items) if (it.node->tag == "geom") add_geom(*it.node, id, it.childclass, it.frame);
+    for (auto& it : items) if (it.node->tag == "body") add_body(it.node, id, it.childclass, it.frame);
     return id;
   }
 };
+
+// <include file="..."/> anywhere in the tree: the children of the included root take its place
+void expand_includes(XmlNode* n, const std::string& base_dir, int depth) {
+  if (depth > 16) throw std::runtime_error("<include> nesting deeper than 16 (a cycle?)");
+  std::vector<std::unique_ptr<XmlNode>> out;
+  for (auto& ch : n->child) {
+    if (ch->tag != "include") { expand_includes(ch.get(), base_dir, depth); out.push_back(std::move(ch)); continue; }
+    const std::string* f = ch->get("file");
+    if (!f) throw std::runtime_error("<include> needs a file attribute");
+    if (base_dir.empty() && (f->empty() || (*f)[0] != '/')) throw std::runtime_error("<include file='" + *f + "'> in a model given as text: no directory to resolve it against");
+    const std::string path = (!f->empty() && (*f)[0] == '/') ? *f : base_dir + "/" + *f;
+    std::ifstream in(path);
+    if (!in) throw std::runtime_error("cannot open included file '" + path + "'");
+    std::stringstream ss; ss << in.rdbuf();
+    const std::string text = ss.str();
+    XmlReader rd(text);
+    rd.skip_misc();
+    if (rd.i >= text.size()) throw std::runtime_error("included file '" + path + "' is empty");
+    std::unique_ptr<XmlNode> root = rd.element();
+    const size_t slash = path.find_last_of('/');
+    expand_includes(root.get(), slash == std::string::npos ? std::string(".") : path.substr(0, slash), depth + 1);
+    for (auto& g : root->child) out.push_back(std::move(g));
+  }
+  n->child = std::move(out);
+}
 
 }  // namespace
 
@@ -338,27 +465,40 @@ void quat_to_mat(const double* qi, double* R) {
   R[6] = 2 * (x * z - w * y);     R[7] = 2 * (y * z + w * x);     R[8] = 1 - 2 * (x * x + y * y);
 }
 
-FlatModel parse_mjcf(const std::string& text) {
+FlatModel parse_mjcf(const std::string& text, const std::string& base_dir) {
   XmlReader rd(text);
   rd.skip_misc();
   if (rd.i >= text.size()) throw std::runtime_error("empty MJCF document");
   std::unique_ptr<XmlNode> root = rd.element();
   if (root->tag != "mujoco") throw std::runtime_error("root element is <" + root->tag + ">, expected <mujoco>");
+  expand_includes(root.get(), base_dir, 0);
   Builder b;
   for (auto& ch : root->child) if (ch->tag == "compiler") {
-    if (const std::string* a = ch->get("angle")) b.comp.degree = (*a != "radian");
-    if (const std::string* a = ch->get("eulerseq")) { if (a->size() != 3) throw std::runtime_error("eulerseq needs 3 letters"); b.comp.eulerseq = *a; }
+    if (const std::string* a = ch->get("angle")) {
+      if (*a != "radian" && *a != "degree") throw std::runtime_error("compiler angle must be 'degree' or 'radian'");
+      b.comp.degree = (*a != "radian");
+    }
+    if (const std::string* a = ch->get("eulerseq")) {
+      if (a->size() != 3) throw std::runtime_error("eulerseq needs 3 letters");
+      for (char c : *a) if (std::tolower(c) < 'x' || std::tolower(c) > 'z') throw std::runtime_error("eulerseq letters must be x, y or z");
+      b.comp.eulerseq = *a;
+    }
+    if (const std::string* a = ch->get("coordinate")) if (*a != "local") throw std::runtime_error("compiler coordinate='" + *a + "' is not supported");
   }
   for (auto& ch : root->child) if (ch->tag == "default") b.read_defaults(*ch, DefaultClass(), true);
-  for (auto& ch : root->child) if (ch->tag == "include") throw std::runtime_error("<include> is not supported");
-  const XmlNode* world = nullptr;
-  for (auto& ch : root->child) if (ch->tag == "worldbody") world = ch.get();
-  if (!world) throw std::runtime_error("no <worldbody>");
-  b.add_body(nullptr, -1, "");
-  for (auto& ch : world->child) if (ch->tag == "geom") b.add_geom(*ch, 0, "");
-  for (auto& ch : world->child) if (ch->tag == "body") b.add_body(ch.get(), 0, "");
+  std::vector<const XmlNode*> worlds;          // several <worldbody> sections are merged, as MuJoCo does
+  for (auto& ch : root->child) if (ch->tag == "worldbody") worlds.push_back(ch.get());
+  if (worlds.empty()) throw std::runtime_error("no <worldbody>");
+  b.add_body(nullptr, -1, "", Pose());
+  std::vector<Builder::Item> items;
+  for (const XmlNode* w : worlds) b.collect(*w, Pose(), "", &items);
+  for (auto& it : items) if (it.node->tag == "joint" || it.node->tag == "freejoint") throw std::runtime_error("joint in the world body");
+  for (auto& it : items) if (it.node->tag == "geom") b.add_geom(*it.node, 0, it.childclass, it.frame);
+  for (auto& it : items) if (it.node->tag == "body") b.add_body(it.node, 0, it.childclass, it.frame);
   for (auto& ch : root->child) if (ch->tag == "contact")
-    for (auto& ex : ch->child) if (ex->tag == "exclude") {
+    for (auto& ex : ch->child) {
+      if (ex->tag == "pair") throw std::runtime_error("<contact><pair> (explicit geom pairs) is not supported");
+      if (ex->tag != "exclude") continue;
       const std::string* b1 = ex->get("body1"); const std::string* b2 = ex->get("body2");
       if (!b1 || !b2) throw std::runtime_error("<exclude> needs body1 and body2");
       const int i1 = b.m.body_id(*b1), i2 = b.m.body_id(*b2);
@@ -372,7 +512,8 @@ FlatModel load_mjcf(const std::string& path) {
   std::ifstream f(path);
   if (!f) throw std::runtime_error("Failed to load MuJoCo model from XML: cannot open '" + path + "'");
   std::stringstream ss; ss << f.rdbuf();
-  try { return parse_mjcf(ss.str()); }
+  const size_t slash = path.find_last_of('/');
+  try { return parse_mjcf(ss.str(), slash == std::string::npos ? std::string(".") : path.substr(0, slash)); }
   catch (const std::exception& e) { throw std::runtime_error(std::string("Failed to load MuJoCo model from XML: ") + e.what()); }
 }
 

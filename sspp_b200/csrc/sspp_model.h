@@ -29,9 +29,13 @@ struct FlatModel {
   int body_id(const std::string& name) const;
 };
 
-// Parse MJCF text.  Throws std::runtime_error with a message on malformed or unsupported input
-// (collidable meshes / height fields / ellipsoids, several joints in one body, ball joints).
-FlatModel parse_mjcf(const std::string& xml_text);
+// Parse MJCF text.  Supported subset: <compiler angle eulerseq>, nested <default> classes with
+// childclass, body trees with pos + quat/euler/axisangle/zaxis/xyaxes, <frame> wrappers, hinge /
+// slide / free joints (several hinge or slide joints in one body become a chain of one-joint
+// bodies sharing a weld id), primitive geoms incl. fromto, <contact><exclude>, <include> (resolved
+// against base_dir).  Throws std::runtime_error with a message on malformed or unsupported input
+// (collidable meshes / height fields / ellipsoids, ball joints, joint ref, explicit contact pairs).
+FlatModel parse_mjcf(const std::string& xml_text, const std::string& base_dir = std::string());
 FlatModel load_mjcf(const std::string& path);   // error text starts like the reference's: "Failed to load ..."
 
 // true when MuJoCo's filters let geoms g1, g2 generate contacts

@@ -67,6 +67,30 @@ def joint_case(n_samples=64, check_points=16, n_points=10, do_update=False, n_qu
     return Case(path, cfg, start, end, limits=np.full(7, np.pi), model=capi.Model(path=str(path)))
 
 
+# collision-free end points whose connecting paths are about 85 % free at the default noise (found by a seeded search)
+ARMLAB_START = np.array([1.704, -0.726, -0.67, 1.41, 0.307, 0.031])
+ARMLAB_END = np.array([-1.691, 0.745, -0.453, -1.473, 0.578, 0.008])
+
+
+def armlab_case(n_samples=64, check_points=16, n_points=10, do_update=False, n_queries=1, w_collision=0.0) -> Case:
+    """Planner A shape on fixtures/armlab.xml: 6 planned coordinates, two of them joints of one body, one a
+    slide joint inside a frame; capsule / sphere / cylinder / box partners."""
+    capi = _capi()
+    cfg = capi.default_config(capi.MODE_JOINT)
+    cfg.dof, cfg.degree, cfg.n_points = 6, 3, n_points
+    cfg.check_points, cfg.n_samples, cfg.n_queries = check_points, n_samples, n_queries
+    cfg.do_update = int(do_update)
+    cfg.w_collision = w_collision
+    cfg.stddev_min, cfg.stddev_max = 1e-4, 2.0
+    path = FIX / "armlab.xml"
+    rng = np.random.default_rng(9)
+    start = np.tile(ARMLAB_START, (n_queries, 1)); end = np.tile(ARMLAB_END, (n_queries, 1))
+    if n_queries > 1:
+        start[1:, :5] += rng.normal(0, 0.05, (n_queries - 1, 5)); end[1:, :5] += rng.normal(0, 0.05, (n_queries - 1, 5))
+    limits = np.array([np.pi, np.pi, np.pi, np.pi, np.pi, 0.04])
+    return Case(path, cfg, start, end, limits=limits, model=capi.Model(path=str(path)))
+
+
 def task_case(scene="robocrane.xml", body=ICRA_BODY, n_samples=15, check_points=40, n_points=3, n_queries=1,
               start=None, end=None, faithful_quirks=True) -> Case:
     """Planner B shape with the parameters of src/main_icra_benchmark.cpp:152-160.  faithful_quirks

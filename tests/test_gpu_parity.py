@@ -7,7 +7,7 @@ REL = 1e-5 relative."""
 import numpy as np
 import pytest
 
-from tests.helpers import SEED, compare_iteration, joint_case, task_case, o1_for, o2_for
+from tests.helpers import SEED, armlab_case, compare_iteration, joint_case, task_case, o1_for, o2_for
 
 pytestmark = pytest.mark.gpu
 REL = 1e-5
@@ -52,6 +52,18 @@ def test_task_stacking_scene():
                      end=np.array([-0.3, 0.3, 0.12, 1.0]))
     h = _handle(case)
     _assert_exact(compare_iteration(h, case, iters=4))
+    h.close()
+
+
+@pytest.mark.parametrize("n_samples,check_points,update", [(64, 16, True), (1000, 64, True)])
+def test_armlab_scene_iterations_match_oracles(n_samples, check_points, update):
+    """fixtures/armlab.xml: frames, a two-joint body (a chain of one-joint links in the kernel tables), a
+    slide joint, capsule / sphere / cylinder / box partners with per-class margins"""
+    case = armlab_case(n_samples=n_samples, check_points=check_points, do_update=update, w_collision=0.5)
+    h = _handle(case)
+    rep = compare_iteration(h, case, iters=3, eps_contact=2e-4)
+    _assert_exact(rep)
+    assert 0 < max(rep["n_success"]) < n_samples          # the start-goal pair has both outcomes
     h.close()
 
 
