@@ -165,8 +165,9 @@ int ssppcu_iterate_restored(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_it
 int ssppcu_sync(ssppcu_t* h);
 /* Diagnostics of the cooperative kernel: with enable != 0 every CTA stamps %globaltimer (ns) at the phase
  * boundaries of each launch's first iteration: [0] start, [1] scored, [2] past grid barrier 1, [3] ranked, [4] past
- * grid barrier 2, [5] updated, [6] rank keys staged, [7] rank counted.  stamps (may be NULL) receives
- * [min(cap_ctas, grid)][8] values of the last launch.  Returns the grid
+ * grid barrier 2, [5] updated, [6] rank keys staged, [7] rank counted; ssppcu_iterate_exchange adds [8] shard ordered, [9] keys
+ * published, [10] peers' flags seen, [11] merge ranked and stamps [5] when it is finished.  stamps (may be NULL)
+ * receives [min(cap_ctas, grid)][12] values of the last launch.  Returns the grid
  * size or a negative error. */
 int ssppcu_phase_probe(ssppcu_t* h, int enable, unsigned long long* stamps, int cap_ctas);
 
@@ -204,6 +205,26 @@ int ssppcu_merge_update(ssppcu_t* h, const unsigned long long* dev_gathered_keys
                         uint64_t seed, uint32_t iter);
 
 int ssppcu_get_merged(ssppcu_t* h, uint32_t* idx, float* cost, float* weight, int cap);
+
+/* ---- population sharding with the key exchange fused into the iteration kernel ----
+ * Instead of iterate + a collective + merge_update, every rank maps its peers' exchange blocks once;
+ * ssppcu_iterate_exchange is then ONE cooperative launch per iteration that scores and ranks the shard,
+ * stores the sorted keys into every peer's block over NVLink (8 bytes per candidate and peer), raises
+ * a flag on every peer, waits for the peers' flags, merges and applies the update - bit-identical to
+ * the unsharded handle on every rank, with no collective call and no host synchronisation.
+ *   1. ssppcu_exchange_export: allocates this rank's block (world equal shards, rank in [0, world));
+ *      *block_out (optional) = its device address (ranks that share a process), ipc_handle_out (optional) =
+ *      64 bytes of cudaIpcMemHandle_t to hand to the other processes (any transport: MPI, torch.distributed ...).
+ *   2. ssppcu_exchange_attach_ipc(handles[world][64]) or ssppcu_exchange_attach_ptrs(blocks[world]);
+ *      every rank must have exported before any rank attaches.
+ *   3. ssppcu_iterate_exchange once per iteration on every rank, in the same order everywhere.
+ * A peer that never publishes trips a 2 s device-side timeout: the launch ends, the next call (or
+ * ssppcu_exchange_status, which synchronises) returns SSPPCU_ECUDA; it never hangs the GPU. */
+int ssppcu_exchange_export(ssppcu_t* h, int world, int rank, void* block_out, void* ipc_handle_out);
+int ssppcu_exchange_attach_ipc(ssppcu_t* h, const void* handles);
+int ssppcu_exchange_attach_ptrs(ssppcu_t* h, void* const* blocks);
+int ssppcu_iterate_exchange(ssppcu_t* h, uint64_t seed, uint32_t iter);
+int ssppcu_exchange_status(ssppcu_t* h);
 
 /* ---- host-side spline algebra the handle applies (no device needed; FP64) ----
  * Restates Eigen's KnotAveraging + SplineFitting::Interpolate + Spline::operator() as the

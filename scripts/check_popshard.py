@@ -5,7 +5,7 @@ from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 import numpy as np, torch, torch.distributed as dist
 from sspp_b200 import capi
-from sspp_b200.sharding import DeviceShard, PopulationSharded, block_range
+from sspp_b200.sharding import DeviceShard, PopulationExchange, PopulationSharded, block_range
 from tests.helpers import task_case, SEED
 
 rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
@@ -33,5 +33,51 @@ with torch.cuda.stream(ps.b.stream):
     for it in range(3, 53): ps.iterate(SEED, it)
     ev[1].record()
 torch.cuda.synchronize()
-print(f"rank {rank}: {'OK' if ok else 'FAIL'}  sharded iteration {ev[0].elapsed_time(ev[1]) / 50:.3f} ms for {N} candidates x 64 points", flush=True)
+def report(what, good, ms):
+    rows = [None] * world
+    dist.all_gather_object(rows, (bool(good), float(ms)))
+    if rank == 0:
+        print(f"{what}: {'OK' if all(r[0] for r in rows) else 'FAIL ' + str([i for i, r in enumerate(rows) if not r[0]])} on {world} ranks, "
+              f"{max(r[1] for r in rows):.3f} ms per iteration (max over ranks) for {N} candidates x 64 points", flush=True)
+report("all-gather + merge", ok, ev[0].elapsed_time(ev[1]) / 50)
+
+# the same population with the exchange fused into the kernel (peer memory, no collective in the loop)
+px = PopulationExchange(mk(hi - lo, lo, N), torch.cuda.Stream())
+full2 = mk(N - 2); full2.set_stream(px.stream.cuda_stream)
+ok2 = True
+for it in range(3):
+    px.iterate(SEED, it); full2.iterate(SEED, it, 1)
+    px.check(); torch.cuda.synchronize()
+    fi, fc, fw = full2.elites(0); mi, mc, mw = px.h.merged(N)
+    m0, s0 = full2.get_distribution(); m1, s1 = px.h.get_distribution()
+    r0, r1 = full2.results(), px.h.results()
+    ok2 &= bool(np.array_equal(mi[:len(fi)], fi) and np.array_equal(mw[:len(fw)], fw) and np.array_equal(m0, m1) and np.array_equal(s0, s1)
+                and r0["n_success"][0] == r1["n_success"][0] and r0["best_idx"][0] == r1["best_idx"][0])
+torch.cuda.synchronize(); dist.barrier()
+with torch.cuda.stream(px.stream):
+    ev[0].record()
+    for it in range(3, 53): px.iterate(SEED, it)
+    ev[1].record()
+torch.cuda.synchronize(); px.check()
+report("fused exchange", ok2, ev[0].elapsed_time(ev[1]) / 50)
+px.h.phase_probe(True)
+tl = []
+for it in range(53, 63):
+    dist.barrier(); px.iterate(SEED, it); px.check()
+    st = px.h.phase_probe(True, read=True).astype(np.int64)
+    tl.append((st - st[:, 0].min()) * 1e-3)
+px.h.phase_probe(False)
+A = np.stack(tl[2:])
+names = {1: "scored", 3: "ranked", 8: "shard_ordered", 9: "published", 10: "flags_seen", 11: "merge_ranked", 5: "finished"}
+if rank == 0:
+    print("fused-exchange phases on rank 0 (us since launch start, min/median/max over CTAs): " +
+          ", ".join(f"{n} {A[:, :, i].min(axis=1).mean():.1f}/{np.median(A[:, :, i], axis=1).mean():.1f}/{A[:, :, i].max(axis=1).mean():.1f}" for i, n in names.items()), flush=True)
+t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+with torch.cuda.stream(px.stream):
+    t0.record()
+    for it in range(3, 13): full2.iterate(SEED, it, 1)
+    t1.record()
+torch.cuda.synchronize()
+if rank == 0: print(f"unsharded iteration on one GPU {t0.elapsed_time(t1) / 10:.3f} ms for {N} candidates x 64 points", flush=True)
+dist.barrier()
 dist.destroy_process_group()

@@ -91,6 +91,8 @@ SYMBOLS = [
     "ssppcu_get_collocation", "ssppcu_get_base", "ssppcu_shard_keys", "ssppcu_merge_update", "ssppcu_version",
     "ssppcu_spline_setup", "ssppcu_collocation_matrix", "ssppcu_save_state", "ssppcu_restore_state",
     "ssppcu_fp32_peak", "ssppcu_get_merged", "ssppcu_get_sdf", "ssppcu_get_spheres", "ssppcu_phase_probe", "ssppcu_iterate_restored",
+    "ssppcu_exchange_export", "ssppcu_exchange_attach_ipc", "ssppcu_exchange_attach_ptrs", "ssppcu_iterate_exchange",
+    "ssppcu_exchange_status",
 ]
 
 lib = _load()
@@ -134,6 +136,11 @@ lib.ssppcu_get_base.argtypes = [C.c_void_p, C.c_void_p]
 lib.ssppcu_shard_keys.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), _ip]
 lib.ssppcu_merge_update.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_uint32]
 lib.ssppcu_get_merged.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+lib.ssppcu_exchange_export.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+lib.ssppcu_exchange_attach_ipc.argtypes = [C.c_void_p, C.c_void_p]
+lib.ssppcu_exchange_attach_ptrs.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
+lib.ssppcu_iterate_exchange.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32]
+lib.ssppcu_exchange_status.argtypes = [C.c_void_p]
 lib.ssppcu_get_sdf.argtypes = [C.c_void_p, C.c_void_p, _ip, _dp, _dp]
 lib.ssppcu_get_spheres.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
 lib.ssppcu_save_state.argtypes = [C.c_void_p]
@@ -342,15 +349,16 @@ class Handle:
         self._ck(lib.ssppcu_sync(self._h))
 
     def phase_probe(self, enable: bool = True, read: bool = False):
-        """diagnostics of the cooperative kernel: per-CTA %globaltimer stamps [grid][8] of the last launch's first
-        iteration (start, scored, past barrier 1, ranked, past barrier 2, updated, rank keys staged, rank counted); None unless `read`"""
+        """diagnostics of the cooperative kernel: per-CTA %globaltimer stamps [grid][12] of the last launch's first
+        iteration (start, scored, past barrier 1, ranked, past barrier 2, updated, rank keys staged, rank counted; fused key
+        exchange: shard ordered, published, peers' flags seen, merge ranked - and `updated` = finished); None unless `read`"""
         lib.ssppcu_phase_probe.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
         grid = lib.ssppcu_phase_probe(self._h, int(enable), None, 0)
         if grid < 0:
             self._ck(grid)
         if not read:
             return None
-        out = np.zeros((grid, 8), np.uint64)
+        out = np.zeros((grid, 12), np.uint64)
         self._ck(min(0, lib.ssppcu_phase_probe(self._h, int(enable), out.ctypes.data_as(C.c_void_p), grid)))
         return out
 
@@ -434,6 +442,27 @@ class Handle:
 
     def merge_update(self, dev_keys_ptr: int, n_keys: int, n_shards: int, seed: int, it: int):
         self._ck(lib.ssppcu_merge_update(self._h, C.c_void_p(dev_keys_ptr), int(n_keys), int(n_shards), C.c_uint64(seed), C.c_uint32(it)))
+
+    # population shard with the key exchange fused into the kernel (ssppcu_exchange_*, include/sspp_cuda.h)
+    def exchange_export(self, world: int, rank: int) -> tuple[int, bytes]:
+        """allocate this rank's exchange block; returns (device address, 64-byte CUDA IPC handle)"""
+        blk = C.c_void_p(); ipc = C.create_string_buffer(64)
+        self._ck(lib.ssppcu_exchange_export(self._h, int(world), int(rank), C.byref(blk), ipc))
+        return blk.value, ipc.raw
+
+    def exchange_attach_ipc(self, handles: list[bytes]):
+        buf = b"".join(handles)
+        self._ck(lib.ssppcu_exchange_attach_ipc(self._h, C.c_char_p(buf)))
+
+    def exchange_attach_ptrs(self, blocks: list[int]):
+        arr = (C.c_void_p * len(blocks))(*blocks)
+        self._ck(lib.ssppcu_exchange_attach_ptrs(self._h, arr))
+
+    def iterate_exchange(self, seed: int, it: int):
+        self._ck(lib.ssppcu_iterate_exchange(self._h, C.c_uint64(seed), C.c_uint32(it)))
+
+    def exchange_status(self):
+        self._ck(lib.ssppcu_exchange_status(self._h))
 
     def merged(self, cap: int):
         idx = np.zeros(cap, np.uint32); cost = np.zeros(cap, np.float32); w = np.zeros(cap, np.float32)

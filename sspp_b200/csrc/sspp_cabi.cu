@@ -52,6 +52,19 @@ struct ssppcu_planner {
   unsigned char* d_res = nullptr; unsigned char* h_res = nullptr; size_t res_bytes = 0;
   size_t o_L = 0, o_Cnf = 0, o_Cwf = 0, o_cost = 0, o_status = 0, o_nsucc = 0, o_nelite = 0, o_bidx = 0, o_bcost = 0, o_extra = 0;
   unsigned char* h_stage = nullptr; size_t stage_bytes = 0, stage_at = 0;
+  // fused key exchange of a population shard (ssppcu_exchange_*): this rank's block, the peers' mappings
+  struct Exchange {
+    int world = 0, rank = 0;
+    unsigned epoch = 0;
+    bool attached = false;
+    unsigned char* block = nullptr; size_t block_bytes = 0;                  // 16-byte lines [2 halves][world][shard_len]
+    unsigned long long* d_gathered = nullptr;
+    void* ipc_mapped[kMaxExchangeRanks] = {};                                // cudaIpcOpenMemHandle results (to close)
+    ExchangeParams* d_params = nullptr;
+    int* d_ticket = nullptr;
+    int* h_status = nullptr; int* d_status = nullptr;                        // mapped pinned word
+    float* d_vals = nullptr;
+  } xc;
 };
 
 namespace {
@@ -189,6 +202,13 @@ void ssppcu_destroy(ssppcu_t* h) {
   if (h->d_eval_pts) cudaFree(h->d_eval_pts);
   if (h->d_eval_out) cudaFree(h->d_eval_out);
   if (h->d_merge_keys) cudaFree(h->d_merge_keys);
+  for (void* m : h->xc.ipc_mapped) if (m) cudaIpcCloseMemHandle(m);
+  if (h->xc.block) cudaFree(h->xc.block);
+  if (h->xc.d_params) cudaFree(h->xc.d_params);
+  if (h->xc.d_ticket) cudaFree(h->xc.d_ticket);
+  if (h->xc.d_vals) cudaFree(h->xc.d_vals);
+  if (h->xc.d_gathered) cudaFree(h->xc.d_gathered);
+  if (h->xc.h_status) cudaFreeHost(h->xc.h_status);
   if (h->d_probe) cudaFree(h->d_probe);
   if (h->d_res) cudaFree(h->d_res);
   if (h->h_res) cudaFreeHost(h->h_res);
@@ -389,6 +409,7 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
   rc |= dalloc(h, &P.params, Q * N * nfd);
   rc |= dalloc(h, &P.keys, Q * P.n_pad); rc |= dalloc(h, &P.keys_raw, Q * P.n_pad); rc |= dalloc(h, &P.elite_w, Q * P.n_pad);
   rc |= dalloc(h, &P.succ_acc, Q);
+  rc |= dalloc(h, &P.tile_counter, 1);
   {
     size_t off = 0;
     auto take = [&](size_t bytes) { const size_t o = off; off += (bytes + 15) & ~(size_t)15; return o; };
@@ -822,10 +843,7 @@ int ssppcu_shard_keys(ssppcu_t* h, unsigned long long** keys, int32_t* n) {
   return SSPPCU_OK;
 }
 
-int ssppcu_merge_update(ssppcu_t* h, const unsigned long long* gathered, int n_keys, int n_shards, uint64_t seed, uint32_t iter) {
-  if (int rc = check(h)) return rc;
-  if (!gathered || n_keys < 1 || n_shards < 1 || n_keys % n_shards) return fail(h, SSPPCU_EINVAL, "bad arguments: n_keys must be n_shards equal shards");
-  if (h->cfg.shard_global <= 0) return fail(h, SSPPCU_EINVAL, "handle is not a population shard");
+static int ensure_merge_buffers(ssppcu_t* h, int n_keys) {
   const int n_pad = next_pow2(std::max(2, n_keys));
   const int nfd = h->P.cfg.n_free * h->P.cfg.D;
   if (n_pad > h->merge_cap) {
@@ -834,6 +852,16 @@ int ssppcu_merge_update(ssppcu_t* h, const unsigned long long* gathered, int n_k
     CU(h, cudaMalloc(&h->d_merge_keys, (size_t)n_pad * (sizeof(unsigned long long) + sizeof(float)) + (3 * nfd + 2) * sizeof(float)));
     h->merge_cap = n_pad;
   }
+  return SSPPCU_OK;
+}
+
+int ssppcu_merge_update(ssppcu_t* h, const unsigned long long* gathered, int n_keys, int n_shards, uint64_t seed, uint32_t iter) {
+  if (int rc = check(h)) return rc;
+  if (!gathered || n_keys < 1 || n_shards < 1 || n_shards > kMaxExchangeRanks || n_keys % n_shards) return fail(h, SSPPCU_EINVAL, "bad arguments: n_keys must be n_shards (at most 16) equal shards");
+  if (h->cfg.shard_global <= 0) return fail(h, SSPPCU_EINVAL, "handle is not a population shard");
+  if (h->xc.attached) return fail(h, SSPPCU_EINVAL, "this handle exchanges keys itself (ssppcu_iterate_exchange)");
+  if (int rc = ensure_merge_buffers(h, n_keys)) return rc;
+  const int n_pad = h->merge_cap;
   MergeParams M;
   std::memset(&M, 0, sizeof(M));
   M.cfg = h->P.cfg;
@@ -850,6 +878,108 @@ int ssppcu_merge_update(ssppcu_t* h, const unsigned long long* gathered, int n_k
   CU(h, cudaMemsetAsync(h->P.succ_acc, 0, sizeof(int), h->stream));
   CU(h, launch_merge_update(M, h->stream));
   h->merged_n = n_keys;
+  return SSPPCU_OK;
+}
+
+// ---- fused key exchange over peer memory (population shards) ----
+int ssppcu_exchange_export(ssppcu_t* h, int world, int rank, void* block_out, void* ipc_handle_out) {
+  if (int rc = check(h)) return rc;
+  if (h->cfg.shard_global <= 0) return fail(h, SSPPCU_EINVAL, "handle is not a population shard");
+  if (!h->P.coop) return fail(h, SSPPCU_EINVAL, "the fused exchange needs the cooperative kernel (shard too small)");
+  if (world < 1 || world > kMaxExchangeRanks || rank < 0 || rank >= world) return fail(h, SSPPCU_EINVAL, "bad world / rank");
+  if ((long long)h->P.cfg.n_cand * world != h->cfg.shard_global) return fail(h, SSPPCU_EINVAL, "shards must be equal: n_local * world != shard_global");
+  if (h->xc.block) return fail(h, SSPPCU_EINVAL, "exchange block already exported");
+  auto& x = h->xc;
+  x.world = world; x.rank = rank; x.epoch = 0; x.attached = false;
+  x.block_bytes = (size_t)2 * world * h->P.cfg.n_cand * sizeof(uint4);
+  CU(h, cudaMalloc(&x.d_gathered, (size_t)world * h->P.cfg.n_cand * sizeof(unsigned long long)));
+  CU(h, cudaMalloc(&x.block, x.block_bytes));
+  CU(h, cudaMemset(x.block, 0, x.block_bytes));
+  CU(h, cudaMalloc(&x.d_params, sizeof(ExchangeParams)));
+  CU(h, cudaMalloc(&x.d_ticket, sizeof(int)));
+  CU(h, cudaMemset(x.d_ticket, 0, sizeof(int)));
+  CU(h, cudaHostAlloc(&x.h_status, sizeof(int), cudaHostAllocMapped));
+  *x.h_status = 0;
+  CU(h, cudaHostGetDevicePointer(&x.d_status, x.h_status, 0));
+  CU(h, cudaDeviceSynchronize());                      // the zeroed lines (epoch 0 = nothing published) exist before any peer can learn the address
+  if (block_out) *reinterpret_cast<void**>(block_out) = x.block;
+  if (ipc_handle_out) {
+    cudaIpcMemHandle_t ih;
+    CU(h, cudaIpcGetMemHandle(&ih, x.block));
+    static_assert(sizeof(ih) == 64, "ipc handle size");
+    std::memcpy(ipc_handle_out, &ih, sizeof(ih));
+  }
+  return SSPPCU_OK;
+}
+
+static int exchange_finish_attach(ssppcu_t* h, void* const* bases) {
+  auto& x = h->xc;
+  const int n_keys = x.world * h->P.cfg.n_cand;
+  if (int rc = ensure_merge_buffers(h, n_keys)) return rc;
+  const int nfd = h->P.cfg.n_free * h->P.cfg.D;
+  ExchangeParams E;
+  std::memset(&E, 0, sizeof(E));
+  E.world = x.world; E.rank = x.rank; E.shard_len = h->P.cfg.n_cand;
+  E.n_global = h->cfg.shard_global; E.n_pad = h->merge_cap;
+  for (int r = 0; r < x.world; ++r) E.peer_lines[r] = reinterpret_cast<uint4*>(bases[r]);
+  E.lines_local = reinterpret_cast<const uint4*>(x.block);
+  E.gathered = x.d_gathered;
+  E.succ = x.d_ticket; E.status = x.d_status;
+  E.timeout_ns = 2000000000ull;
+  E.mkeys = h->d_merge_keys;
+  E.elite_w = reinterpret_cast<float*>(h->d_merge_keys + h->merge_cap);
+  E.state0 = E.elite_w + h->merge_cap;
+  CU(h, cudaMalloc(&x.d_vals, (size_t)std::max(1, nfd) * h->merge_cap * sizeof(float)));
+  E.vals = x.d_vals;
+  CU(h, cudaMemcpy(x.d_params, &E, sizeof(E), cudaMemcpyHostToDevice));
+  x.attached = true;
+  return SSPPCU_OK;
+}
+
+int ssppcu_exchange_attach_ipc(ssppcu_t* h, const void* handles) {
+  if (int rc = check(h)) return rc;
+  auto& x = h->xc;
+  if (!x.block || !handles) return fail(h, SSPPCU_EINVAL, "export the exchange block first");
+  if (x.attached) return fail(h, SSPPCU_EINVAL, "already attached");
+  void* bases[kMaxExchangeRanks] = {};
+  for (int r = 0; r < x.world; ++r) {
+    if (r == x.rank) { bases[r] = x.block; continue; }
+    cudaIpcMemHandle_t ih;
+    std::memcpy(&ih, reinterpret_cast<const unsigned char*>(handles) + (size_t)r * sizeof(ih), sizeof(ih));
+    cudaError_t e = cudaIpcOpenMemHandle(&bases[r], ih, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) return cuda_fail(h, e, "cudaIpcOpenMemHandle (peer exchange block)");
+    x.ipc_mapped[r] = bases[r];
+  }
+  return exchange_finish_attach(h, bases);
+}
+
+int ssppcu_exchange_attach_ptrs(ssppcu_t* h, void* const* blocks) {
+  if (int rc = check(h)) return rc;
+  auto& x = h->xc;
+  if (!x.block || !blocks) return fail(h, SSPPCU_EINVAL, "export the exchange block first");
+  if (x.attached) return fail(h, SSPPCU_EINVAL, "already attached");
+  if (blocks[x.rank] != x.block) return fail(h, SSPPCU_EINVAL, "blocks[rank] is not this handle's block");
+  return exchange_finish_attach(h, blocks);
+}
+
+int ssppcu_iterate_exchange(ssppcu_t* h, uint64_t seed, uint32_t iter) {
+  if (int rc = check(h)) return rc;
+  auto& x = h->xc;
+  if (!x.attached) return fail(h, SSPPCU_EINVAL, "exchange blocks are not attached");
+  if (*reinterpret_cast<volatile int*>(x.h_status)) return fail(h, SSPPCU_ECUDA, "key exchange timed out: a peer rank did not publish its keys");
+  IterParams P = h->P;
+  P.seed = seed; P.iter0 = iter; P.n_inner = 1; P.state_in = nullptr;
+  P.xchg = x.d_params; P.xchg_epoch = ++x.epoch;
+  CU(h, launch_iterate(h->view, P, h->variant, h->threads, h->smem + h->smem_model, h->grid, h->stream));
+  h->merged_n = x.world * h->P.cfg.n_cand;
+  return SSPPCU_OK;
+}
+
+int ssppcu_exchange_status(ssppcu_t* h) {
+  if (int rc = check(h)) return rc;
+  if (!h->xc.h_status) return fail(h, SSPPCU_EINVAL, "no exchange block");
+  CU(h, cudaStreamSynchronize(h->stream));
+  if (*reinterpret_cast<volatile int*>(h->xc.h_status)) return fail(h, SSPPCU_ECUDA, "key exchange timed out: a peer rank did not publish its keys");
   return SSPPCU_OK;
 }
 

@@ -633,6 +633,99 @@ __device__ void update_phase(const IterParams& P, float* s_part, float* s_val, i
   }
 }
 
+// ---- population shard with the fused key exchange (ExchangeParams, sspp_kernels.h) ----
+__device__ __forceinline__ void merge_rank_body(const MergeParams& P, int block, int n_blocks, unsigned long long* s_keys, int cap_keys);
+// regenerate a candidate's sampled element from the Philox counters (population-sharded path)
+struct RegenParams {
+  const ScoreConfig* c; uint64_t seed; uint32_t iter; const float* mean0; const float* sigma0; const float* best0; int best_ok;
+  __device__ __forceinline__ float operator()(unsigned idx, int t) const {
+    const int kind = candidate_kind(*c, (int)idx, best_ok);
+    return candidate_param(*c, seed, iter, 0u, (int)idx, kind, t, mean0, sigma0, best0);
+  }
+};
+__device__ __forceinline__ void merge_finish_body(const MergeParams& P, float* s_part, int block, int n_blocks, const float* vals = nullptr, int vals_pitch = 0);
+
+__device__ __forceinline__ void st_line(uint4* p, unsigned long long key, unsigned epoch) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};"
+               :: "l"(p), "r"((unsigned)key), "r"(epoch), "r"((unsigned)(key >> 32)), "r"(epoch) : "memory");
+}
+__device__ __forceinline__ uint4 ld_line(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+
+template <class Stamp>
+__device__ void exchange_and_merge(const IterParams& P, cg::grid_group& grid, float* s_part, uint32_t iter, unsigned char* smem_raw, Stamp stamp) {
+  __shared__ MergeParams s_mp;
+  const ExchangeParams& X = *P.xchg;
+  const int tid = threadIdx.x, T = blockDim.x;
+  const int W = X.world, len = X.shard_len, me = X.rank;
+  const unsigned epoch = P.xchg_epoch, half = epoch & 1u;
+  int* succ = X.succ;
+  if (blockIdx.x == 0 && tid == 0) *succ = 0;
+  grid.sync();                                          // the shard's sorted order is complete
+  stamp(8);
+  // publish: key j of this shard -> line (half, this rank, j) of every rank's block, its own included
+  const size_t slot = ((size_t)half * W + me) * len;
+  const long long total = (long long)W * len;
+  for (long long e = (long long)blockIdx.x * T + tid; e < total; e += (long long)gridDim.x * T) {
+    const int j = (int)(e / W), r = (int)(e - (long long)j * W);      // neighbouring threads feed different links
+    st_line(X.peer_lines[r] + slot + j, __ldcg(P.keys + j), epoch);
+  }
+  stamp(9);
+  // receive: poll every line of this epoch's half until both flag words carry the epoch; keys go to a compact array
+  const uint4* lines = X.lines_local + (size_t)half * W * len;
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  for (long long e = (long long)blockIdx.x * T + tid; e < total; e += (long long)gridDim.x * T) {
+    uint4 v = ld_line(lines + e);
+    while (v.y != epoch || v.w != epoch) {
+      unsigned long long t1;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (t1 - t0 > X.timeout_ns) { *reinterpret_cast<volatile int*>(X.status) = 1; break; }
+      __nanosleep(100);
+      v = ld_line(lines + e);
+    }
+    X.gathered[e] = (unsigned long long)v.x | ((unsigned long long)v.z << 32);
+  }
+  grid.sync();
+  stamp(10);
+  if (tid == 0) {
+    MergeParams& M = s_mp;
+    M.cfg = P.cfg; M.cfg.n_cand = X.n_global;
+    M.n_keys = W * len; M.n_shards = W; M.shard_len = len; M.n_pad = X.n_pad;
+    M.iter = iter; M.seed = P.seed;
+    M.gathered = X.gathered;
+    M.keys = X.mkeys; M.elite_w = X.elite_w; M.state0 = X.state0; M.succ_acc = succ;
+    M.mean = P.mean; M.sigma = P.sigma; M.best = P.best; M.best_valid = P.best_valid;
+    M.n_success = P.n_success; M.n_elite = P.n_elite; M.best_idx = P.best_idx; M.best_cost = P.best_cost;
+    M.any_success = P.any_success;
+  }
+  __syncthreads();
+  merge_rank_body(s_mp, blockIdx.x, gridDim.x, reinterpret_cast<unsigned long long*>(smem_raw), P.smem_words / 2);
+  stamp(11);
+  grid.sync();
+  // the elites' sampled values come back from the Philox counters (only keys crossed NVLink): regenerate them with the
+  // whole grid into vals[element][elite], then the update reads them like the unsharded kernel reads its stored rows
+  const ScoreConfig& cg = s_mp.cfg;
+  const int nfd = cg.n_free * cg.D;
+  const int n_succ = __ldcg(succ);
+  const int k = elite_count(n_succ, cg.elite_frac);
+  if (cg.do_update && n_succ > 0) {
+    const int best_ok0 = cg.include_best ? __ldcg(reinterpret_cast<const int*>(X.state0) + 3 * nfd) : 0;
+    RegenParams gp{&cg, P.seed, iter, X.state0, X.state0 + nfd, X.state0 + 2 * nfd, best_ok0};
+    const long long items = (long long)nfd * k;
+    for (long long e = (long long)blockIdx.x * T + tid; e < items; e += (long long)gridDim.x * T) {
+      const int t = (int)(e / k), j = (int)(e - (long long)t * k);
+      X.vals[(size_t)t * X.n_pad + j] = gp((unsigned)(__ldcg(X.mkeys + j) & 0xFFFFFFFFu), t);
+    }
+    grid.sync();
+  }
+  merge_finish_body(s_mp, s_part, blockIdx.x, gridDim.x, X.vals, X.n_pad);
+  stamp(5);
+}
+
 // Launch-bound variants: (max threads, min CTAs per SM) fixes the register budget ptxas works with, and so
 // the resident warps per SM; the handle picks one per problem shape (kIterVariants, sspp_kernels.h).
 template <bool COOP, int MAXT, int MINB>
@@ -707,20 +800,30 @@ sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant_
     }
     // ---- phase A: score the tiles ----
     load_basis(s, c, P, tid, T);                         // phase B reuses this shared memory
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+    const bool handout = P.n_tiles > (int)gridDim.x;     // first wave by CTA index, the rest first come first served:
+    for (int tile = blockIdx.x; tile < P.n_tiles;) {     // tiles differ in cost (culling), a fixed assignment leaves a tail
       const int query = tile / P.ctas_per_query;
       const int c0 = (tile - query * P.ctas_per_query) * P.cand_per_cta;
       const int nc = min(P.cand_per_cta, c.n_cand - c0);
       score_tile(M, P, s, query, c0, nc, P.iter0 + (uint32_t)it, from_saved);
+      if (!handout) { __syncthreads(); break; }
+      if (tid == 0) s_int[0] = (int)gridDim.x + atomicAdd(P.tile_counter, 1);
       __syncthreads();
+      tile = s_int[0];
+      __syncthreads();                                   // everybody has read the ticket before thread 0 can draw the next
     }
     stamp(it, 1);
     grid.sync();
     stamp(it, 2);
+    if (handout && blockIdx.x == 0 && tid == 0) *P.tile_counter = 0;   // nobody draws again before the next iteration's barrier
     // ---- phase B: order the keys ----
     rank_phase(P, smem_raw, &s_mbar, mbar_phase, [&](int slot) { stamp(it, slot); });
     stamp(it, 3);
-    if (P.sort_only) { if (it + 1 < P.n_inner) grid.sync(); continue; }
+    if (P.sort_only) {
+      if (P.xchg) exchange_and_merge(P, grid, s_part, P.iter0 + (uint32_t)it, smem_raw, [&](int slot) { stamp(it, slot); });
+      if (it + 1 < P.n_inner) grid.sync();
+      continue;
+    }
     grid.sync();
     stamp(it, 4);
     // ---- phase C: distribution update ----
@@ -730,60 +833,126 @@ sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant_
   }
 }
 
-// regenerate a candidate's sampled element from the Philox counters (population-sharded path)
-struct RegenParams {
-  const ScoreConfig* c; uint64_t seed; uint32_t iter; const float* mean0; const float* sigma0; const float* best0; int best_ok;
-  __device__ __forceinline__ float operator()(unsigned idx, int t) const {
-    const int kind = candidate_kind(*c, (int)idx, best_ok);
-    return candidate_param(*c, seed, iter, 0u, (int)idx, kind, t, mean0, sigma0, best0);
-  }
-};
 
-__global__ void __launch_bounds__(256)
-sspp_merge_rank_kernel(const __grid_constant__ MergeParams P) {
+// count of keys < key in the ascending run a[0..n)
+__device__ __forceinline__ int lower_bound_cg(const unsigned long long* a, int n, unsigned long long key) {
+  int lo = 0, hi = n;
+  while (lo < hi) { const int mid = (lo + hi) >> 1; if (__ldcg(a + mid) < key) lo = mid + 1; else hi = mid; }
+  return lo;
+}
+// the same by a whole warp: 32 probes per round cut the run 32-fold (3 rounds of L2 latency for 8192 keys instead of 13)
+__device__ __forceinline__ int lower_bound_warp(const unsigned long long* a, int n, unsigned long long key, int lane) {
+  int lo = 0, hi = n;
+  while (hi > lo) {
+    const int seg = (hi - lo + 31) >> 5;
+    const int q = lo + lane * seg;
+    const bool less = q < hi && __ldcg(a + q) < key;
+    const int cnt = __popc(__ballot_sync(0xFFFFFFFFu, less));   // the probes are ascending: the first cnt of them are smaller
+    if (cnt == 0) { hi = lo; break; }
+    const int nlo = lo + (cnt - 1) * seg + 1;
+    hi = min(hi, lo + cnt * seg);
+    lo = nlo;
+  }
+  return lo;
+}
+__device__ __forceinline__ int lower_bound_smem(const unsigned long long* a, int n, unsigned long long key) {
+  int lo = 0, hi = n;
+  while (lo < hi) { const int mid = (lo + hi) >> 1; if (a[mid] < key) lo = mid + 1; else hi = mid; }
+  return lo;
+}
+
+// Merge-rank over a virtual grid of n_blocks CTAs (this one is `block`).  A CTA takes T consecutive keys of one
+// shard; their positions in another shard all lie in the window between the positions of the first and the last
+// of them, so two binary searches per shard and CTA (not per key) find the windows, the windows are staged in
+// shared memory (s_keys, cap_keys entries; a window that does not fit is searched in place), and every thread
+// finishes its key with short searches there.  Position = own position + the counts in the other shards.
+__device__ __forceinline__ void merge_rank_body(const MergeParams& P, int block, int n_blocks, unsigned long long* s_keys, int cap_keys) {
+  __shared__ int s_wlo[kMaxExchangeRanks], s_wn[kMaxExchangeRanks], s_woff[kMaxExchangeRanks];
   const ScoreConfig& c = P.cfg;
-  const int nfd = c.n_free * c.D;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (blockIdx.x == 0) {           // snapshot of the state the elites were sampled from
-    for (int t = threadIdx.x; t < nfd; t += blockDim.x) {
+  const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31;
+  const int nfd = c.n_free * c.D, W = P.n_shards, len = P.shard_len;
+  if (block == 0) {            // snapshot of the state the elites were sampled from
+    for (int t = tid; t < nfd; t += T) {
       P.state0[t] = P.mean[t]; P.state0[nfd + t] = P.sigma[t]; P.state0[2 * nfd + t] = P.best[t];
     }
-    if (threadIdx.x == 0) reinterpret_cast<int*>(P.state0)[3 * nfd] = *P.best_valid;
+    if (tid == 0) reinterpret_cast<int*>(P.state0)[3 * nfd] = *P.best_valid;
   }
-  for (int k = P.n_keys + i; k < P.n_pad; k += gridDim.x * blockDim.x) P.keys[k] = ~0ull;
-  int succ_hi = 0;
-  if (i < P.n_keys) {
-    const int shard = i / P.shard_len;
-    const unsigned long long key = P.gathered[i];
-    int rank = i - shard * P.shard_len;
-    for (int s = 0; s < P.n_shards; ++s) {
-      if (s == shard) continue;
-      const unsigned long long* a = P.gathered + (size_t)s * P.shard_len;
-      int lo = 0, hi = P.shard_len;                 // first position with a[pos] >= key
-      while (lo < hi) { const int mid = (lo + hi) >> 1; if (a[mid] < key) lo = mid + 1; else hi = mid; }
-      rank += lo;
+  for (int k = P.n_keys + block * T + tid; k < P.n_pad; k += n_blocks * T) P.keys[k] = ~0ull;
+  const int chunks = (len + T - 1) / T;
+  for (int item = block; item < W * chunks; item += n_blocks) {
+    const int shard = item / chunks, p0 = (item - shard * chunks) * T;
+    const int n_mine = min(T, len - p0);
+    const unsigned long long* mine = P.gathered + (size_t)shard * len + p0;
+    const unsigned long long key = (tid < n_mine) ? __ldcg(mine + tid) : ~0ull;
+    // Failed keys order by candidate index alone, successful ones by cost: a chunk that holds the last successes and the
+    // first failures of its shard would span most of every other shard.  Such a chunk is merged in two parts.
+    const int n_ok = __syncthreads_count(tid < n_mine && key_success(key));
+    const int n_parts = (n_ok > 0 && n_ok < n_mine) ? 2 : 1;
+    int succ_hi = 0;
+    for (int part = 0; part < n_parts; ++part) {
+      const int a0 = (part == 0) ? 0 : n_ok, a1 = (n_parts == 1 || part == 1) ? n_mine : n_ok;
+      __syncthreads();                                   // the previous windows have been consumed
+      for (int b = tid >> 5; b < 2 * W; b += T >> 5) {   // window bounds, one warp each: 2s -> first key, 2s+1 -> last key, in shard s
+        const int s2 = b >> 1;
+        if (s2 == shard) continue;
+        const unsigned long long bound = __ldcg(mine + ((b & 1) ? a1 - 1 : a0));
+        const int pos = lower_bound_warp(P.gathered + (size_t)s2 * len, len, bound, lane);
+        if (lane == 0) { if (b & 1) s_wn[s2] = pos; else s_wlo[s2] = pos; }
+      }
+      __syncthreads();
+      if (tid == 0) {                                    // window lengths and their places in the staging buffer
+        int off = 0;
+        for (int s2 = 0; s2 < W; ++s2) {
+          if (s2 == shard) { s_wn[s2] = 0; s_woff[s2] = -1; continue; }
+          const int n = s_wn[s2] - s_wlo[s2];
+          s_wn[s2] = n;
+          if (off + n <= cap_keys) { s_woff[s2] = off; off += n; } else s_woff[s2] = -1;
+        }
+      }
+      __syncthreads();
+      for (int s2 = 0; s2 < W; ++s2) {
+        const int off = s_woff[s2];
+        if (off < 0) continue;
+        const unsigned long long* w = P.gathered + (size_t)s2 * len + s_wlo[s2];
+        for (int j = tid; j < s_wn[s2]; j += T) s_keys[off + j] = __ldcg(w + j);
+      }
+      __syncthreads();
+      if (tid >= a0 && tid < a1) {
+        int rank = p0 + tid;
+        for (int s2 = 0; s2 < W; ++s2) {
+          if (s2 == shard) continue;
+          const int off = s_woff[s2];
+          rank += s_wlo[s2] + (off >= 0 ? lower_bound_smem(s_keys + off, s_wn[s2], key)
+                                        : lower_bound_cg(P.gathered + (size_t)s2 * len + s_wlo[s2], s_wn[s2], key));
+        }
+        P.keys[rank] = key;
+        if (key_success(key)) succ_hi = rank + 1;
+      }
     }
-    P.keys[rank] = key;
-    if (key_success(key)) succ_hi = rank + 1;
+    succ_hi = __reduce_max_sync(0xFFFFFFFFu, succ_hi);
+    if (lane == 0 && succ_hi) atomicMax(P.succ_acc, succ_hi);
   }
-  succ_hi = __reduce_max_sync(0xFFFFFFFFu, succ_hi);
-  if ((threadIdx.x & 31) == 0 && succ_hi) atomicMax(P.succ_acc, succ_hi);
 }
 
 __global__ void __launch_bounds__(256)
-sspp_merge_finish_kernel(const __grid_constant__ MergeParams P) {     // one CTA per distribution element (+1: the scalars)
-  __shared__ float s_part[8];
+sspp_merge_rank_kernel(const __grid_constant__ MergeParams P) {
+  __shared__ unsigned long long s_keys[2048];
+  merge_rank_body(P, blockIdx.x, gridDim.x, s_keys, 2048);
+}
+
+// finish over a virtual grid of n_blocks CTAs (this one is `block`): one CTA per distribution element (+1: the scalars)
+__device__ __forceinline__ void merge_finish_body(const MergeParams& P, float* s_part, int block, int n_blocks, const float* vals, int vals_pitch) {
   const ScoreConfig& c = P.cfg;
   const int tid = threadIdx.x, T = blockDim.x;
   const int nfd = c.n_free * c.D;
-  const int n_succ = *P.succ_acc;
+  const int n_succ = __ldcg(P.succ_acc);
   const int k = elite_count(n_succ, c.elite_frac);
-  const int best_ok0 = c.include_best ? reinterpret_cast<const int*>(P.state0)[3 * nfd] : 0;
+  const int best_ok0 = c.include_best ? __ldcg(reinterpret_cast<const int*>(P.state0) + 3 * nfd) : 0;
   RegenParams gp{&c, P.seed, P.iter, P.state0, P.state0 + nfd, P.state0 + 2 * nfd, best_ok0};
-  for (int t = blockIdx.x; t <= nfd; t += gridDim.x) {
+  for (int t = block; t <= nfd; t += n_blocks) {
     if (t == nfd) {
       if (tid == 0) { *P.n_success = n_succ; *P.n_elite = k; }
-      const unsigned long long k0 = P.keys[0];
+      const unsigned long long k0 = __ldcg(P.keys);
       if (n_succ > 0) {
         if (tid == 0) { *P.best_idx = (int)(unsigned)(k0 & 0xFFFFFFFFu); *P.best_cost = key_cost(k0); *P.any_success = 1; *P.best_valid = 1; }
         for (int e = tid; e < nfd; e += T) P.best[e] = gp((unsigned)(k0 & 0xFFFFFFFFu), e);
@@ -797,8 +966,15 @@ sspp_merge_finish_kernel(const __grid_constant__ MergeParams P) {     // one CTA
     if (n_succ == 0) { if (tid == 0) P.sigma[t] = clamp_sigma(c, P.sigma[t] * c.inc); continue; }
     const float lk = log_poly((float)k + 0.5f);
     const float sumw = ces_weight_sum(k, lk, CtaSum{s_part});
-    update_element(c, k, lk, sumw, t, P.mean, P.sigma, [&](int j) { return gp((unsigned)(P.keys[j] & 0xFFFFFFFFu), t); }, CtaSum{s_part}, tid == 0);
+    if (vals) update_element(c, k, lk, sumw, t, P.mean, P.sigma, [&](int j) { return __ldcg(vals + (size_t)t * vals_pitch + j); }, CtaSum{s_part}, tid == 0);
+    else update_element(c, k, lk, sumw, t, P.mean, P.sigma, [&](int j) { return gp((unsigned)(__ldcg(P.keys + j) & 0xFFFFFFFFu), t); }, CtaSum{s_part}, tid == 0);
   }
+}
+
+__global__ void __launch_bounds__(256)
+sspp_merge_finish_kernel(const __grid_constant__ MergeParams P) {
+  __shared__ float s_part[8];
+  merge_finish_body(P, s_part, blockIdx.x, gridDim.x);
 }
 
 __global__ void __launch_bounds__(128)

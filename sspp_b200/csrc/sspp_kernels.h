@@ -45,7 +45,31 @@ struct IterParams {
   int* n_success; int* n_elite; int* best_idx; int* any_success;   // [Q]
   float* best_cost;         // [Q]
   int* succ_acc;            // [Q] scratch: success count accumulated by the ranking phase
+  int* tile_counter;        // coop, more tiles than CTAs: tiles beyond the first wave are handed out from this counter (zero between iterations)
+  const struct ExchangeParams* xchg;  // population shard with the fused key exchange (device-resident block), else NULL
+  unsigned xchg_epoch;      // value this launch publishes in the peers' flag words (monotonic per handle, > 0)
   unsigned long long* probe; // diagnostics, NULL = off: [grid][kProbeSlots] %globaltimer stamps at the phase boundaries (coop kernel)
+};
+
+// Fused key exchange of the population-sharded path (sort_only handles, cooperative kernel).  Every rank owns an
+// exchange block of 16-byte lines [2 halves][world][shard_len] that its peers map (CUDA IPC across processes, plain
+// pointers inside one).  After ranking its shard the kernel stores every sorted key into its line of every peer's
+// block as {key low word, epoch, key high word, epoch} with ONE 16-byte store over NVLink - data and flag travel
+// together, so there is no fence and no separate signal; the receiving kernel polls each line until both flag
+// words carry the epoch, compacts the keys into a local array, then merges and updates in the same launch.
+// Halves alternate with the epoch: a peer can be at most one iteration ahead.
+constexpr int kMaxExchangeRanks = 16;
+struct ExchangeParams {
+  int world, rank, shard_len;
+  int n_global, n_pad;                                   // merged population, pitch of the merged key array
+  uint4* peer_lines[kMaxExchangeRanks];                  // base of rank r's block
+  const uint4* lines_local;                              // this rank's own block
+  unsigned long long* gathered;                          // [world][shard_len] keys received this iteration (local)
+  int* succ;                                             // scratch word of the merge
+  int* status;                                           // mapped host word: 1 = a peer did not publish before the timeout
+  unsigned long long timeout_ns;
+  unsigned long long* mkeys; float* elite_w; float* state0;   // merge outputs (MergeParams::keys / elite_w / state0)
+  float* vals;                                           // [n_free*D][n_pad] elites' sampled values, regenerated grid-wide before the update
 };
 
 // shared-memory bytes of the staged scene tables, and of the scoring phase for the given tile shape (the
@@ -55,7 +79,7 @@ size_t iterate_smem_bytes(const ssppm::DevModelHead& M, const IterParams& P, int
 
 // Launch-bound variants of the iteration kernel: __launch_bounds__(max_threads, min_ctas) sets the register
 // budget (65536 / (max_threads * min_ctas), rounded down to 8) and with it the resident warps per SM.
-constexpr int kProbeSlots = 8;   // phase-probe stamps per CTA
+constexpr int kProbeSlots = 12;  // phase-probe stamps per CTA (0-7: iteration phases, 8-11: fused key exchange)
 struct IterVariant { int max_threads, min_ctas; };
 constexpr int kNumIterVariants = 8;
 constexpr IterVariant kIterVariants[kNumIterVariants] = {{256, 2}, {256, 3}, {320, 2}, {320, 3}, {448, 2}, {384, 2}, {128, 7}, {192, 5}};

@@ -11,6 +11,11 @@ Two ways the path shards; neither exists in the reference (OpenMP on
   applies the identical merge + CES update (elites' rows are regenerated from the counters, so the
   sampled control points never travel) and all ranks hold bit-identical state without a second collective.
 
+`PopulationExchange` is the same iteration with the exchange fused into the kernel: the ranks map each
+other's exchange blocks once (CUDA IPC handles passed through torch.distributed), after which an
+iteration is ONE launch per rank that scores, ranks, stores its keys into every peer's block over NVLink,
+waits for the peers' flags and applies the update - no collective call in the loop.
+
 The collective code is backend-agnostic (nccl on GPUs; gloo in the CPU tests with a checker backend).
 """
 from __future__ import annotations
@@ -94,3 +99,33 @@ class PopulationSharded:
             else:
                 dist.all_gather_into_tensor(self.gathered, keys, group=self.group)
         self.b.merge(self.gathered, self.world, seed, it)
+
+
+class PopulationExchange:
+    """PopulationSharded with the key exchange inside the iteration kernel (peer memory over NVLink).
+
+    `handle` is a capi.Handle created with shard_offset / shard_global (equal shards).  The constructor is
+    collective: every rank of `group` must call it.  world == 1 needs no process group."""
+
+    def __init__(self, handle, stream: "torch.cuda.Stream | None" = None, group=None):
+        self.h = handle
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.stream = stream if stream is not None and stream.cuda_stream != 0 else torch.cuda.Stream()
+        handle.set_stream(self.stream.cuda_stream)
+        _, ipc = handle.exchange_export(self.world, self.rank)
+        if self.world == 1:
+            handle.exchange_attach_ipc([ipc])
+        else:
+            handles = [None] * self.world
+            dist.all_gather_object(handles, ipc, group=group)     # every rank has exported once this returns
+            handle.exchange_attach_ipc(handles)
+            dist.barrier(group=group)                             # nobody publishes before everybody is attached
+
+    def iterate(self, seed: int, it: int):
+        self.h.iterate_exchange(seed, it)
+
+    def check(self):
+        """synchronise and raise if a peer failed to publish (device-side timeout)"""
+        self.h.exchange_status()

@@ -183,6 +183,45 @@ def test_population_shards_match_unsharded(kind, n_global):
     full.close()
 
 
+@pytest.mark.parametrize("kind,n_global", [("task", 2048), ("joint", 4096)])
+def test_fused_exchange_single_rank_matches_unsharded(kind, n_global):
+    """the exchange fused into the iteration kernel (ssppcu_iterate_exchange) with world = 1: publish into the
+    rank's own block, flag, merge and update inside one launch reach the unsharded state bit for bit.  world > 1
+    needs one GPU per rank: scripts/check_popshard.py under torchrun (profiles/README.md)."""
+    import torch
+    from sspp_b200 import capi
+    from sspp_b200.sharding import PopulationExchange
+
+    def mk(n_samples, offset=0, glob=0):
+        case = task_case(n_samples=n_samples, check_points=32) if kind == "task" else \
+            joint_case(n_samples=n_samples, check_points=32, do_update=True)
+        case.cfg.shard_offset, case.cfg.shard_global = offset, glob
+        h = capi.Handle(case.model, case.cfg)
+        case.prepare(h)
+        return h
+    slots = 2 if kind == "task" else 0
+    full = mk(n_global - slots)
+    px = PopulationExchange(mk(n_global, 0, n_global))
+    with pytest.raises(capi.SsppError):
+        px.h.exchange_export(1, 0)                    # one block per handle
+    for it in range(4):
+        full.iterate(SEED, it, 1)
+        px.iterate(SEED, it)
+        px.check()
+        r, rs = full.results(), px.h.results()
+        fi, fc, fw = full.elites(0)
+        mi, mc, mw = px.h.merged(n_global)
+        assert np.array_equal(mi, fi) and np.array_equal(mc.view(np.uint32), fc.view(np.uint32))
+        k = int(r["n_elite"][0])
+        assert k > 0 and np.array_equal(mw[:k].view(np.uint32), fw[:k].view(np.uint32))
+        assert rs["n_success"][0] == r["n_success"][0] and rs["best_idx"][0] == r["best_idx"][0]
+        m0, s0 = full.get_distribution(); m1, s1 = px.h.get_distribution()
+        assert np.array_equal(m0, m1) and np.array_equal(s0, s1)
+        b0, v0 = full.best(); b1, v1 = px.h.best()
+        assert np.array_equal(b0, b1) and np.array_equal(v0, v1)
+    px.h.close(); full.close()
+
+
 def test_sdf_mode_matches_oracles():
     """cfg 3 back end: grid baked on the device == the replica's grid bit for bit; scored iterations bit-exact
     against the replica and within tolerance of the FP64 statement."""
@@ -269,7 +308,7 @@ def test_phase_probe_stamps_are_ordered():
     h.phase_probe(True)
     h.iterate(SEED, 0, 1)
     st = h.phase_probe(True, read=True).astype(np.int64)
-    assert st.shape[1] == 8 and (st[:, :6] > 0).all()
+    assert st.shape[1] == 12 and (st[:, :6] > 0).all()
     assert (np.diff(st[:, :6], axis=1) >= 0).all()              # start <= scored <= barrier 1 <= ranked <= barrier 2 <= updated
     assert st[:, 2].min() >= st[:, 1].max() - 2000              # nobody passes barrier 1 before everybody has scored (timer granularity)
     h.close()
