@@ -243,7 +243,8 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         step(args.warmup + i)
     ev1.record(stream)
     barrier()
-    ms_total = max_over_ranks(ev0.elapsed_time(ev1))
+    ms_local = ev0.elapsed_time(ev1)
+    ms_total = max_over_ranks(ms_local)
     value = pts_per_step * world * args.steps / (ms_total * 1e-3)
     # ---- roofline pass: the fused kernel alone, one event pair per launch ----
     nk = min(args.steps, 100)
@@ -251,7 +252,9 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     for i, (a, b) in enumerate(evs):
         a.record(stream); h.iterate(SEED, (args.warmup + i) * inner, inner, restored=True); b.record(stream)
     torch.cuda.synchronize()
-    k_ms = float(np.mean([a.elapsed_time(b) for a, b in evs]))
+    k_ms_isolated = float(np.mean([a.elapsed_time(b) for a, b in evs]))      # one event pair per launch (adds the event gaps)
+    k_ms = ms_local / args.steps      # the kernel's time per step over the timed region (events on the launch stream; a step is this kernel only:
+                                      # `launches_per_step` launches of it, and work per step is counted the same way)
     # ---- e2e: through the host API, host buffers in, every candidate's result out ----
     n_e2e = min(args.steps, 200)
     barrier()
@@ -288,7 +291,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     if tf.exists():
         traffic = json.loads(tf.read_text()).get(args.workload, {}).get("dram_bytes_per_launch")
     roof = dict(bound="fp32", achieved=ach, peak=fp32_peak, unit="TFLOP/s", frac=ach / fp32_peak, traffic=traffic,
-                kernel="sspp_iterate_kernel", kernel_ms=k_ms, flop_per_point=wm["flop_per_point"],
+                kernel="sspp_iterate_kernel", kernel_ms=k_ms, kernel_ms_isolated=k_ms_isolated, flop_per_point=wm["flop_per_point"],
                 note="nominal FLOP model of sspp_b200/roofline.py (every filtered pair charged its full narrow phase; the kernel culls "
                      "most by bounding spheres) over the FMA peak measured live by ssppcu_fp32_peak; MEASURED_PEAKS.json has no FP32 entry",
                 hbm=dict(achieved=hbm_ach, peak=peaks.get("hbm_gbs"), unit="GB/s",

@@ -52,6 +52,7 @@ struct ssppcu_planner {
   unsigned char* d_res = nullptr; unsigned char* h_res = nullptr; size_t res_bytes = 0;
   size_t o_L = 0, o_Cnf = 0, o_Cwf = 0, o_cost = 0, o_status = 0, o_nsucc = 0, o_nelite = 0, o_bidx = 0, o_bcost = 0, o_extra = 0;
   unsigned char* h_stage = nullptr; size_t stage_bytes = 0, stage_at = 0;
+  bool best_fresh = false;   // the pinned mirror holds best | best_valid of the current device state (set by get_results, cleared by any other call)
   // fused key exchange of a population shard (ssppcu_exchange_*): this rank's block, the peers' mappings
   struct Exchange {
     int world = 0, rank = 0;
@@ -484,6 +485,7 @@ namespace {
 
 int check(ssppcu_t* h) {
   if (!h) return SSPPCU_EINVAL;
+  h->best_fresh = false;
   cudaError_t e = cudaSetDevice(h->cfg.device);
   if (e != cudaSuccess) return cuda_fail(h, e, "cudaSetDevice");
   return 0;
@@ -716,6 +718,10 @@ int ssppcu_get_results(ssppcu_t* h, float* L, float* Cnf, float* Cwf, float* cos
   CU(h, cudaMemcpyAsync(h->h_res + from, h->d_res + from, h->res_bytes - from, cudaMemcpyDeviceToHost, h->stream));
   int32_t* h_any = reinterpret_cast<int32_t*>(h->h_res + h->o_extra);
   if (any_success) CU(h, cudaMemcpyAsync(h_any, h->P.any_success, Q * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+  {   // best | best_valid ride along: a get_best right after this call needs no second round trip
+    const size_t nfd = (size_t)h->P.cfg.n_free * h->P.cfg.D;
+    CU(h, cudaMemcpyAsync(h->h_res + h->o_extra + Q * 4, h->P.best, Q * nfd * 4 + Q * 4, cudaMemcpyDeviceToHost, h->stream));
+  }
   CU(h, cudaStreamSynchronize(h->stream));
   if (L) std::memcpy(L, h->h_res + h->o_L, QN * 4);
   if (Cnf) std::memcpy(Cnf, h->h_res + h->o_Cnf, QN * 4);
@@ -727,6 +733,7 @@ int ssppcu_get_results(ssppcu_t* h, float* L, float* Cnf, float* Cwf, float* cos
   if (best_idx) std::memcpy(best_idx, h->h_res + h->o_bidx, Q * 4);
   if (best_cost) std::memcpy(best_cost, h->h_res + h->o_bcost, Q * 4);
   if (any_success) std::memcpy(any_success, h_any, Q * 4);
+  h->best_fresh = true;
   return SSPPCU_OK;
 }
 
@@ -740,11 +747,15 @@ int ssppcu_get_params(ssppcu_t* h, float* params) {
 }
 
 int ssppcu_get_best(ssppcu_t* h, float* best, int32_t* valid) {
+  const bool fresh = h && h->best_fresh;                     // fetched by the ssppcu_get_results call just before this one
   if (int rc = check(h)) return rc;
   const size_t Q = h->P.n_query, nfd = (size_t)h->P.cfg.n_free * h->P.cfg.D;
   unsigned char* m = h->h_res + h->o_extra + Q * 4;          // after the any_success mirror
-  CU(h, cudaMemcpyAsync(m, h->P.best, Q * nfd * 4 + Q * 4, cudaMemcpyDeviceToHost, h->stream));   // best | best_valid
-  CU(h, cudaStreamSynchronize(h->stream));
+  if (!fresh) {
+    CU(h, cudaMemcpyAsync(m, h->P.best, Q * nfd * 4 + Q * 4, cudaMemcpyDeviceToHost, h->stream));   // best | best_valid
+    CU(h, cudaStreamSynchronize(h->stream));
+  }
+  h->best_fresh = true;
   if (best) std::memcpy(best, m, Q * nfd * 4);
   if (valid) std::memcpy(valid, m + Q * nfd * 4, Q * 4);
   return SSPPCU_OK;

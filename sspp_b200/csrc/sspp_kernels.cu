@@ -798,8 +798,8 @@ sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant_
       const size_t words = (size_t)P.n_query * (3 * nfd + 2);
       for (size_t e = (size_t)blockIdx.x * T + tid; e < words; e += (size_t)gridDim.x * T) P.mean[e] = P.state_in[e];
     }
-    // ---- phase A: score the tiles ----
     load_basis(s, c, P, tid, T);                         // phase B reuses this shared memory
+    // ---- phase A: score the tiles ----
     const bool handout = P.n_tiles > (int)gridDim.x;     // first wave by CTA index, the rest first come first served:
     for (int tile = blockIdx.x; tile < P.n_tiles;) {     // tiles differ in cost (culling), a fixed assignment leaves a tail
       const int query = tile / P.ctas_per_query;

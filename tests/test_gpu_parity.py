@@ -283,6 +283,29 @@ def test_iterate_restored_equals_restore_then_iterate(kind):
     assert np.array_equal(m0, m1) and np.array_equal(s0, s1) and np.array_equal(b0, b1) and np.array_equal(v0, v1)
 
 
+def test_best_read_after_results_needs_no_second_fetch_and_stays_current():
+    """get_results brings best | best_valid along; get_best right after it reads the pinned mirror, any call in
+    between (an iteration, a reset) makes it fetch again"""
+    case = task_case(n_samples=126, check_points=40)
+    h = _handle(case)
+    h.iterate(SEED, 0, 1)
+    b_direct, v_direct = h.best()                     # fetched
+    h.results()
+    b_mirror, v_mirror = h.best()                     # from the mirror get_results filled
+    assert np.array_equal(b_direct, b_mirror) and np.array_equal(v_direct, v_mirror) and v_direct[0] == 1
+    h.results()
+    h.iterate(SEED, 1, 3)                             # state moves on after the results call
+    b2, _ = h.best()
+    h.results()
+    b3, _ = h.best()
+    assert np.array_equal(b2, b3)
+    h.results()
+    case.prepare(h)                                   # reset_distribution clears the forwarded best
+    _, v4 = h.best()
+    assert v4[0] == 0
+    h.close()
+
+
 def test_tile_shapes_and_kernel_variants_agree_bitwise():
     """the launch-bound variant, threads per CTA and candidates per CTA are pure tuning knobs"""
     ref = None
