@@ -188,6 +188,14 @@ int ssppcu_eval_points(ssppcu_t* h, const float* pts, int n, float* cost_out);
 
 /* SDF mode: the baked node grid [nz][ny][nx] (host copy) and its geometry; nodes may be NULL to query sizes */
 int ssppcu_get_sdf(ssppcu_t* h, float* nodes, int32_t dims[3], double lo[3], double cell[3]);
+/* SDF mode, optional refinement step (restates scripts/sdf_gradient/main.py:37-81 on the baked grid): for every row m of
+ * `weights` [rows][n_points] (NULL: the handle's collision collocation matrix, rows = check points) the configuration
+ * q_m = sum_j weights[m][j] * pts[j] (pts [n_points][dof] host floats), the clearance of the closest sample sphere
+ * (dist[m]) and dirs[m] = -clearance * unit gradient of the field there (clearance times the direction towards the
+ * obstacle, main.py:60-61); grad[j] = (1/rows) * sum_m dirs[m] * weights[m][j] ([n_points][3], main.py:66-81).  With
+ * weights = basis functions and pts = control points this is the reference's formula; with the collocation matrix and
+ * the point matrix it is the same derivative in the planner's own parameters.  dist / dirs may be NULL.  Synchronises. */
+int ssppcu_sdf_gradient(ssppcu_t* h, const float* pts, const float* weights, int rows, float* grad, float* dist, float* dirs);
 /* SDF mode: sample spheres of the moving geoms, [n][5] = centre (body frame) x,y,z, radius, body index; returns n */
 int ssppcu_get_spheres(ssppcu_t* h, float* out, int cap);
 

@@ -92,7 +92,7 @@ SYMBOLS = [
     "ssppcu_spline_setup", "ssppcu_collocation_matrix", "ssppcu_save_state", "ssppcu_restore_state",
     "ssppcu_fp32_peak", "ssppcu_get_merged", "ssppcu_get_sdf", "ssppcu_get_spheres", "ssppcu_phase_probe", "ssppcu_iterate_restored",
     "ssppcu_exchange_export", "ssppcu_exchange_attach_ipc", "ssppcu_exchange_attach_ptrs", "ssppcu_iterate_exchange",
-    "ssppcu_exchange_status",
+    "ssppcu_exchange_status", "ssppcu_sdf_gradient",
 ]
 
 lib = _load()
@@ -143,6 +143,7 @@ lib.ssppcu_iterate_exchange.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32]
 lib.ssppcu_exchange_status.argtypes = [C.c_void_p]
 lib.ssppcu_get_sdf.argtypes = [C.c_void_p, C.c_void_p, _ip, _dp, _dp]
 lib.ssppcu_get_spheres.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+lib.ssppcu_sdf_gradient.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
 lib.ssppcu_save_state.argtypes = [C.c_void_p]
 lib.ssppcu_restore_state.argtypes = [C.c_void_p]
 lib.ssppcu_fp32_peak.argtypes = [C.c_int, _dp, _dp]
@@ -361,6 +362,20 @@ class Handle:
         out = np.zeros((grid, 12), np.uint64)
         self._ck(min(0, lib.ssppcu_phase_probe(self._h, int(enable), out.ctypes.data_as(C.c_void_p), grid)))
         return out
+
+    def sdf_gradient(self, pts, weights=None):
+        """SDF mode refinement step: (grad [n_points][3], clearance [rows], dirs [rows][3]); see ssppcu_sdf_gradient"""
+        pts = np.ascontiguousarray(pts, np.float32)
+        K = self.dims.n_points
+        if weights is None:
+            rows, W = self.collocation()[0].shape[0], None
+        else:
+            W = np.ascontiguousarray(weights, np.float32); rows = W.shape[0]
+            assert W.shape[1] == K
+        assert pts.shape == (K, self.dims.dof)
+        grad = np.zeros((K, 3), np.float32); dist = np.zeros(rows, np.float32); dirs = np.zeros((rows, 3), np.float32)
+        self._ck(lib.ssppcu_sdf_gradient(self._h, _ptr(pts), _ptr(W), rows, _ptr(grad), _ptr(dist), _ptr(dirs)))
+        return grad, dist, dirs
 
     def save_state(self):
         self._ck(lib.ssppcu_save_state(self._h))

@@ -812,6 +812,31 @@ int ssppcu_eval_points(ssppcu_t* h, const float* pts, int n, float* out) {
   return SSPPCU_OK;
 }
 
+int ssppcu_sdf_gradient(ssppcu_t* h, const float* pts, const float* weights, int rows, float* grad, float* dist, float* dirs) {
+  if (int rc = check(h)) return rc;
+  if (!h->dev.sdf_mode) return fail(h, SSPPCU_EINVAL, "handle is not in SDF collision mode");
+  if (!pts || !grad) return fail(h, SSPPCU_EINVAL, "bad arguments");
+  const int D = h->P.cfg.D, K = h->P.cfg.K;
+  if (!weights) { weights = h->psi_col.data(); rows = h->P.cfg.Mc; }      // the handle's collision collocation matrix [Mc][K]
+  if (rows < 1 || rows > 65536) return fail(h, SSPPCU_EINVAL, "rows out of range");
+  const size_t nW = (size_t)rows * K, nP = (size_t)K * D, nO = (size_t)rows * 4 + (size_t)K * 3;
+  float* d_buf = nullptr;
+  CU(h, cudaMalloc(&d_buf, (nW + nP + nO) * sizeof(float)));
+  float* d_W = d_buf; float* d_pts = d_W + nW; float* d_dist = d_pts + nP; float* d_dirs = d_dist + rows; float* d_G = d_dirs + 3 * (size_t)rows;
+  std::vector<float> out(nO);
+  cudaError_t e = cudaMemcpyAsync(d_W, weights, nW * sizeof(float), cudaMemcpyHostToDevice, h->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(d_pts, pts, nP * sizeof(float), cudaMemcpyHostToDevice, h->stream);
+  if (e == cudaSuccess) e = launch_sdf_gradient(h->view, D, K, rows, d_W, d_pts, d_dist, d_dirs, d_G, h->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(out.data(), d_dist, nO * sizeof(float), cudaMemcpyDeviceToHost, h->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+  cudaFree(d_buf);
+  if (e != cudaSuccess) return cuda_fail(h, e, "ssppcu_sdf_gradient");
+  if (dist) std::memcpy(dist, out.data(), (size_t)rows * sizeof(float));
+  if (dirs) std::memcpy(dirs, out.data() + rows, (size_t)rows * 3 * sizeof(float));
+  std::memcpy(grad, out.data() + (size_t)rows * 4, (size_t)K * 3 * sizeof(float));
+  return SSPPCU_OK;
+}
+
 int ssppcu_get_sdf(ssppcu_t* h, float* nodes, int32_t dims[3], double lo[3], double cell[3]) {
   if (int rc = check(h)) return rc;
   if (!h->dev.sdf_mode) return fail(h, SSPPCU_EINVAL, "handle is not in SDF collision mode");

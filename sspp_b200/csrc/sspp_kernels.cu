@@ -991,6 +991,45 @@ sspp_eval_points_kernel(const __grid_constant__ ModelView M, int D, const float*
   out[i] = point_collision_cost(M, qa, xf);
 }
 
+// SDF refinement step: per collocation row m the configuration q_m = sum_j W[m][j] pts[j], the closest
+// sample sphere and g_m = -clearance * grad / |grad| (clearance times the unit direction towards the obstacle, the
+// `grad` of scripts/sdf_gradient/main.py:60-61); then G_j = (1/rows) sum_m g_m W[m][j] (main.py:66-81) by one thread
+// per output in row order.  One CTA: rows are few (the collocation grid of one path).
+__global__ void __launch_bounds__(128)
+sspp_sdf_gradient_kernel(const __grid_constant__ ModelView M, int D, int K, int rows, const float* __restrict__ W,
+                         const float* __restrict__ pts, float* __restrict__ dist, float* __restrict__ dirs, float* __restrict__ G) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float* s_qs = reinterpret_cast<float*>(smem_raw);
+  float* s_xf = s_qs + D * blockDim.x;
+  const int tid = threadIdx.x, T = blockDim.x;
+  for (int m0 = 0; m0 < rows; m0 += T) {
+    const int m = m0 + tid;
+    if (m < rows) {
+      for (int d = 0; d < D; ++d) {
+        float acc = 0.0f;
+        for (int j = 0; j < K; ++j) acc = fmaf(W[(size_t)m * K + j], pts[(size_t)j * D + d], acc);
+        s_qs[d * T + tid] = acc;
+      }
+      SmemXF xf{s_xf, T, tid};
+      SmemQ qa{s_qs, T, tid};
+      float cl; v3 g;
+      point_closest_sample(M, qa, xf, &cl, &g);
+      const float n = sqrtf(dot(g, g));
+      const float sc = (n > 0.0f) ? -cl / n : 0.0f;
+      dist[m] = cl;
+      dirs[3 * m] = sc * g.x; dirs[3 * m + 1] = sc * g.y; dirs[3 * m + 2] = sc * g.z;
+    }
+  }
+  __threadfence_block();
+  __syncthreads();
+  for (int o = tid; o < K * 3; o += T) {
+    const int j = o / 3, a = o - 3 * j;
+    float acc = 0.0f;
+    for (int m = 0; m < rows; ++m) acc = fmaf(dirs[3 * m + a], W[(size_t)m * K + j], acc);
+    G[o] = acc / (float)rows;
+  }
+}
+
 // node value = min over the static primitives of the exact point-primitive signed distance
 __global__ void __launch_bounds__(256)
 sspp_sdf_bake_kernel(const __grid_constant__ ModelView M, float* __restrict__ nodes) {
@@ -1119,6 +1158,18 @@ cudaError_t launch_eval_points(const ModelView& M, int D, const float* pts, int 
     configured = smem;
   }
   sspp_eval_points_kernel<<<(n + T - 1) / T, T, smem, stream>>>(M, D, pts, n, out);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_sdf_gradient(const ModelView& M, int D, int K, int rows, const float* W, const float* pts, float* dist, float* dirs,
+                                float* G, cudaStream_t stream) {
+  const int T = 128;
+  const size_t smem = (size_t)(D + (M.chain ? 0 : M.n_mbody * 12)) * T * sizeof(float);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(sspp_sdf_gradient_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  sspp_sdf_gradient_kernel<<<1, T, smem, stream>>>(M, D, K, rows, W, pts, dist, dirs, G);
   return cudaGetLastError();
 }
 

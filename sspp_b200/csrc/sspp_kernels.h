@@ -117,6 +117,11 @@ cudaError_t launch_eval_points(const ssppm::ModelView& M, int D, const float* pt
 // 8 corners of every cell contiguously for the kernel's two 16-byte loads per sample
 cudaError_t launch_sdf_bake(const ssppm::ModelView& M, float* nodes, float* cells, cudaStream_t stream);
 
+// SDF mode, refinement step: per collocation row the closest sample sphere's clearance and -clearance * unit field
+// gradient, and their projection on the point-matrix rows G[K][3] = (1/rows) sum_m dirs[m] W[m][.]  (device pointers)
+cudaError_t launch_sdf_gradient(const ssppm::ModelView& M, int D, int K, int rows, const float* W, const float* pts, float* dist,
+                                float* dirs, float* G, cudaStream_t stream);
+
 // FP32 FMA peak probe: every thread runs `iters` rounds of 8 independent FMA chains
 cudaError_t launch_fma_probe(float* sink, int blocks, int threads, int iters, cudaStream_t stream);
 

@@ -958,6 +958,63 @@ SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf) {
   return cost;
 }
 
+// SDF mode, refinement step: the sphere sample closest to the static scene at configuration q, its clearance
+// (field value - radius) and the gradient of the trilinear interpolant there (d clearance / d world position).
+// Restates get_closest_points of /root/reference/scripts/sdf_gradient/main.py:37-63 on the grid instead of
+// mj_geomDistance: the minimum over (moving geom x environment geom) pairs becomes the minimum over sample spheres
+// of the baked field, the witness direction becomes the field gradient.
+SSPP_HD v3 sdf_gradient_at(const SdfGrid& g, v3 x, float* value) {
+  int i, j, k; float fx, fy, fz;
+  sdf_locate(g, x, &i, &j, &k, &fx, &fy, &fz);
+  float v[8];
+#if defined(__CUDA_ARCH__)
+  sdf_load_cell(g.cells + 8 * (((size_t)k * (g.ny - 1) + j) * (g.nx - 1) + i), v);
+#else
+  for (int c = 0; c < 8; ++c)
+    v[c] = g.nodes[((size_t)(k + (c >> 2)) * g.ny + (j + ((c >> 1) & 1))) * g.nx + (i + (c & 1))];
+#endif
+  *value = trilerp(v, fx, fy, fz);
+  const float a0 = v[1] - v[0], a1 = v[3] - v[2], a2 = v[5] - v[4], a3 = v[7] - v[6];
+  const float ax0 = fmaf(fy, a1 - a0, a0), ax1 = fmaf(fy, a3 - a2, a2);
+  const float c00 = fmaf(fx, a0, v[0]), c10 = fmaf(fx, a1, v[2]), c01 = fmaf(fx, a2, v[4]), c11 = fmaf(fx, a3, v[6]);
+  const float b0 = c10 - c00, b1 = c11 - c01;
+  const float c0 = fmaf(fy, b0, c00), c1 = fmaf(fy, b1, c01);
+  return mk(fmaf(fz, ax1 - ax0, ax0) * g.inv_h[0], fmaf(fz, b1 - b0, b0) * g.inv_h[1], (c1 - c0) * g.inv_h[2]);
+}
+
+template <class MT, class XF, class QA>
+SSPP_HD void point_closest_sample(const MT& M, QA& q, XF& xf, float* clearance, v3* grad) {
+  float best = 3.0e38f;
+  v3 best_g = mk(0.f, 0.f, 0.f);
+  m3 R; v3 p = mk(0.f, 0.f, 0.f);
+  for (int k = 0; k < 9; ++k) R.a[k] = 0.0f;
+  for (int b = 0; b < M.n_mbody; ++b) {
+    const i4 jt = rec_i4(M.body, b, BW_JOINT);
+    m3 Rp; v3 pp;
+    const bool hp = jt.x >= 0;
+    if (hp) {
+      if (M.chain) { Rp = R; pp = p; }
+      else {
+        for (int k = 0; k < 9; ++k) Rp.a[k] = xf.get(jt.x, k);
+        pp = mk(xf.get(jt.x, 9), xf.get(jt.x, 10), xf.get(jt.x, 11));
+      }
+    } else { pp = mk(0.f, 0.f, 0.f); Rp = R; }
+    fk_body(M.body, b, jt, hp, Rp, pp, q, &R, &p);
+    if (!M.chain) {
+      for (int k = 0; k < 9; ++k) xf.put(b, k, R.a[k]);
+      xf.put(b, 9, p.x); xf.put(b, 10, p.y); xf.put(b, 11, p.z);
+    }
+    const i4 sp = rec_i4(M.body, b, BW_SPH);
+    for (int k = sp.x; k < sp.y; ++k) {
+      const f4 sc = rec_f4(M.sph, k, SW_C);
+      float val;
+      const v3 g = sdf_gradient_at(M.grid, add(p, mulv(R, mk(sc.x, sc.y, sc.z))), &val);
+      if (val - sc.w < best) { best = val - sc.w; best_g = g; }
+    }
+  }
+  *clearance = best; *grad = best_g;
+}
+
 // value of grid node (i,j,k): min over the static primitives (shared by the bake kernel and the replica)
 template <class MT>
 SSPP_HD float sdf_node_value(const MT& M, int i, int j, int k) {
