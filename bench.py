@@ -132,7 +132,16 @@ class CpuArm:
             self.sigma = [np.full_like(m, case.sigma0) for m in self.mean]
         else:
             self.sigma = [np.tile(case.joint_sigma * case.limits, (self.nfree, 1)) for _ in self.mean]
+        # all the host threads the process may use: torchrun exports OMP_NUM_THREADS=1 to its workers, which would
+        # leave the CPU arm single-threaded; the OpenMP runtime the oracle is linked to is told explicitly
         self.cores = len(os.sched_getaffinity(0))
+        try:
+            import ctypes
+            gomp = ctypes.CDLL("libgomp.so.1")
+            gomp.omp_set_num_threads(self.cores)
+            self.cores = int(gomp.omp_get_max_threads())
+        except OSError:
+            self.cores = int(os.environ.get("OMP_NUM_THREADS", self.cores))
         self.M = c.check_points
 
     def step(self, it: int, n_cand: int, query: int = 0) -> int:
