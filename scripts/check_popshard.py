@@ -1,19 +1,23 @@
-"""torchrun check on N GPUs: a population sharded over the ranks (NCCL all-gather of keys) reaches the
-state of the unsharded population computed on rank 0's GPU.  Prints OK/FAIL per rank."""
+"""torchrun check on N GPUs: a population sharded over the ranks reaches the state of the unsharded population,
+bit for bit, with both transports (all-gather + merge kernels; key exchange fused into the iteration kernel), and what
+an iteration costs either way.  POP_CASE=sdf runs the cfg 3 scene (cluttered stacking scene, SDF grid 128^3) instead
+of the robocrane task scene; POP_PER_RANK (default 8192) candidates per rank."""
 import os, sys
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 import numpy as np, torch, torch.distributed as dist
 from sspp_b200 import capi
 from sspp_b200.sharding import DeviceShard, PopulationExchange, PopulationSharded, block_range
-from tests.helpers import task_case, SEED
+from tests.helpers import sdf_case, task_case, SEED
 
 rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(lr)
 dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
-N = 8192 * world
+N = int(os.environ.get("POP_PER_RANK", "8192")) * world
+SDF = os.environ.get("POP_CASE", "task") == "sdf"
 def mk(n, off=0, glob=0):
-    c = task_case(n_samples=n, check_points=64, n_points=5); c.cfg.device = lr
+    c = sdf_case(n_samples=n, check_points=64, n_points=5, dims=(128, 128, 128)) if SDF else task_case(n_samples=n, check_points=64, n_points=5)
+    c.cfg.device = lr
     c.cfg.shard_offset, c.cfg.shard_global = off, glob
     h = capi.Handle(c.model, c.cfg); c.prepare(h); return h
 lo, hi = block_range(N, rank, world)
