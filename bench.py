@@ -242,6 +242,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         h.iterate(SEED, i * inner, inner, restored=True)      # re-arm from the snapshot + iterate: ONE launch
 
     clocks = ClockSampler(local_rank)
+    h.set_result_mirror(False)                       # value / roofline: results stay in HBM, nothing is written to the host
     for i in range(max(args.warmup, 3)):
         step(i)
     # ---- value: K steps, device resident, CUDA events on the launch stream ----
@@ -266,13 +267,15 @@ def run_ours(args, rank: int, world: int, local_rank: int):
                                       # `launches_per_step` launches of it, and work per step is counted the same way)
     # ---- e2e: through the host API, host buffers in, every candidate's result out ----
     n_e2e = min(args.steps, 200)
+    h.set_result_mirror(True)                        # the library's default: the kernel fills the pinned result mirror itself
+    res, best = h.results(), h.best()                # caller-owned host buffers, refilled by every step
     barrier()
     t0 = time.perf_counter()
     for i in range(n_e2e):
         case.prepare(h)                              # H2D: start/end -> point matrix, mean, sigma
         h.iterate(SEED, (args.warmup + i) * inner, inner)
-        res = h.results()                            # D2H: L, Cnf, Cwf, cost, status per candidate + per-query scalars
-        best = h.best()
+        res = h.results(res)                         # D2H: L, Cnf, Cwf, cost, status per candidate + per-query scalars
+        best = h.best(best)
     barrier()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     clk = clocks.stop()
@@ -281,7 +284,8 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     d2h = d.n_queries * (d.n_cand * (4 * 4 + 1) + 5 * 4 + nfd * 4 + 4)
     e2e = dict(value=pts_per_step * world * n_e2e / e2e_s, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h,
                steps=n_e2e, api="sspp_b200.capi (ctypes over the C ABI): set_queries + set_joint_noise/reset_distribution + iterate + get_results + get_best; "
-                   "host arrays are pageable numpy buffers, the library stages them through its pinned ring / pinned result mirror")
+                   "host arrays are pageable numpy buffers, the library stages inputs through its pinned ring; the result block reaches its "
+                   "mapped pinned mirror from inside the kernel (cooperative shapes) or by one D2H copy, and is copied out to the caller's arrays")
     if rank != 0:
         h.close()
         return

@@ -171,6 +171,14 @@ int ssppcu_sync(ssppcu_t* h);
  * size or a negative error. */
 int ssppcu_phase_probe(ssppcu_t* h, int enable, unsigned long long* stamps, int cap_ctas);
 
+/* Result mirror (on by default; the environment variable SSPPCU_RESULT_MIRROR=0 sets the default to off): the
+ * cooperative kernel copies its result block into the handle's mapped pinned host block itself, behind the grid
+ * barrier that makes the values final, so that ssppcu_get_results / _get_best right after a launch are a stream
+ * synchronisation and no D2H copy.  The device block is written as before (ssppcu_device_view stays valid).  A caller
+ * that keeps the results on the device turns it off and saves the PCIe writes (about 70 KB per launch at 4096
+ * candidates). */
+int ssppcu_set_result_mirror(ssppcu_t* h, int on);
+
 /* host copies of the last iteration; any pointer may be NULL.  Per-candidate arrays are
  * [n_queries][n_cand], per-query arrays [n_queries].  Synchronises the stream. */
 int ssppcu_get_results(ssppcu_t* h, float* L, float* Cnf, float* Cwf, float* cost, uint8_t* status,

@@ -92,7 +92,7 @@ SYMBOLS = [
     "ssppcu_spline_setup", "ssppcu_collocation_matrix", "ssppcu_save_state", "ssppcu_restore_state",
     "ssppcu_fp32_peak", "ssppcu_get_merged", "ssppcu_get_sdf", "ssppcu_get_spheres", "ssppcu_phase_probe", "ssppcu_iterate_restored",
     "ssppcu_exchange_export", "ssppcu_exchange_attach_ipc", "ssppcu_exchange_attach_ptrs", "ssppcu_iterate_exchange",
-    "ssppcu_exchange_status", "ssppcu_sdf_gradient",
+    "ssppcu_exchange_status", "ssppcu_sdf_gradient", "ssppcu_set_result_mirror",
 ]
 
 lib = _load()
@@ -117,6 +117,7 @@ lib.ssppcu_model_free.restype = None
 lib.ssppcu_last_error.argtypes = [C.c_void_p]
 lib.ssppcu_dims.argtypes = [C.c_void_p, C.POINTER(Dims)]
 lib.ssppcu_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+lib.ssppcu_set_result_mirror.argtypes = [C.c_void_p, C.c_int]
 lib.ssppcu_set_queries.argtypes = [C.c_void_p, _dp, _dp]
 lib.ssppcu_reset_distribution.argtypes = [C.c_void_p, C.c_double]
 lib.ssppcu_set_distribution.argtypes = [C.c_void_p, _dp, _dp]
@@ -287,6 +288,11 @@ class Model:
                     exclude=ai(v.exclude, 2 * v.nexclude).reshape(-1, 2))
 
 
+class _Results(dict):
+    """the dict Handle.results returns; keeps the ctypes pointers of its arrays so that a refill converts nothing"""
+    ptrs: list
+
+
 class Handle:
     """One ssppcu_t: a scene specialised for one planner shape, resident on one GPU."""
 
@@ -315,6 +321,10 @@ class Handle:
 
     def set_stream(self, stream_ptr: int | None):
         self._ck(lib.ssppcu_set_stream(self._h, stream_ptr))
+
+    def set_result_mirror(self, on: bool):
+        """on (default): the cooperative kernel writes its results into the pinned host mirror itself; off: device only"""
+        self._ck(lib.ssppcu_set_result_mirror(self._h, int(bool(on))))
 
     def set_queries(self, start, end):
         d = self.dims
@@ -383,15 +393,20 @@ class Handle:
     def restore_state(self):
         self._ck(lib.ssppcu_restore_state(self._h))
 
-    def results(self) -> dict:
-        d = self.dims
-        Q, N = d.n_queries, d.n_cand
-        out = dict(L=np.empty((Q, N), np.float32), Cnf=np.empty((Q, N), np.float32), Cwf=np.empty((Q, N), np.float32),
-                   cost=np.empty((Q, N), np.float32), status=np.empty((Q, N), np.uint8),
-                   n_success=np.empty(Q, np.int32), n_elite=np.empty(Q, np.int32), best_idx=np.empty(Q, np.int32),
-                   best_cost=np.empty(Q, np.float32), any_success=np.empty(Q, np.int32))
-        self._ck(lib.ssppcu_get_results(self._h, *[_ptr(out[k]) for k in (
-            "L", "Cnf", "Cwf", "cost", "status", "n_success", "n_elite", "best_idx", "best_cost", "any_success")]))
+    _RES_KEYS = ("L", "Cnf", "Cwf", "cost", "status", "n_success", "n_elite", "best_idx", "best_cost", "any_success")
+
+    def results(self, out: dict | None = None) -> dict:
+        """every candidate's L / Cnf / Cwf / cost / status and the per-query scalars.  `out`: a dict returned by an earlier
+        call on this handle, filled again in place (caller-owned buffers, as a C caller of ssppcu_get_results would keep)"""
+        if out is None:
+            d = self.dims
+            Q, N = d.n_queries, d.n_cand
+            out = _Results(L=np.empty((Q, N), np.float32), Cnf=np.empty((Q, N), np.float32), Cwf=np.empty((Q, N), np.float32),
+                       cost=np.empty((Q, N), np.float32), status=np.empty((Q, N), np.uint8),
+                       n_success=np.empty(Q, np.int32), n_elite=np.empty(Q, np.int32), best_idx=np.empty(Q, np.int32),
+                       best_cost=np.empty(Q, np.float32), any_success=np.empty(Q, np.int32))
+            out.ptrs = [_ptr(out[k]) for k in self._RES_KEYS]
+        self._ck(lib.ssppcu_get_results(self._h, *out.ptrs))
         return out
 
     def params(self) -> np.ndarray:
@@ -400,11 +415,13 @@ class Handle:
         self._ck(lib.ssppcu_get_params(self._h, _ptr(p)))
         return p
 
-    def best(self):
-        d = self.dims
-        b = np.zeros((d.n_queries, d.n_free, d.dof), np.float32); v = np.zeros(d.n_queries, np.int32)
-        self._ck(lib.ssppcu_get_best(self._h, _ptr(b), _ptr(v)))
-        return b, v
+    def best(self, out: tuple | None = None):
+        """forwarded best candidate of every query and its validity flag; `out`: the pair of an earlier call, refilled in place"""
+        if out is None:
+            d = self.dims
+            out = (np.zeros((d.n_queries, d.n_free, d.dof), np.float32), np.zeros(d.n_queries, np.int32))
+        self._ck(lib.ssppcu_get_best(self._h, _ptr(out[0]), _ptr(out[1])))
+        return out
 
     def elites(self, query: int = 0, cap: int | None = None):
         cap = self.dims.n_cand if cap is None else cap

@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <stdexcept>
 #include <string>
@@ -53,6 +54,10 @@ struct ssppcu_planner {
   size_t o_L = 0, o_Cnf = 0, o_Cwf = 0, o_cost = 0, o_status = 0, o_nsucc = 0, o_nelite = 0, o_bidx = 0, o_bcost = 0, o_extra = 0;
   unsigned char* h_stage = nullptr; size_t stage_bytes = 0, stage_at = 0;
   bool best_fresh = false;   // the pinned mirror holds best | best_valid of the current device state (set by get_results, cleared by any other call)
+  // the pinned mirror is mapped: the cooperative kernel copies the result block into it itself (mirror_results, sspp_kernels.cu),
+  // so a read-back right after such a launch is a stream synchronisation and no copy.  SSPPCU_RESULT_MIRROR=0 turns it off.
+  unsigned char* h_res_dev = nullptr; bool mirror_on = true;
+  bool res_fresh = false;    // the last call was a launch that mirrors its results (cleared by any other call)
   // fused key exchange of a population shard (ssppcu_exchange_*): this rank's block, the peers' mappings
   struct Exchange {
     int world = 0, rank = 0;
@@ -421,7 +426,10 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
     if (!rc) {
       cudaError_t e1 = cudaMalloc(&h->d_res, h->res_bytes);
       if (e1 == cudaSuccess) e1 = cudaMemset(h->d_res, 0, h->res_bytes);
-      if (e1 == cudaSuccess) e1 = cudaMallocHost(&h->h_res, off);
+      if (e1 == cudaSuccess) e1 = cudaHostAlloc(&h->h_res, off, cudaHostAllocMapped);
+      if (e1 == cudaSuccess) e1 = cudaHostGetDevicePointer(reinterpret_cast<void**>(&h->h_res_dev), h->h_res, 0);
+      if (e1 == cudaSuccess) std::memset(h->h_res, 0, off);
+      if (const char* m = std::getenv("SSPPCU_RESULT_MIRROR")) h->mirror_on = std::atoi(m) != 0;
       h->stage_bytes = std::max<size_t>(64 * 1024, 4 * (Q * s.K * s.D + 2 * Q * nfd) * sizeof(float));
       if (e1 == cudaSuccess) e1 = cudaMallocHost(&h->h_stage, h->stage_bytes);
       if (e1 != cudaSuccess) rc |= cuda_fail(h, e1, "result / staging blocks");
@@ -485,7 +493,7 @@ namespace {
 
 int check(ssppcu_t* h) {
   if (!h) return SSPPCU_EINVAL;
-  h->best_fresh = false;
+  h->best_fresh = false; h->res_fresh = false;
   cudaError_t e = cudaSetDevice(h->cfg.device);
   if (e != cudaSuccess) return cuda_fail(h, e, "cudaSetDevice");
   return 0;
@@ -577,7 +585,8 @@ int ssppcu_reset_distribution(ssppcu_t* h, double sigma0) {
   if (int rc = check(h)) return rc;
   const ScoreConfig& s = h->P.cfg;
   const int Q = h->P.n_query, D = s.D, nfd = s.n_free * D;
-  std::vector<float> mean((size_t)Q * nfd), sigma((size_t)Q * nfd);
+  std::vector<float> ms((size_t)2 * Q * nfd);               // mean | sigma are neighbours in the live state block: one copy
+  float* mean = ms.data(); float* sigma = mean + (size_t)Q * nfd;
   for (int q = 0; q < Q; ++q)
     for (int r = 0; r < s.n_free; ++r)
       for (int d = 0; d < D; ++d) {
@@ -588,19 +597,20 @@ int ssppcu_reset_distribution(ssppcu_t* h, double sigma0) {
         double sg = std::max(std::min(std::max(sigma0, h->cfg.stddev_min), h->cfg.stddev_max), h->cfg.sigma_floor);
         sigma[(size_t)q * nfd + r * D + d] = (float)sg;
       }
-  if (int rc = h2d(h, h->P.mean, mean.data(), mean.size())) return rc;
-  if (int rc = h2d(h, h->P.sigma, sigma.data(), sigma.size())) return rc;
-  CU(h, cudaMemsetAsync(h->P.best_valid, 0, Q * sizeof(int), h->stream));
-  CU(h, cudaMemsetAsync(h->P.any_success, 0, Q * sizeof(int), h->stream));
+  if (int rc = h2d(h, h->P.mean, ms.data(), ms.size())) return rc;
+  CU(h, cudaMemsetAsync(h->P.best_valid, 0, 2 * Q * sizeof(int), h->stream));   // best_valid | any_success
   return SSPPCU_OK;
 }
 
 int ssppcu_set_distribution(ssppcu_t* h, const double* mean, const double* sigma) {
   if (int rc = check(h)) return rc;
   const size_t n = (size_t)h->P.n_query * h->P.cfg.n_free * h->P.cfg.D;
-  std::vector<float> tmp(n);
-  if (mean) { for (size_t i = 0; i < n; ++i) tmp[i] = (float)mean[i]; if (int rc = h2d(h, h->P.mean, tmp.data(), n)) return rc; }
-  if (sigma) { for (size_t i = 0; i < n; ++i) tmp[i] = (float)sigma[i]; if (int rc = h2d(h, h->P.sigma, tmp.data(), n)) return rc; }
+  std::vector<float> tmp(2 * n);
+  if (mean) for (size_t i = 0; i < n; ++i) tmp[i] = (float)mean[i];
+  if (sigma) for (size_t i = 0; i < n; ++i) tmp[n + i] = (float)sigma[i];
+  if (mean && sigma) return h2d(h, h->P.mean, tmp.data(), 2 * n);            // neighbours in the live state block: one copy
+  if (mean) return h2d(h, h->P.mean, tmp.data(), n);
+  if (sigma) return h2d(h, h->P.sigma, tmp.data() + n, n);
   return SSPPCU_OK;
 }
 
@@ -628,8 +638,7 @@ int ssppcu_set_joint_noise(ssppcu_t* h, double sg, const double* limits) {
         mean[(size_t)q * nfd + r * D + d] = h->base_host[((size_t)q * s.K + s.free_begin + r) * D + d];
         sigma[(size_t)q * nfd + r * D + d] = sg * limits[d];
       }
-  CU(h, cudaMemsetAsync(h->P.best_valid, 0, Q * sizeof(int), h->stream));
-  CU(h, cudaMemsetAsync(h->P.any_success, 0, Q * sizeof(int), h->stream));
+  CU(h, cudaMemsetAsync(h->P.best_valid, 0, 2 * Q * sizeof(int), h->stream));   // best_valid | any_success
   return ssppcu_set_distribution(h, mean.data(), sigma.data());
 }
 
@@ -680,7 +689,14 @@ static int iterate_impl(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters,
   IterParams P = h->P;
   P.seed = seed; P.iter0 = iter0; P.n_inner = n_iters;
   P.state_in = restored ? h->d_state : nullptr;
+  const bool mirror = h->mirror_on && P.coop && !P.sort_only && h->h_res_dev;
+  if (mirror) {
+    P.host_out = h->h_res_dev; P.res_dev = h->d_res;
+    P.mir_bytes = (unsigned)h->res_bytes; P.mir_nsucc = (unsigned)h->o_nsucc; P.mir_nelite = (unsigned)h->o_nelite;
+    P.mir_bidx = (unsigned)h->o_bidx; P.mir_extra = (unsigned)h->o_extra;
+  }
   CU(h, launch_iterate(h->view, P, h->variant, h->threads, h->smem + h->smem_model, h->grid, h->stream));
+  h->res_fresh = mirror;
   return SSPPCU_OK;
 }
 
@@ -702,6 +718,12 @@ int ssppcu_phase_probe(ssppcu_t* h, int enable, unsigned long long* stamps, int 
 int ssppcu_iterate(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters) { return iterate_impl(h, seed, iter0, n_iters, false); }
 int ssppcu_iterate_restored(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters) { return iterate_impl(h, seed, iter0, n_iters, true); }
 
+int ssppcu_set_result_mirror(ssppcu_t* h, int on) {
+  if (int rc = check(h)) return rc;
+  h->mirror_on = on != 0;
+  return SSPPCU_OK;
+}
+
 int ssppcu_sync(ssppcu_t* h) {
   if (int rc = check(h)) return rc;
   CU(h, cudaStreamSynchronize(h->stream));
@@ -710,17 +732,18 @@ int ssppcu_sync(ssppcu_t* h) {
 
 int ssppcu_get_results(ssppcu_t* h, float* L, float* Cnf, float* Cwf, float* cost, uint8_t* status, int32_t* n_success,
                        int32_t* n_elite, int32_t* best_idx, float* best_cost, int32_t* any_success) {
+  const bool mirrored = h && h->res_fresh;                   // the launch just before this call wrote the pinned mirror itself
   if (int rc = check(h)) return rc;
   const size_t Q = h->P.n_query, QN = Q * h->P.cfg.n_cand;
-  // one copy of the result block into its pinned mirror (per-candidate arrays only when somebody wants them)
-  const bool per_cand = L || Cnf || Cwf || cost || status;
-  const size_t from = per_cand ? 0 : h->o_nsucc;
-  CU(h, cudaMemcpyAsync(h->h_res + from, h->d_res + from, h->res_bytes - from, cudaMemcpyDeviceToHost, h->stream));
-  int32_t* h_any = reinterpret_cast<int32_t*>(h->h_res + h->o_extra);
-  if (any_success) CU(h, cudaMemcpyAsync(h_any, h->P.any_success, Q * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
-  {   // best | best_valid ride along: a get_best right after this call needs no second round trip
-    const size_t nfd = (size_t)h->P.cfg.n_free * h->P.cfg.D;
-    CU(h, cudaMemcpyAsync(h->h_res + h->o_extra + Q * 4, h->P.best, Q * nfd * 4 + Q * 4, cudaMemcpyDeviceToHost, h->stream));
+  const size_t nfd = (size_t)h->P.cfg.n_free * h->P.cfg.D;
+  int32_t* h_any = reinterpret_cast<int32_t*>(h->h_res + h->o_extra + Q * nfd * 4 + Q * 4);   // mirror tail: best | best_valid | any_success
+  if (!mirrored) {
+    // one copy of the result block into its pinned mirror (per-candidate arrays only when somebody wants them)
+    const bool per_cand = L || Cnf || Cwf || cost || status;
+    const size_t from = per_cand ? 0 : h->o_nsucc;
+    CU(h, cudaMemcpyAsync(h->h_res + from, h->d_res + from, h->res_bytes - from, cudaMemcpyDeviceToHost, h->stream));
+    // best | best_valid | any_success (the tail of the live state block) ride along: a get_best right after this call needs no second round trip
+    CU(h, cudaMemcpyAsync(h->h_res + h->o_extra, h->P.best, Q * nfd * 4 + 2 * Q * 4, cudaMemcpyDeviceToHost, h->stream));
   }
   CU(h, cudaStreamSynchronize(h->stream));
   if (L) std::memcpy(L, h->h_res + h->o_L, QN * 4);
@@ -750,7 +773,7 @@ int ssppcu_get_best(ssppcu_t* h, float* best, int32_t* valid) {
   const bool fresh = h && h->best_fresh;                     // fetched by the ssppcu_get_results call just before this one
   if (int rc = check(h)) return rc;
   const size_t Q = h->P.n_query, nfd = (size_t)h->P.cfg.n_free * h->P.cfg.D;
-  unsigned char* m = h->h_res + h->o_extra + Q * 4;          // after the any_success mirror
+  unsigned char* m = h->h_res + h->o_extra;                  // mirror tail: best | best_valid | any_success
   if (!fresh) {
     CU(h, cudaMemcpyAsync(m, h->P.best, Q * nfd * 4 + Q * 4, cudaMemcpyDeviceToHost, h->stream));   // best | best_valid
     CU(h, cudaStreamSynchronize(h->stream));

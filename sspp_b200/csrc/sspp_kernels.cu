@@ -595,7 +595,7 @@ __device__ void rank_phase(const IterParams& P, unsigned char* smem_raw, unsigne
 }
 
 // ---- coop phase C: one CTA per (query, distribution element); element nfd = the query's scalars ----
-__device__ void update_phase(const IterParams& P, float* s_part, float* s_val, int s_val_cap) {
+__device__ void update_phase(const IterParams& P, float* s_part, float* s_val, int s_val_cap, bool mirror) {
   const ScoreConfig& c = P.cfg;
   const int tid = threadIdx.x, T = blockDim.x;
   const int nfd = c.n_free * c.D, N = c.n_cand;
@@ -608,7 +608,13 @@ __device__ void update_phase(const IterParams& P, float* s_part, float* s_val, i
     float* mean = P.mean + (size_t)query * nfd;
     float* sigma = P.sigma + (size_t)query * nfd;
     if (t == nfd) {                     // scalars + elite weights of the query
-      if (tid == 0) { P.n_success[query] = n_succ; P.n_elite[query] = k; }
+      if (tid == 0) {
+        P.n_success[query] = n_succ; P.n_elite[query] = k;
+        if (mirror) {                   // the two scalars mirror_scalars() leaves out (it runs beside this CTA)
+          reinterpret_cast<int*>(P.host_out + P.mir_nsucc)[query] = n_succ;
+          reinterpret_cast<int*>(P.host_out + P.mir_nelite)[query] = k;
+        }
+      }
       if (n_succ > 0) {
         const float lk = log_poly((float)k + 0.5f);
         const float sumw = ces_weight_sum(k, lk, CtaSum{s_part});
@@ -631,6 +637,31 @@ __device__ void update_phase(const IterParams& P, float* s_part, float* s_val, i
       update_element(c, k, lk, sumw, t, mean, sigma, [&](int j) { return gp((unsigned)(keys[j] & 0xFFFFFFFFu), t); }, CtaSum{s_part}, tid == 0);
     }
   }
+}
+
+// ---- coop: result block -> its mirror in mapped pinned host memory (IterParams::host_out) ----
+// L / Cnf / Cwf / cost / status are final at grid barrier 1: they go out right behind it as 16-byte vectors, one per
+// thread, by the CTAs at the top of the grid; the stores are posted, so they drain over PCIe while the keys are ranked
+// and the distribution is updated.  best_idx / best_cost and best | best_valid | any_success are final at barrier 2
+// and follow there; update_phase writes n_success / n_elite to both places.  ssppcu_get_results then needs no D2H copy.
+__device__ __forceinline__ void mirror_candidates(const IterParams& P) {
+  const unsigned tid = threadIdx.x, T = blockDim.x;
+  const unsigned total = P.mir_nsucc >> 4;                // [0, n_success): the per-candidate arrays
+  const uint4* src = reinterpret_cast<const uint4*>(P.res_dev);
+  uint4* dst = reinterpret_cast<uint4*>(P.host_out);
+  for (unsigned v = (gridDim.x - 1 - blockIdx.x) * T + tid; v < total; v += gridDim.x * T) dst[v] = __ldcg(src + v);
+}
+__device__ __forceinline__ void mirror_scalars(const IterParams& P) {
+  if (blockIdx.x != gridDim.x - 1) return;
+  const unsigned tid = threadIdx.x, T = blockDim.x;
+  const unsigned w0 = P.mir_bidx >> 2, w1 = P.mir_bytes >> 2;     // [best_idx, end of the block)
+  const unsigned* src = reinterpret_cast<const unsigned*>(P.res_dev);
+  unsigned* dst = reinterpret_cast<unsigned*>(P.host_out);
+  for (unsigned e = w0 + tid; e < w1; e += T) dst[e] = __ldcg(src + e);
+  const unsigned words = (unsigned)P.n_query * (unsigned)(P.cfg.n_free * P.cfg.D + 2);   // best | best_valid | any_success
+  const unsigned* s = reinterpret_cast<const unsigned*>(P.best);
+  unsigned* d = reinterpret_cast<unsigned*>(P.host_out + P.mir_extra);
+  for (unsigned e = tid; e < words; e += T) d[e] = __ldcg(s + e);
 }
 
 // ---- population shard with the fused key exchange (ExchangeParams, sspp_kernels.h) ----
@@ -815,6 +846,8 @@ sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant_
     stamp(it, 1);
     grid.sync();
     stamp(it, 2);
+    const bool mirror = P.host_out != nullptr && it + 1 == P.n_inner;
+    if (mirror) mirror_candidates(P);
     if (handout && blockIdx.x == 0 && tid == 0) *P.tile_counter = 0;   // nobody draws again before the next iteration's barrier
     // ---- phase B: order the keys ----
     rank_phase(P, smem_raw, &s_mbar, mbar_phase, [&](int slot) { stamp(it, slot); });
@@ -827,7 +860,8 @@ sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant_
     grid.sync();
     stamp(it, 4);
     // ---- phase C: distribution update ----
-    update_phase(P, s_part, reinterpret_cast<float*>(smem_raw), P.smem_words);
+    if (mirror) mirror_scalars(P);
+    update_phase(P, s_part, reinterpret_cast<float*>(smem_raw), P.smem_words, mirror);
     stamp(it, 5);
     if (it + 1 < P.n_inner) grid.sync();
   }

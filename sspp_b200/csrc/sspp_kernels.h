@@ -48,6 +48,10 @@ struct IterParams {
   int* tile_counter;        // coop, more tiles than CTAs: tiles beyond the first wave are handed out from this counter (zero between iterations)
   const struct ExchangeParams* xchg;  // population shard with the fused key exchange (device-resident block), else NULL
   unsigned xchg_epoch;      // value this launch publishes in the peers' flag words (monotonic per handle, > 0)
+  // result mirror (coop kernel, last inner iteration of a launch; NULL = off): host_out is the device address of a mapped pinned
+  // host block laid out like the result block at res_dev, with best | best_valid | any_success behind it at mir_extra
+  unsigned char* host_out; const unsigned char* res_dev;
+  unsigned mir_bytes, mir_nsucc, mir_nelite, mir_bidx, mir_extra;   // byte offsets (multiples of 16): block end, n_success, n_elite, best_idx
   unsigned long long* probe; // diagnostics, NULL = off: [grid][kProbeSlots] %globaltimer stamps at the phase boundaries (coop kernel)
 };
 

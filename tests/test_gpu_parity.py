@@ -303,6 +303,28 @@ def test_best_read_after_results_needs_no_second_fetch_and_stays_current():
     case.prepare(h)                                   # reset_distribution clears the forwarded best
     _, v4 = h.best()
     assert v4[0] == 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_iters", [1, 3])
+def test_results_mirrored_by_the_kernel_equal_the_copied_ones(n_iters):
+    """the cooperative kernel copies the result block into the mapped pinned mirror itself (mirror_results): a read-back
+    right after the launch does no D2H copy.  Any call in between (here: sync) makes get_results copy the device block
+    instead - both must give the same bytes, for every array, the scalars and best, and re-used output buffers too"""
+    case = joint_case(n_samples=2046, check_points=32, n_points=10, do_update=True)
+    h = _handle(case)
+    assert h.dims.ctas_per_query > 1                  # the cooperative shape
+    buf = None
+    for it in range(3):
+        h.iterate(SEED, it * n_iters, n_iters)
+        buf = h.results(buf); b_m, v_m = h.best()     # mirrored by the kernel
+        r_m = {k: buf[k].copy() for k in h._RES_KEYS}
+        h.sync()
+        r_c = h.results(); b_c, v_c = h.best()        # copied from the device block
+        for k in h._RES_KEYS:
+            assert np.array_equal(r_m[k], r_c[k]), (it, k)
+        assert np.array_equal(b_m, b_c) and np.array_equal(v_m, v_c)
+        assert r_m["n_success"][0] > 0 and r_m["n_elite"][0] > 0 and v_m[0] == 1
     h.close()
 
 
