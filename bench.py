@@ -211,6 +211,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         raise SystemExit("bench.py: no CUDA device; the scoring path has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # NCCL's version / INFO lines go to stdout otherwise: stdout is the ONE JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():

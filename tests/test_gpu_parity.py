@@ -357,3 +357,27 @@ def test_phase_probe_stamps_are_ordered():
     assert (np.diff(st[:, :6], axis=1) >= 0).all()              # start <= scored <= barrier 1 <= ranked <= barrier 2 <= updated
     assert st[:, 2].min() >= st[:, 1].max() - 2000              # nobody passes barrier 1 before everybody has scored (timer granularity)
     h.close()
+
+
+def test_set_distribution_round_trips_mean_sigma_and_either_alone():
+    """ssppcu_set_distribution: both blocks in one staged copy, or either alone without touching the other"""
+    case = task_case(n_samples=30, check_points=20, n_queries=3)
+    h = _handle(case)
+    d = h.dims
+    rng = np.random.default_rng(5)
+    m0, s0 = h.get_distribution()
+    m1 = rng.uniform(-1, 1, m0.shape).astype(np.float32).astype(np.float64)
+    s1 = rng.uniform(0.01, 0.5, s0.shape).astype(np.float32).astype(np.float64)
+    h.set_distribution(mean=m1)
+    m, s = h.get_distribution()
+    assert np.array_equal(m, m1) and np.array_equal(s, s0)
+    h.set_distribution(sigma=s1)
+    m, s = h.get_distribution()
+    assert np.array_equal(m, m1) and np.array_equal(s, s1)
+    h.set_distribution(mean=m0, sigma=s0)
+    m, s = h.get_distribution()
+    assert np.array_equal(m, m0) and np.array_equal(s, s0)
+    case.prepare(h)                                   # reset: best_valid | any_success cleared by one memset
+    h.iterate(SEED, 0, 1)
+    r = h.results()
+    assert r["any_success"].shape == (d.n_queries,)
