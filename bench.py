@@ -196,7 +196,7 @@ def run_reference(args, rank: int, world: int):
                 data="synthetic", config=desc,
                 cpu_baseline=dict(value=val, unit=UNIT, cores=arm.cores, kind="port", sample=sample),
                 e2e=dict(value=val, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0))
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------
@@ -211,7 +211,6 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         raise SystemExit("bench.py: no CUDA device; the scoring path has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # NCCL's version / INFO lines go to stdout otherwise: stdout is the ONE JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():
@@ -321,11 +320,20 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         line["cpu_baseline"] = cpu_baseline(case)
     # elites of the last step as a sanity field
     line["last_step"] = dict(n_success=int(res["n_success"][0]), n_elite=int(res["n_elite"][0]), best_cost=float(res["best_cost"][0]))
-    print(json.dumps(line), flush=True)
+    emit(line)
     h.close()
 
 
+_JSON_FD = 1
+
+
+def emit(line: dict):
+    """the ONE JSON line, on the process's original stdout"""
+    os.write(_JSON_FD, (json.dumps(line) + "\n").encode())
+
+
 def main():
+    global _JSON_FD
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -335,6 +343,11 @@ def main():
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29531"), __file__] + sys.argv[1:]
         raise SystemExit(subprocess.call(cmd))
+    # stdout carries the JSON line and nothing else: libraries that print there (NCCL writes its version line to stdout
+    # when the box exports NCCL_DEBUG=VERSION, and honours NCCL_DEBUG_FILE only above that level) are sent to stderr
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args, rank, world)
         return

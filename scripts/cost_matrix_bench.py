@@ -29,11 +29,13 @@ W, BATCH, ITERS, REPS = int(os.environ.get("CM_WAYPOINTS", 256)), int(os.environ
 
 
 def main():
+    sys.stdout.flush()
+    json_fd = os.dup(1)                                  # stdout = the JSON line only (NCCL prints its version there)
+    os.dup2(2, 1)
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     case = task_case(n_queries=BATCH)
     case.cfg.device = local
@@ -65,14 +67,14 @@ def main():
     d = planner.h.dims
     if rank == 0:
         off = m[np.triu_indices(W, 1)]
-        print(json.dumps(dict(
+        os.write(json_fd, (json.dumps(dict(
             workload=f"cfg5: {W} waypoints, {n_pairs} Planner-B plans x {ITERS} iterations x {d.n_cand} candidates x "
                      f"{case.cfg.check_points} collocation points, robocrane.xml gripper, batches of {BATCH} pairs",
             n_gpus=world, seconds=s, plans_per_s=n_pairs / s,
             points_per_s=n_pairs * ITERS * d.n_cand * case.cfg.check_points / s,
             launches_per_rank=planner.launches // (REPS + 1), reps=REPS, times=times,
             finite_entries=int(np.isfinite(off).sum()), mean_finite_cost=float(off[np.isfinite(off)].mean()),
-            symmetric=bool(np.array_equal(m, m.T)), matrix_crc=zlib.crc32(m.tobytes()))))
+            symmetric=bool(np.array_equal(m, m.T)), matrix_crc=zlib.crc32(m.tobytes()))) + "\n").encode())
     planner.close()
     if world > 1:
         dist.destroy_process_group()
