@@ -644,14 +644,14 @@ __device__ void update_phase(const IterParams& P, float* s_part, float* s_val, i
 // thread, by the CTAs at the top of the grid; the stores are posted, so they drain over PCIe while the keys are ranked
 // and the distribution is updated.  best_idx / best_cost and best | best_valid | any_success are final at barrier 2
 // and follow there; update_phase writes n_success / n_elite to both places.  ssppcu_get_results then needs no D2H copy.
-__device__ __forceinline__ void mirror_candidates(const IterParams& P) {
+__device__ __noinline__ void mirror_candidates(const IterParams& P) {
   const unsigned tid = threadIdx.x, T = blockDim.x;
   const unsigned total = P.mir_nsucc >> 4;                // [0, n_success): the per-candidate arrays
   const uint4* src = reinterpret_cast<const uint4*>(P.res_dev);
   uint4* dst = reinterpret_cast<uint4*>(P.host_out);
   for (unsigned v = (gridDim.x - 1 - blockIdx.x) * T + tid; v < total; v += gridDim.x * T) dst[v] = __ldcg(src + v);
 }
-__device__ __forceinline__ void mirror_scalars(const IterParams& P) {
+__device__ __noinline__ void mirror_scalars(const IterParams& P) {
   if (blockIdx.x != gridDim.x - 1) return;
   const unsigned tid = threadIdx.x, T = blockDim.x;
   const unsigned w0 = P.mir_bidx >> 2, w1 = P.mir_bytes >> 2;     // [best_idx, end of the block)
