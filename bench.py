@@ -305,6 +305,11 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     n_e2e = min(args.steps, 200)
     h.set_result_mirror(True)                        # the library's default: the kernel fills the pinned result mirror itself
     res, best = h.results(), h.best()                # caller-owned host buffers, refilled by every step
+    for i in range(max(args.warmup, 3)):             # untimed: the mirroring instantiation of the kernel is loaded by its first launch
+        case.prepare(h)
+        h.iterate(SEED, i * inner, inner)
+        res = h.results(res)
+        best = h.best(best)
     barrier()
     t0 = time.perf_counter()
     for i in range(n_e2e):

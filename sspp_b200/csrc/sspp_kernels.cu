@@ -595,7 +595,9 @@ __device__ void rank_phase(const IterParams& P, unsigned char* smem_raw, unsigne
 }
 
 // ---- coop phase C: one CTA per (query, distribution element); element nfd = the query's scalars ----
-__device__ void update_phase(const IterParams& P, float* s_part, float* s_val, int s_val_cap, bool mirror) {
+template <bool MIRROR>
+__device__ void update_phase(const IterParams& P, float* s_part, float* s_val, int s_val_cap, bool mirror_now) {
+  const bool mirror = MIRROR && mirror_now;
   const ScoreConfig& c = P.cfg;
   const int tid = threadIdx.x, T = blockDim.x;
   const int nfd = c.n_free * c.D, N = c.n_cand;
@@ -759,7 +761,9 @@ __device__ void exchange_and_merge(const IterParams& P, cg::grid_group& grid, fl
 
 // Launch-bound variants: (max threads, min CTAs per SM) fixes the register budget ptxas works with, and so
 // the resident warps per SM; the handle picks one per problem shape (kIterVariants, sspp_kernels.h).
-template <bool COOP, int MAXT, int MINB>
+// MIRROR (cooperative shapes only): the instantiation that posts its results to the mapped pinned host block; the plain
+// one carries none of that code, so a device-resident caller runs exactly the kernel that was tuned without it
+template <bool COOP, int MAXT, int MINB, bool MIRROR = false>
 __global__ void __launch_bounds__(MAXT, MINB)
 sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant__ IterParams P) {
   __shared__ int s_int[4];
@@ -846,7 +850,7 @@ sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant_
     stamp(it, 1);
     grid.sync();
     stamp(it, 2);
-    const bool mirror = P.host_out != nullptr && it + 1 == P.n_inner;
+    const bool mirror = MIRROR && it + 1 == P.n_inner;
     if (mirror) mirror_candidates(P);
     if (handout && blockIdx.x == 0 && tid == 0) *P.tile_counter = 0;   // nobody draws again before the next iteration's barrier
     // ---- phase B: order the keys ----
@@ -861,7 +865,7 @@ sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant_
     stamp(it, 4);
     // ---- phase C: distribution update ----
     if (mirror) mirror_scalars(P);
-    update_phase(P, s_part, reinterpret_cast<float*>(smem_raw), P.smem_words, mirror);
+    update_phase<MIRROR>(P, s_part, reinterpret_cast<float*>(smem_raw), P.smem_words, mirror);
     stamp(it, 5);
     if (it + 1 < P.n_inner) grid.sync();
   }
@@ -1142,9 +1146,11 @@ size_t iterate_smem_bytes(const ssppm::DevModelHead& M, const IterParams& P, int
 
 namespace {
 using IterKernel = void (*)(const ModelView, const IterParams);
-struct VariantFns { IterKernel coop, solo; };
+struct VariantFns { IterKernel coop, solo, coop_mirror; };
 template <int MAXT, int MINB>
-constexpr VariantFns variant_fns() { return {sspp_iterate_kernel<true, MAXT, MINB>, sspp_iterate_kernel<false, MAXT, MINB>}; }
+constexpr VariantFns variant_fns() {
+  return {sspp_iterate_kernel<true, MAXT, MINB>, sspp_iterate_kernel<false, MAXT, MINB>, sspp_iterate_kernel<true, MAXT, MINB, true>};
+}
 // same order as kIterVariants
 #ifdef SSPP_FAST_BUILD   // kernel experiments: only the two default variants are compiled (the others alias them)
 const VariantFns kFns[kNumIterVariants] = {variant_fns<256, 2>(), variant_fns<256, 2>(), variant_fns<320, 2>(), variant_fns<320, 2>(),
@@ -1175,10 +1181,11 @@ cudaError_t launch_iterate(const ModelView& M, const IterParams& P, int variant,
     kFns[variant].solo<<<(unsigned)P.n_tiles, threads, smem_bytes, stream>>>(M, P);
     return cudaGetLastError();
   }
-  cudaError_t e = set_smem(kFns[variant].coop, smem_bytes);
+  const IterKernel k = P.host_out ? kFns[variant].coop_mirror : kFns[variant].coop;
+  cudaError_t e = set_smem(k, smem_bytes);
   if (e != cudaSuccess) return e;
   void* args[] = {const_cast<ModelView*>(&M), const_cast<IterParams*>(&P)};
-  return cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(kFns[variant].coop), dim3((unsigned)grid), dim3((unsigned)threads),
+  return cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(k), dim3((unsigned)grid), dim3((unsigned)threads),
                                      args, smem_bytes, stream);
 }
 
