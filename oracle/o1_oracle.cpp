@@ -149,16 +149,16 @@ void geom_frames(const Model& m, const std::vector<V3>& xpos, const std::vector<
 }
 
 // full qpos from the planned coordinates
-std::vector<double> make_qpos(const Model& m, const double* q) {
-  std::vector<double> qp = m.qpos0;
+void make_qpos(const Model& m, const double* q, std::vector<double>& qp) {
+  qp = m.qpos0;
   if (m.mode == 0) { for (int d = 0; d < m.dof; ++d) qp[d] = q[d]; }
   else {   // utility.h:149-175: x,y,z then quaternion of a pure yaw
     const int a = m.qadr[m.plan_body];
     qp[a] = q[0]; qp[a + 1] = q[1]; qp[a + 2] = q[2];
     qp[a + 3] = std::cos(q[3] / 2); qp[a + 4] = 0; qp[a + 5] = 0; qp[a + 6] = std::sin(q[3] / 2);
   }
-  return qp;
 }
+std::vector<double> make_qpos(const Model& m, const double* q) { std::vector<double> qp; make_qpos(m, q, qp); return qp; }
 
 // ---- narrow phase (signed distance, negative = penetration depth) ----
 V3 to_local(const Geom& B, V3 w) { V3 d = w - B.p; return {dot(d, B.ax[0]), dot(d, B.ax[1]), dot(d, B.ax[2])}; }
@@ -197,7 +197,7 @@ double segment_box(V3 p0, V3 p1, V3 h) {   // box frame; convex in t: golden-sec
   double lo = 0, hi = 1;
   const double gr = (std::sqrt(5.0) - 1) / 2;
   double c = hi - gr * (hi - lo), d = lo + gr * (hi - lo), fc = f(c), fd = f(d);
-  for (int it = 0; it < 200; ++it) {
+  for (int it = 0; it < 200 && hi - lo > 1e-14; ++it) {   // the bracket shrinks by 0.618 per step: 67 steps reach 1e-14
     if (fc <= fd) { hi = d; d = c; fd = fc; c = hi - gr * (hi - lo); fc = f(c); }
     else { lo = c; c = d; fc = fd; d = lo + gr * (hi - lo); fd = f(d); }
   }
@@ -301,9 +301,15 @@ double sdf_value(const Model& m, V3 x) {   // trilinear interpolation, coordinat
 }
 
 // collision cost of one configuration: the whole scene, as mj_forward + the reference's read-out
-double point_cost(const Model& m, const double* q, int* ncon_out, double* min_dist_out) {
-  std::vector<V3> xpos; std::vector<Quat> xquat; std::vector<Geom> G;
-  kinematics(m, make_qpos(m, q), xpos, xquat);
+// band_out (optional): number of tested pairs / sphere samples whose signed distance lies within EPS_BAND of a decision
+// threshold (planner A: the pair's margin, sspp.h:144 through MuJoCo's dist < margin; planner B: -1e-3, Collision.h:93) -
+// where FP32 and FP64 may legitimately decide differently
+constexpr double EPS_BAND = 1e-4;
+double point_cost(const Model& m, const double* q, int* ncon_out, double* min_dist_out, int* band_out = nullptr) {
+  static thread_local std::vector<V3> xpos; static thread_local std::vector<Quat> xquat; static thread_local std::vector<Geom> G;
+  static thread_local std::vector<double> qp;      // scratch reused across calls (one set per OpenMP thread)
+  make_qpos(m, q, qp);
+  kinematics(m, qp, xpos, xquat);
   geom_frames(m, xpos, xquat, G);
   double cost = 0.0, mind = std::numeric_limits<double>::infinity();
   int ncon = 0;
@@ -312,6 +318,7 @@ double point_cost(const Model& m, const double* q, int* ncon_out, double* min_di
       const V3 c = xpos[sp.body] + qrot(xquat[sp.body], sp.c);
       const double d = sdf_value(m, c) - sp.r;
       mind = std::min(mind, d);
+      if (band_out && std::fabs(d - (m.mode == 0 ? m.sdf_margin : -1e-3)) <= EPS_BAND) ++*band_out;
       if (!(d < m.sdf_margin)) continue;
       ++ncon;
       if (m.mode == 0) cost += 1.0;
@@ -327,6 +334,7 @@ double point_cost(const Model& m, const double* q, int* ncon_out, double* min_di
     if (!ok) continue;
     mind = std::min(mind, d);
     const double margin = std::max(m.gmargin[pr.first], m.gmargin[pr.second]);
+    if (band_out && std::fabs(d - (m.mode == 0 ? margin : std::min(margin, -1e-3))) <= EPS_BAND) ++*band_out;
     if (!(d < margin)) continue;   // MuJoCo keeps a contact iff dist < margin
     ++ncon;
     if (m.mode == 0) cost += 1.0;                                   // sspp.h:144  ncon > 0
@@ -534,7 +542,7 @@ void o1_basis_row(int K, int p, const double* knots, double u, double* out) {
 //   base [K][D] point matrix (control points for JOINT, interpolation points for TASK)
 //   params [n][n_free*D] -> L, Cnf, Cwf, cost, status per candidate; pts_out (optional) [n][M+1][D]
 void o1_score(void* h, const Cfg* c, const double* base, const double* params, int n, double* L, double* Cnf, double* Cwf,
-              double* cost, int32_t* status, double* min_dist_out, double* pts_out) {
+              double* cost, int32_t* status, double* min_dist_out, double* pts_out, int32_t* band_out) {
   const Model& m = *static_cast<Model*>(h);
   const int K = c->K, D = c->D, p = c->p, M = c->M;
   const std::vector<double> t = averaged_knots(K, p);
@@ -545,12 +553,13 @@ void o1_score(void* h, const Cfg* c, const double* base, const double* params, i
     std::vector<double> ctrl = (c->mode == 0) ? X : interpolate(X, K, D, p, t);   // tsp_path_model.h:32-43
     double pt[9], prev[9];
     double len = 0, cnf = 0, cwf = 0, md_all = std::numeric_limits<double>::infinity();
+    int band = 0;
     if (c->mode == 0) {
       for (int k = 0; k <= M; ++k) {                          // sspp.h:134-148 (no early exit: same flag)
         spline_point(ctrl, K, D, p, t, (double)k / M, pt);
         if (pts_out) std::copy(pt, pt + D, pts_out + ((size_t)i * (M + 1) + k) * D);
         int ncon; double md;
-        const double cc = point_cost(m, pt, &ncon, &md);
+        const double cc = point_cost(m, pt, &ncon, &md, &band);
         md_all = std::min(md_all, md);
         double pen = 0;
         if (c->limit_scale > 0) for (int d = 0; d < D; ++d) { const double ex = std::fabs(pt[d]) - c->hi[d]; if (ex > 0) pen += c->limit_scale * ex * ex; }
@@ -572,7 +581,7 @@ void o1_score(void* h, const Cfg* c, const double* base, const double* params, i
         double s2 = 0; for (int d = 0; d < D; ++d) s2 += (pt[d] - prev[d]) * (pt[d] - prev[d]);
         len += std::sqrt(s2);
         int ncon; double md;
-        const double cc = point_cost(m, pt, &ncon, &md);
+        const double cc = point_cost(m, pt, &ncon, &md, &band);
         md_all = std::min(md_all, md);
         const double deficit = (c->eval_zmin + c->floor_margin) - pt[2];
         const double fl = deficit > 0 ? c->floor_scale * deficit * deficit : 0.0;
@@ -583,6 +592,7 @@ void o1_score(void* h, const Cfg* c, const double* base, const double* params, i
     L[i] = len; Cnf[i] = cnf; Cwf[i] = cwf; cost[i] = len + c->w_collision * cwf;
     status[i] = (cnf == 0.0) ? 0 : 1;                         // tsp_planner.h:110
     if (min_dist_out) min_dist_out[i] = md_all;
+    if (band_out) band_out[i] = band;
   }
 }
 

@@ -76,7 +76,7 @@ class O1:
         L.o1_num_pairs.argtypes = [C.c_void_p]
         L.o1_get_pairs.argtypes = [C.c_void_p, C.c_void_p]
         L.o1_destroy.argtypes = [C.c_void_p]
-        L.o1_score.argtypes = [C.c_void_p, C.POINTER(O1Cfg), _dp, _dp, C.c_int, _dp, _dp, _dp, _dp, C.c_void_p, _dp, _dp]
+        L.o1_score.argtypes = [C.c_void_p, C.POINTER(O1Cfg), _dp, _dp, C.c_int, _dp, _dp, _dp, _dp, C.c_void_p, _dp, _dp, C.c_void_p]
         L.o1_elites.argtypes = [_dp, C.c_void_p, C.c_int, C.c_double, C.c_void_p, _dp, C.POINTER(C.c_int32)]
         L.o1_update.argtypes = [C.POINTER(O1Cfg), _dp, _dp, _dp, _dp, C.c_int]
         L.o1_sample.argtypes = [C.POINTER(O1Cfg), C.c_uint64, C.c_uint32, C.c_uint32, C.c_int, C.c_int, _dp, _dp, _dp]
@@ -145,9 +145,10 @@ class O1:
         L = np.zeros(n); Cnf = np.zeros(n); Cwf = np.zeros(n); cost = np.zeros(n); md = np.zeros(n)
         st = np.zeros(n, np.int32)
         pts = np.zeros((n, cfg.M + 1, cfg.D)) if want_points else None
+        band = np.zeros(n, np.int32)      # decisions within EPS_BAND of a threshold, per candidate
         self.lib.o1_score(self.h, C.byref(cfg), _d(base), _d(params), n, _d(L), _d(Cnf), _d(Cwf), _d(cost),
-                          st.ctypes.data_as(C.c_void_p), _d(md), None if pts is None else _d(pts))
-        return dict(L=L, Cnf=Cnf, Cwf=Cwf, cost=cost, status=st, min_dist=md, pts=pts)
+                          st.ctypes.data_as(C.c_void_p), _d(md), None if pts is None else _d(pts), band.ctypes.data_as(C.c_void_p))
+        return dict(L=L, Cnf=Cnf, Cwf=Cwf, cost=cost, status=st, min_dist=md, pts=pts, band=band)
 
     def elites(self, cost, status, frac: float):
         cost = np.ascontiguousarray(cost, np.float64); status = np.ascontiguousarray(status, np.int32)

@@ -21,9 +21,10 @@ def test_cfg3_full_size_matches_replica_and_shards():
     N = 65536
     case = sdf_case(n_samples=N - 2, check_points=64, n_points=5, dims=(128, 128, 128))
     h = capi.Handle(case.model, case.cfg); case.prepare(h)
-    rep = compare_iteration(h, case, iters=2, check_o1=False)
-    for k in EXACT:
+    rep = compare_iteration(h, case, iters=2)            # O1 leg on 512 seeded candidates of the 65536 per iteration
+    for k in EXACT + ("o1_flag_mismatch",):
         assert rep[k] == 0, rep
+    assert rep["o1_max_rel"] <= 1e-5 and rep["o1_checked"] >= 1000, rep
     assert 0 < min(rep["n_success"]) and max(rep["n_success"]) < N
     h.close()
 
@@ -81,9 +82,10 @@ def test_cfg4_full_batch_queries_match_replica():
     case = task_case(n_queries=Q, start=s, end=e)
     for q in rng.choice(Q, 3, replace=False):
         h = capi.Handle(case.model, case.cfg); case.prepare(h)
-        rep = compare_iteration(h, case, iters=12, query=int(q), check_o1=False)
-        for k in EXACT:
+        rep = compare_iteration(h, case, iters=12, query=int(q))
+        for k in EXACT + ("o1_flag_mismatch",):
             assert rep[k] == 0, (int(q), rep)
+        assert rep["o1_max_rel"] <= 1e-5, (int(q), rep)
         h.close()
     h = capi.Handle(case.model, case.cfg); case.prepare(h)
     h.iterate(SEED, 0, 60)                                           # a whole 60-iteration plan of every query in one launch

@@ -148,6 +148,10 @@ def test_scored_iteration_agrees(kind):
         np.testing.assert_allclose(r["L"][ok], s1["L"][ok], rtol=REL)
         good = ok & (r["status"] == 0)
         np.testing.assert_allclose(r["cost"][good], s1["cost"][good], rtol=REL, atol=1e-6)
+        clean = ok & (s1["band"] == 0)           # failed candidates too: collision sums agree unless a decision sat in the contact band
+        assert clean.sum() >= 0.8 * live.sum()
+        for k in ("Cnf", "Cwf", "cost"):
+            np.testing.assert_allclose(r[k][clean], s1[k][clean], rtol=REL, atol=1e-5)
         # elites + update from the replica's own costs (so ties/ordering are the same question)
         st = np.where(r["status"] == 0, 0, 1).astype(np.int32)
         idx, w, ns = o1.elites(r["cost"].astype(np.float64), st, case.cfg.elite_fraction)
