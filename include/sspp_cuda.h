@@ -131,6 +131,24 @@ int ssppcu_model_pair_counts(const ssppcu_model_t* m, int mode, int dof, const c
                              int32_t* n_moving_static, int32_t* n_moving_moving, int32_t* n_static_static,
                              char* err, size_t errlen);
 
+/* ---- the reference's Python spline twins as product functions (host FP64) ----
+ * sspp/BSplines.py:58-62 knot_vector: clamped uniform knots, n_ctrl + k + 1 values. */
+int ssppcu_bspline_knot_vector(int n_ctrl, int k, double* knots);
+/* Rows [n_theta][n_ctrl] over a knot vector of n_ctrl + k + 1 values.  kind 0: B(theta, k, i, t) for every i
+ * (BSplines.py:11-29, half-open spans); 1: dB (:31-42); 2: the row r with bspline(theta, t, c, k) = r . c including the
+ * end rules theta < 0 / theta >= 1 (:44-51); 3: bspline_derivative (:53-55). */
+int ssppcu_bspline_rows(int n_ctrl, int k, const double* knots, const double* theta, int n_theta, int kind, double* out);
+/* sspp/BSplines.py:65-106 compute_control_points: via [n][d] at theta_i = i/(n-1) -> ctrl [n][d], knots [n + k + 1] (may be NULL) */
+int ssppcu_bspline_fit(const double* via, int n, int d, int k, double* ctrl, double* knots);
+/* sspp/CubicPath.py:8-60: the cubic through start, via (u = 1/2), end with zero start velocity, at u[n_u] (clipped to [0,1]):
+ * pos / vel / acc [n_u][d], each may be NULL */
+int ssppcu_cubic_path(const double* start, const double* via, const double* end, int d, const double* u, int n_u, double* pos, double* vel,
+                      double* acc);
+/* Batched evaluation on the GPU: out[n_curves][n_theta][d] = rows[n_theta][n_ctrl] . ctrl[n_curves][n_ctrl][d] in FP32 (rows from
+ * ssppcu_bspline_rows kind 2 / 3, cast to float).  Host pointers; fails with SSPPCU_ECUDA without a device. */
+int ssppcu_bspline_eval_batch(int device, const float* rows, int n_theta, int n_ctrl, const float* ctrl, int n_curves, int d, float* out,
+                              char* err, size_t errlen);
+
 /* ---- planner handle ---- */
 void ssppcu_default_config(int mode, SsppPlannerConfig* cfg);
 int ssppcu_create(const ssppcu_model_t* m, const SsppPlannerConfig* cfg, ssppcu_t** out, char* err, size_t errlen);
@@ -162,6 +180,13 @@ int ssppcu_iterate(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters);
  * the live state with it (a planner that is reset before every plan(), tsp_planner.h:54-69, needs no separate
  * device-to-device copy) */
 int ssppcu_iterate_restored(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters);
+/* One cold-start planner step in ONE call and ONE launch: ssppcu_set_queries + ssppcu_set_joint_noise (JOINT: sigma,
+ * limits - sspp.h:194-216) or ssppcu_reset_distribution (TASK: sigma = sigma0, limits ignored - tsp_planner.h:72-75 with
+ * iterate = false) + ssppcu_iterate.  The query's point matrices and initial state travel in the kernel's parameter block
+ * (no host-to-device copy precedes the launch) when they fit (1 KiB: one to a few queries); otherwise the three calls run
+ * as they are.  Same results bit for bit either way. */
+int ssppcu_plan_step(ssppcu_t* h, const double* start, const double* end, double sigma, const double* limits, uint64_t seed,
+                     uint32_t iter0, int n_iters);
 int ssppcu_sync(ssppcu_t* h);
 /* Diagnostics of the cooperative kernel: with enable != 0 every CTA stamps %globaltimer (ns) at the phase
  * boundaries of each launch's first iteration: [0] start, [1] scored, [2] past grid barrier 1, [3] ranked, [4] past
@@ -170,6 +195,17 @@ int ssppcu_sync(ssppcu_t* h);
  * receives [min(cap_ctas, grid)][12] values of the last launch.  Returns the grid
  * size or a negative error. */
 int ssppcu_phase_probe(ssppcu_t* h, int enable, unsigned long long* stamps, int cap_ctas);
+/* Diagnostics: the work the scoring path EXECUTED for the candidates of the last iteration (F_executed
+ * beside F_nominal).  A separate, untimed kernel re-scores the stored candidates with counters switched on inside
+ * the same arithmetic header and returns their totals: out[SSPPCU_WC_*], see the enum below; cap = entries of out.
+ * Returns the number of counters or a negative error.  (The reference has no counterpart: it cannot see inside
+ * mj_forward.) */
+enum { SSPPCU_WC_POINTS = 0, SSPPCU_WC_FK_HINGE_AXIS, SSPPCU_WC_FK_HINGE_GEN, SSPPCU_WC_FK_SLIDE, SSPPCU_WC_FK_FREE4, SSPPCU_WC_FK_R0,
+       SSPPCU_WC_FK_ANCHOR, SSPPCU_WC_GEOM_POS, SSPPCU_WC_GEOM_ROT_BOX, SSPPCU_WC_GEOM_ROT_AXIS, SSPPCU_WC_BROAD, SSPPCU_WC_NP_PLANE,
+       SSPPCU_WC_NP_SPHERE_BOX, SSPPCU_WC_NP_CAPS_BOX_EARLY, SSPPCU_WC_NP_CAPS_BOX, SSPPCU_WC_NP_CAPS_NEWTON, SSPPCU_WC_NP_BOX_BOX_FACE,
+       SSPPCU_WC_NP_BOX_BOX, SSPPCU_WC_NP_CYL_BOX_FACE, SSPPCU_WC_NP_CYL_BOX, SSPPCU_WC_NP_OTHER, SSPPCU_WC_CONTACTS, SSPPCU_WC_MM_TESTS,
+       SSPPCU_WC_MM_NARROW, SSPPCU_WC_SDF_SAMPLES, SSPPCU_WC_COUNT };
+int ssppcu_work_counters(ssppcu_t* h, uint64_t* out, int cap);
 
 /* Result mirror (on by default; the environment variable SSPPCU_RESULT_MIRROR=0 sets the default to off): the
  * cooperative kernel copies its result block into the handle's mapped pinned host block itself, behind the grid
@@ -178,6 +214,17 @@ int ssppcu_phase_probe(ssppcu_t* h, int enable, unsigned long long* stamps, int 
  * that keeps the results on the device turns it off and saves the PCIe writes (about 70 KB per launch at 4096
  * candidates). */
 int ssppcu_set_result_mirror(ssppcu_t* h, int on);
+/* Success rows (off by default): with on != 0 every iteration launch is followed by a compaction kernel that writes the
+ * sampled rows [n_free*dof] of the CONVERGED candidates, in candidate order, with their candidate indices, into a mapped
+ * pinned host block - what SamplingPathPlanner::plan hands back as ret_success_paths (sspp.h:215-216, 222) without
+ * copying the failed candidates' rows.  ssppcu_get_success_rows synchronises and returns views into that block for one
+ * query (valid until the next launch): rows [n][n_free*dof], idx [n]. */
+int ssppcu_set_success_rows(ssppcu_t* h, int on);
+int ssppcu_get_success_rows(ssppcu_t* h, int query, const float** rows, const int32_t** idx, int32_t* n);
+/* The K x dof point matrix (control points for JOINT, interpolation points for TASK) of candidate idx of the last
+ * iteration of `query`: the query's fixed rows with the candidate's sampled rows written in (SURVEY 8b B-c: makes
+ * returning list[Spline] lazy).  The sampled rows are kept in HBM, so this is a 100-byte read, not a regeneration. */
+int ssppcu_candidate_ctrl(ssppcu_t* h, int query, uint32_t idx, float* out);
 
 /* host copies of the last iteration; any pointer may be NULL.  Per-candidate arrays are
  * [n_queries][n_cand], per-query arrays [n_queries].  Synchronises the stream. */

@@ -22,6 +22,7 @@
 #include <iostream>
 #include <limits>
 #include <map>
+#include <memory>
 #include <stdexcept>
 #include <string>
 #include <tuple>
@@ -42,19 +43,33 @@ struct ControlPoints {
   void resize(int k) { cols = k; data.assign((size_t)k * kDOF, 0.0); }
 };
 
+// What the successful candidates of one plan() share: the initial spline (knots + control points, sspp.h:82-97) and the
+// block of their sampled control-point rows as it came back from the device.  A Spline that refers to a row of the block
+// builds its own knots / control points on first use, so handing a few thousand successes back to the caller
+// (sspp.h:222 copies every spline) costs one small object each instead of two heap vectors each.
+template <int kDOF>
+struct SplineBlock {
+  std::vector<double> knots;
+  ControlPoints<kDOF> init;          // the unperturbed control points
+  int first_free = 0, n_free = 0;    // columns [first_free, first_free + n_free) are the sampled ones (sspp.h:123)
+  std::vector<float> rows;           // [n][n_free][kDOF]
+};
+
 template <int kDOF, int kDegree = 3>
 class Spline {
  public:
   using Point = std::array<double, kDOF>;
   Spline() = default;
   Spline(std::vector<double> knots, ControlPoints<kDOF> ctrls) : knots_(std::move(knots)), ctrls_(std::move(ctrls)) {}
-  const std::vector<double>& knots() const { return knots_; }
-  const ControlPoints<kDOF>& ctrls() const { return ctrls_; }
-  ControlPoints<kDOF>& ctrls() { return ctrls_; }
+  Spline(std::shared_ptr<const SplineBlock<kDOF>> block, int row) : block_(std::move(block)), row_(row) {}
+  const std::vector<double>& knots() const { materialise(); return knots_; }
+  const ControlPoints<kDOF>& ctrls() const { materialise(); return ctrls_; }
+  ControlPoints<kDOF>& ctrls() { materialise(); return ctrls_; }
   int degree() const { return kDegree; }
 
   // Eigen::Spline::operator(): span by upper_bound on the knots (last span at u = 1), Cox-de Boor basis
   Point operator()(double u) const {
+    materialise();
     Point out{};
     const int n = ctrls_.cols, p = kDegree;
     if (n < p + 1 || (int)knots_.size() != n + p + 1) return out;
@@ -83,8 +98,20 @@ class Spline {
   }
 
  private:
-  std::vector<double> knots_;
-  ControlPoints<kDOF> ctrls_;
+  void materialise() const {
+    if (!block_) return;
+    const SplineBlock<kDOF>& b = *block_;
+    knots_ = b.knots;
+    ctrls_ = b.init;
+    const float* r = b.rows.data() + (size_t)row_ * b.n_free * kDOF;
+    for (int j = 0; j < b.n_free; ++j)
+      for (int d = 0; d < kDOF; ++d) ctrls_(d, b.first_free + j) = r[(size_t)j * kDOF + d];
+    block_.reset();
+  }
+  mutable std::vector<double> knots_;
+  mutable ControlPoints<kDOF> ctrls_;
+  mutable std::shared_ptr<const SplineBlock<kDOF>> block_;   // non-null: knots_ / ctrls_ not built yet
+  int row_ = -1;
 };
 
 // RAII wrappers of the C handles
@@ -107,7 +134,9 @@ struct PlanBuffers {
   int n_cand = 0, n_free = 0;
   std::vector<float> L, cost;        // per candidate: arc length, L + w*Cwf
   std::vector<uint8_t> status;       // SSPPCU_ST_*
-  std::vector<float> params;         // [n_cand][n_free][kDOF] sampled control points
+  std::vector<float> params;         // [n_cand][n_free][kDOF] sampled control points of EVERY candidate: filled on demand (all_params)
+  const float* succ_rows = nullptr;  // [n_success][n_free][kDOF] rows of the collision-free candidates, candidate order (pinned view,
+  const int32_t* succ_idx = nullptr; //  valid until the next plan) and their candidate indices
   int n_success = 0, best_idx = -1;
   float best_cost = std::numeric_limits<float>::infinity();
   SsppDeviceView view{};             // raw device pointers (valid until the next plan on this shape)
@@ -190,14 +219,22 @@ class SamplingPathPlanner {
   bool plan(const Point& start, const Point& end, double sigma, const Point& limits, std::vector<Spline>& ret_success_paths,
             int sample_count = 50, int check_points = 50, int init_points = 10) {
     PlanBuffers& B = plan_device(start, end, sigma, limits, sample_count, check_points, init_points);
+    // the successes share one block (initial spline + their rows); each returned Spline is a (block, row) reference
+    auto block = std::make_shared<SplineBlock<kDOF>>();
+    block->knots = init_spline_.knots(); block->init = init_spline_.ctrls();
+    block->first_free = kSplineDegree; block->n_free = B.n_free;
+    block->rows.assign(B.succ_rows, B.succ_rows + (size_t)B.n_success * B.n_free * kDOF);
     ret_success_paths.clear();
     ret_success_paths.reserve(B.n_success);
-    for (int i = 0; i < B.n_cand; ++i)
-      if (B.status[i] == SSPPCU_ST_CONVERGED) ret_success_paths.push_back(candidate_spline(B, i));
+    int best_row = -1;
+    for (int s = 0; s < B.n_success; ++s) {
+      ret_success_paths.emplace_back(block, s);
+      if (B.succ_idx[s] == B.best_idx) best_row = s;
+    }
     if (verbose_)
       std::cout << "Sampled " << sample_count << " splines. Successful paths found: " << ret_success_paths.size() << std::endl;
-    if (B.best_idx < 0) return false;
-    path_spline_ = candidate_spline(B, B.best_idx);
+    if (B.best_idx < 0 || best_row < 0) return false;
+    path_spline_ = Spline(block, best_row);
     return true;
   }
   bool plan(const Point& start, const Point& end, double sigma, const Point& limits, int sample_count = 50, int check_points = 50,
@@ -211,19 +248,22 @@ class SamplingPathPlanner {
   PlanBuffers& plan_device(const Point& start, const Point& end, double sigma, const Point& limits, int sample_count,
                            int check_points, int init_points) {
     ssppcu_t* h = handle_for(sample_count, check_points, init_points);
-    check(h, ssppcu_set_queries(h, start.data(), end.data()));
-    check(h, ssppcu_set_joint_noise(h, sigma, limits.data()));
-    check(h, ssppcu_iterate(h, seed_, iteration_++, 1));
+    // ONE call, ONE scoring launch: the query and its noise scale ride in the kernel's parameter block; the compaction
+    // kernel behind it posts the successful rows to pinned host memory; one stream synchronisation reads everything back
+    check(h, ssppcu_plan_step(h, start.data(), end.data(), sigma, limits.data(), seed_, iteration_++, 1));
     PlanBuffers& B = buffers_;
     SsppDims d;
     ssppcu_dims(h, &d);
     B.n_cand = d.n_cand; B.n_free = d.n_free;
     B.L.resize(d.n_cand); B.cost.resize(d.n_cand); B.status.resize(d.n_cand);
-    B.params.resize((size_t)d.n_cand * d.nfd);
+    B.params.clear();
     int32_t ns = 0, bi = -1; float bc = 0;
-    check(h, ssppcu_get_results(h, B.L.data(), nullptr, nullptr, B.cost.data(), B.status.data(), &ns, nullptr, &bi, &bc, nullptr));
-    check(h, ssppcu_get_params(h, B.params.data()));
+    check(h, ssppcu_get_success_rows(h, 0, &B.succ_rows, &B.succ_idx, &ns));
+    int32_t ns2 = 0;
+    check(h, ssppcu_get_results(h, B.L.data(), nullptr, nullptr, B.cost.data(), B.status.data(), &ns2, nullptr, &bi, &bc, nullptr));
+    if (ns2 != ns) throw std::runtime_error("sspp CUDA path: success rows and result block disagree");
     B.n_success = ns; B.best_idx = bi; B.best_cost = bc;
+    last_handle_ = h;
     ssppcu_device_view(h, &B.view);
     // the spline pieces shared by every candidate of this plan
     initializePath(start, end, init_spline_, init_points);
@@ -234,12 +274,26 @@ class SamplingPathPlanner {
   void set_verbose(bool v) { verbose_ = v; }
   int device() const { return device_; }
 
-  // Spline of candidate i of the last plan: init spline with the sampled control points written in
+  // sampled control points of EVERY candidate of the last plan [n_cand][n_free][kDOF] (failed ones included): one extra
+  // device-to-host copy, made on demand
+  const std::vector<float>& all_params() {
+    PlanBuffers& B = buffers_;
+    if (B.params.empty() && last_handle_) {
+      B.params.resize((size_t)B.n_cand * B.n_free * kDOF);
+      check(last_handle_, ssppcu_get_params(last_handle_, B.params.data()));
+    }
+    return B.params;
+  }
+
+  // Spline of candidate i of the last plan (any status): init spline with the candidate's control points written in,
+  // fetched from the device row by row (ssppcu_candidate_ctrl)
   Spline candidate_spline(const PlanBuffers& B, int i) const {
     Spline s = init_spline_;
-    const int p = kSplineDegree;
-    for (int r = 0; r < B.n_free; ++r)
-      for (int d = 0; d < kDOF; ++d) s.ctrls()(d, p + r) = B.params[((size_t)i * B.n_free + r) * kDOF + d];
+    std::vector<float> pts((size_t)s.ctrls().cols * kDOF);
+    check(last_handle_, ssppcu_candidate_ctrl(last_handle_, 0, (uint32_t)i, pts.data()));
+    for (int j = 0; j < s.ctrls().cols; ++j)
+      for (int d = 0; d < kDOF; ++d) s.ctrls()(d, j) = pts[(size_t)j * kDOF + d];
+    (void)B;
     return s;
   }
 
@@ -259,6 +313,7 @@ class SamplingPathPlanner {
     ssppcu_t* h = nullptr;
     const int rc = ssppcu_create(model_->get(), &cfg, &h, err, sizeof(err));
     if (rc != SSPPCU_OK) throw std::runtime_error(std::string("sspp CUDA path: ") + err);
+    check(h, ssppcu_set_success_rows(h, 1));
     handles_[key] = h;
     return h;
   }
@@ -268,6 +323,7 @@ class SamplingPathPlanner {
   Spline path_spline_, init_spline_;
   std::map<std::tuple<int, int, int>, ssppcu_t*> handles_;   // one device-resident scene per planner shape
   PlanBuffers buffers_;
+  ssppcu_t* last_handle_ = nullptr;
   uint64_t seed_ = 0x53535050ull;
   uint32_t iteration_ = 0;
   bool verbose_ = true;

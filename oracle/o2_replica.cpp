@@ -25,6 +25,8 @@ struct Replica {
   DevModel dev;
   ScoreConfig cfg;
   std::vector<float> nodes;   // SDF mode: the node grid, baked with the same function as the device kernel
+  bool count_work = false;    // o2_work: accumulate the work counters of sspp_math.h over the points scored
+  unsigned long long work[WC_COUNT] = {};
 };
 
 struct HostXF {
@@ -141,6 +143,15 @@ float o2_point_cost(void* h, const float* q) {
   return point_collision_cost(r->dev, qa, xf);
 }
 
+// work counters: enable / disable, read (and clear) the totals accumulated by o2_iterate since
+int o2_work(void* h, int enable, unsigned long long* out, int cap) {
+  Replica* r = static_cast<Replica*>(h);
+  for (int e = 0; out && e < WC_COUNT && e < cap; ++e) out[e] = r->work[e];
+  std::memset(r->work, 0, sizeof(r->work));
+  r->count_work = enable != 0;
+  return WC_COUNT;
+}
+
 void o2_philox(uint32_t ctr[4], uint32_t k0, uint32_t k1) { philox4x32_10(ctr, k0, k1); }
 float o2_normal(uint64_t seed, uint32_t iter, uint32_t query, uint32_t cand, uint32_t stream, uint32_t j) { return normal_at(seed, iter, query, cand, stream, j); }
 void o2_sincos(float x, float* s, float* c) { sincos_poly(x, s, c); }
@@ -189,7 +200,11 @@ int o2_iterate(void* h, const float* psi_col, const float* psi_arc, const float*
       float a = 0.0f, b = 0.0f;
       if (m >= c.col_first) {
         HostXF xf; HostQ qa{&qcol[m * D]};
-        a = point_collision_cost(r->dev, qa, xf);
+        if (r->count_work) {
+          uint32_t wc[WC_COUNT] = {};
+          a = point_collision_cost(r->dev, qa, xf, wc);
+          for (int e = 0; e < WC_COUNT; ++e) r->work[e] += wc[e];
+        } else a = point_collision_cost(r->dev, qa, xf);
         b = a + point_penalty(c, qa);
       }
       cc[m] = a; cw[m] = b;

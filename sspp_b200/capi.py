@@ -92,8 +92,14 @@ SYMBOLS = [
     "ssppcu_spline_setup", "ssppcu_collocation_matrix", "ssppcu_save_state", "ssppcu_restore_state",
     "ssppcu_fp32_peak", "ssppcu_get_merged", "ssppcu_get_sdf", "ssppcu_get_spheres", "ssppcu_phase_probe", "ssppcu_iterate_restored",
     "ssppcu_exchange_export", "ssppcu_exchange_attach_ipc", "ssppcu_exchange_attach_ptrs", "ssppcu_iterate_exchange",
-    "ssppcu_exchange_status", "ssppcu_sdf_gradient", "ssppcu_set_result_mirror",
+    "ssppcu_exchange_status", "ssppcu_sdf_gradient", "ssppcu_set_result_mirror", "ssppcu_work_counters",
+    "ssppcu_plan_step", "ssppcu_set_success_rows", "ssppcu_get_success_rows", "ssppcu_candidate_ctrl",
+    "ssppcu_bspline_knot_vector", "ssppcu_bspline_rows", "ssppcu_bspline_fit", "ssppcu_cubic_path", "ssppcu_bspline_eval_batch",
 ]
+WORK_COUNTERS = ("points", "fk_hinge_axis", "fk_hinge_gen", "fk_slide", "fk_free4", "fk_r0", "fk_anchor", "geom_pos", "geom_rot_box",
+                 "geom_rot_axis", "broad", "np_plane", "np_sphere_box", "np_caps_box_early", "np_caps_box", "np_caps_newton",
+                 "np_box_box_face", "np_box_box", "np_cyl_box_face", "np_cyl_box", "np_other", "contacts", "mm_tests", "mm_narrow",
+                 "sdf_samples")
 
 lib = _load()
 lib.ssppcu_last_error.restype = C.c_char_p
@@ -356,6 +362,35 @@ class Handle:
         fn = lib.ssppcu_iterate_restored if restored else lib.ssppcu_iterate
         self._ck(fn(self._h, C.c_uint64(seed), C.c_uint32(iter0), int(n_iters)))
 
+    def plan_step(self, start, end, sigma: float, limits=None, seed: int = 0, iter0: int = 0, n_iters: int = 1):
+        """set_queries + set_joint_noise / reset_distribution + iterate in one call and one launch (ssppcu_plan_step)"""
+        s = np.ascontiguousarray(start, np.float64); e = np.ascontiguousarray(end, np.float64)
+        lim = None if limits is None else np.ascontiguousarray(limits, np.float64)
+        lib.ssppcu_plan_step.argtypes = [C.c_void_p, _dp, _dp, C.c_double, _dp, C.c_uint64, C.c_uint32, C.c_int]
+        self._ck(lib.ssppcu_plan_step(self._h, _dptr(s), _dptr(e), float(sigma), None if lim is None else _dptr(lim), seed, iter0, n_iters))
+
+    def set_success_rows(self, on: bool):
+        lib.ssppcu_set_success_rows.argtypes = [C.c_void_p, C.c_int]
+        self._ck(lib.ssppcu_set_success_rows(self._h, int(on)))
+
+    def success_rows(self, query: int = 0):
+        """(rows [n][nfd], candidate indices [n]) of the converged candidates of the last launch, candidate order; views into
+        the handle's pinned block, valid until the next launch"""
+        rows, idx, n = C.POINTER(C.c_float)(), C.POINTER(C.c_int32)(), C.c_int32()
+        lib.ssppcu_get_success_rows.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        self._ck(lib.ssppcu_get_success_rows(self._h, query, C.byref(rows), C.byref(idx), C.byref(n)))
+        d = self.dims
+        if n.value == 0:
+            return np.zeros((0, d.nfd), np.float32), np.zeros(0, np.int32)
+        return np.ctypeslib.as_array(rows, shape=(n.value, d.nfd)), np.ctypeslib.as_array(idx, shape=(n.value,))
+
+    def candidate_ctrl(self, idx: int, query: int = 0) -> np.ndarray:
+        d = self.dims
+        out = np.zeros((d.n_points, d.dof), np.float32)
+        lib.ssppcu_candidate_ctrl.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p]
+        self._ck(lib.ssppcu_candidate_ctrl(self._h, query, idx, out.ctypes.data_as(C.c_void_p)))
+        return out
+
     def sync(self):
         self._ck(lib.ssppcu_sync(self._h))
 
@@ -372,6 +407,15 @@ class Handle:
         out = np.zeros((grid, 12), np.uint64)
         self._ck(min(0, lib.ssppcu_phase_probe(self._h, int(enable), out.ctypes.data_as(C.c_void_p), grid)))
         return out
+
+    def work_counters(self) -> dict:
+        """executed work of the last iteration's candidates (untimed diagnostic kernel): counter name -> total"""
+        out = np.zeros(len(WORK_COUNTERS), np.uint64)
+        lib.ssppcu_work_counters.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        n = lib.ssppcu_work_counters(self._h, out.ctypes.data_as(C.c_void_p), len(out))
+        if n < 0:
+            self._ck(n)
+        return {k: int(v) for k, v in zip(WORK_COUNTERS, out)}
 
     def sdf_gradient(self, pts, weights=None):
         """SDF mode refinement step: (grad [n_points][3], clearance [rows], dirs [rows][3]); see ssppcu_sdf_gradient"""

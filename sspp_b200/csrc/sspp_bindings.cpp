@@ -80,18 +80,25 @@ void bind_SamplingPathPlanner(py::module& m, const std::string& class_name, cons
            [](Planner& self, const py::object& start, const py::object& end, double sigma, const py::object& limits, int sample_count,
               int check_points, int init_points) {
              std::vector<Spline> result;
-             const bool success = self.plan(to_point<kDOF>(start, "start"), to_point<kDOF>(end, "end"), sigma,
-                                            to_point<kDOF>(limits, "limits"), result, sample_count, check_points, init_points);
-             return py::make_tuple(success, result);
+             const auto s = to_point<kDOF>(start, "start"), e = to_point<kDOF>(end, "end"), lim = to_point<kDOF>(limits, "limits");
+             bool success;
+             {   // the reference holds the GIL through its OpenMP loop (no call_guard, sspp_bindings.cpp:43); the launch + the
+                 // wait for the device need none of Python, so other threads run meanwhile
+               py::gil_scoped_release release;
+               success = self.plan(s, e, sigma, lim, result, sample_count, check_points, init_points);
+             }
+             return py::make_tuple(success, std::move(result));
            },
            py::arg("start"), py::arg("end"), py::arg("sigma"), py::arg("limits"), py::arg("sample_count") = 50,
            py::arg("check_points") = 50, py::arg("init_points") = 10)
       // ---- additive: device-buffer path ----
       .def("plan_device",
            [](Planner& self, const py::object& start, const py::object& end, double sigma, const py::object& limits, int sample_count,
-              int check_points, int init_points) {
-             sspp::PlanBuffers& B = self.plan_device(to_point<kDOF>(start, "start"), to_point<kDOF>(end, "end"), sigma,
-                                                     to_point<kDOF>(limits, "limits"), sample_count, check_points, init_points);
+              int check_points, int init_points, bool fetch_ctrl) {
+             const auto s = to_point<kDOF>(start, "start"), e = to_point<kDOF>(end, "end"), lim = to_point<kDOF>(limits, "limits");
+             sspp::PlanBuffers* Bp;
+             { py::gil_scoped_release release; Bp = &self.plan_device(s, e, sigma, lim, sample_count, check_points, init_points); }
+             sspp::PlanBuffers& B = *Bp;
              py::dict d;
              d["n_candidates"] = B.n_cand;
              d["n_success"] = B.n_success;
@@ -100,7 +107,11 @@ void bind_SamplingPathPlanner(py::module& m, const std::string& class_name, cons
              d["arc_length"] = py::array_t<float>((py::ssize_t)B.L.size(), B.L.data());
              d["cost"] = py::array_t<float>((py::ssize_t)B.cost.size(), B.cost.data());
              d["status"] = py::array_t<uint8_t>((py::ssize_t)B.status.size(), B.status.data());
-             d["ctrl"] = py::array_t<float>({(py::ssize_t)B.n_cand, (py::ssize_t)B.n_free, (py::ssize_t)kDOF}, B.params.data());
+             // sampled control points: the collision-free candidates' rows arrived with the results; every candidate's rows
+             // (failed ones too) cost one more device-to-host copy and come only when asked for
+             d["ctrl_success"] = py::array_t<float>({(py::ssize_t)B.n_success, (py::ssize_t)B.n_free, (py::ssize_t)kDOF}, B.succ_rows);
+             d["success_idx"] = py::array_t<int32_t>((py::ssize_t)B.n_success, B.succ_idx);
+             if (fetch_ctrl) d["ctrl"] = py::array_t<float>({(py::ssize_t)B.n_cand, (py::ssize_t)B.n_free, (py::ssize_t)kDOF}, self.all_params().data());
              py::dict dev;   // raw device addresses (float32 / uint8 / uint64), for __cuda_array_interface__ wrappers
              dev["arc_length"] = (uintptr_t)B.view.L; dev["cost"] = (uintptr_t)B.view.cost; dev["status"] = (uintptr_t)B.view.status;
              dev["ctrl"] = (uintptr_t)B.view.params; dev["sorted_keys"] = (uintptr_t)B.view.keys; dev["stream"] = (uintptr_t)B.view.stream;
@@ -109,7 +120,7 @@ void bind_SamplingPathPlanner(py::module& m, const std::string& class_name, cons
              return d;
            },
            py::arg("start"), py::arg("end"), py::arg("sigma"), py::arg("limits"), py::arg("sample_count") = 50,
-           py::arg("check_points") = 50, py::arg("init_points") = 10)
+           py::arg("check_points") = 50, py::arg("init_points") = 10, py::arg("fetch_ctrl") = false)
       .def("set_seed", &Planner::set_seed, py::arg("seed"))
       .def("set_verbose", &Planner::set_verbose, py::arg("verbose"));
 }

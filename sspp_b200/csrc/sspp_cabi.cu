@@ -58,6 +58,10 @@ struct ssppcu_planner {
   // so a read-back right after such a launch is a stream synchronisation and no copy.  SSPPCU_RESULT_MIRROR=0 turns it off.
   unsigned char* h_res_dev = nullptr; bool mirror_on = true;
   bool res_fresh = false;    // the last call was a launch that mirrors its results (cleared by any other call)
+  // success rows (ssppcu_set_success_rows): mapped pinned block rows [Q][N][nfd] | idx [Q][N] | count [Q], filled by a
+  // compaction kernel enqueued behind every iteration launch
+  bool rows_on = false, rows_fresh = false;
+  unsigned char* h_rows = nullptr; unsigned char* h_rows_dev = nullptr; size_t o_ridx = 0, o_rcount = 0;
   // fused key exchange of a population shard (ssppcu_exchange_*): this rank's block, the peers' mappings
   struct Exchange {
     int world = 0, rank = 0;
@@ -121,6 +125,72 @@ int ssppcu_collocation_matrix(int n_points, int degree, const double* grid, int 
     std::copy(P.begin(), P.end(), psi);
     return SSPPCU_OK;
   } catch (const std::exception&) { return SSPPCU_EINVAL; }
+}
+
+// ---- sspp/BSplines.py + sspp/CubicPath.py as product functions ----
+int ssppcu_bspline_knot_vector(int n_ctrl, int k, double* knots) {
+  if (!knots) return SSPPCU_EINVAL;
+  try { const std::vector<double> t = uniform_knots(n_ctrl, k); std::copy(t.begin(), t.end(), knots); return SSPPCU_OK; }
+  catch (const std::exception&) { return SSPPCU_EINVAL; }
+}
+int ssppcu_bspline_rows(int n_ctrl, int k, const double* knots, const double* theta, int n_theta, int kind, double* out) {
+  if (!knots || !theta || !out || n_theta < 0 || k < 0 || n_ctrl < 1 || kind < 0 || kind > 3) return SSPPCU_EINVAL;
+  try {
+    const std::vector<double> t(knots, knots + n_ctrl + k + 1);
+    for (int m = 0; m < n_theta; ++m) {
+      const std::vector<double> r = (kind < 2) ? half_open_basis_row(theta[m], k, t, kind == 1) : curve_row(theta[m], k, t, kind == 3);
+      std::copy(r.begin(), r.end(), out + (size_t)m * n_ctrl);
+    }
+    return SSPPCU_OK;
+  } catch (const std::exception&) { return SSPPCU_EINVAL; }
+}
+int ssppcu_bspline_fit(const double* via, int n, int d, int k, double* ctrl, double* knots) {
+  if (!via || !ctrl || n < 2 || d < 1) return SSPPCU_EINVAL;
+  try {
+    std::vector<double> t;
+    const std::vector<double> c = fit_uniform(std::vector<double>(via, via + (size_t)n * d), n, d, k, &t);
+    std::copy(c.begin(), c.end(), ctrl);
+    if (knots) std::copy(t.begin(), t.end(), knots);
+    return SSPPCU_OK;
+  } catch (const std::exception&) { return SSPPCU_EINVAL; }
+}
+int ssppcu_cubic_path(const double* start, const double* via, const double* end, int d, const double* u, int n_u, double* pos, double* vel,
+                      double* acc) {
+  if (!start || !via || !end || !u || d < 1 || n_u < 0) return SSPPCU_EINVAL;
+  for (int e = 0; e < d; ++e) {
+    const double a = 2.0 * (end[e] + 3.0 * start[e] - 4.0 * via[e]);       // CubicPath.py:23-26
+    const double b = 4.0 * (via[e] - start[e] - a / 8.0);
+    const double c = 0.0, dd = start[e];
+    for (int m = 0; m < n_u; ++m) {
+      const double x = std::min(std::max(u[m], 0.0), 1.0);                 // np.clip(u, 0, 1), CubicPath.py:39
+      const double x3 = std::pow(x, 3.0), x2 = std::pow(x, 2.0);           // numpy's u**3, u**2; same operation order as :41, :56-58
+      if (pos) pos[(size_t)m * d + e] = ((a * x3 + b * x2) + c * x) + dd;
+      if (vel) vel[(size_t)m * d + e] = ((3.0 * a) * x2 + (2.0 * b) * x) + c;
+      if (acc) acc[(size_t)m * d + e] = (6.0 * a) * x + 2.0 * b;
+    }
+  }
+  return SSPPCU_OK;
+}
+int ssppcu_bspline_eval_batch(int device, const float* rows, int n_theta, int n_ctrl, const float* ctrl, int n_curves, int d, float* out,
+                              char* err, size_t errlen) {
+  if (!rows || !ctrl || !out || n_theta < 1 || n_ctrl < 1 || n_curves < 1 || d < 1) { set_err(err, errlen, "bad arguments"); return SSPPCU_EINVAL; }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) { set_err(err, errlen, "no CUDA device (this library has no CPU path)"); return SSPPCU_ECUDA; }
+  if (device < 0 || device >= ndev) { set_err(err, errlen, "device ordinal out of range"); return SSPPCU_EINVAL; }
+  cudaDeviceProp prop;
+  float *d_rows = nullptr, *d_ctrl = nullptr, *d_out = nullptr;
+  const size_t nr = (size_t)n_theta * n_ctrl, nc = (size_t)n_curves * n_ctrl * d, no = (size_t)n_curves * n_theta * d;
+  e = cudaSetDevice(device);
+  if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
+  if (e == cudaSuccess) e = cudaMalloc(&d_rows, (nr + nc + no) * sizeof(float));
+  if (e == cudaSuccess) { d_ctrl = d_rows + nr; d_out = d_ctrl + nc; e = cudaMemcpy(d_rows, rows, nr * sizeof(float), cudaMemcpyHostToDevice); }
+  if (e == cudaSuccess) e = cudaMemcpy(d_ctrl, ctrl, nc * sizeof(float), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = launch_bspline_eval(d_rows, n_theta, n_ctrl, d_ctrl, n_curves, d, d_out, prop.multiProcessorCount, 0);
+  if (e == cudaSuccess) e = cudaMemcpy(out, d_out, no * sizeof(float), cudaMemcpyDeviceToHost);
+  if (d_rows) cudaFree(d_rows);
+  if (e != cudaSuccess) { set_err(err, errlen, std::string("ssppcu_bspline_eval_batch: ") + cudaGetErrorString(e)); return SSPPCU_ECUDA; }
+  return SSPPCU_OK;
 }
 
 int ssppcu_model_load(const char* path, ssppcu_model_t** out, char* err, size_t errlen) {
@@ -219,6 +289,7 @@ void ssppcu_destroy(ssppcu_t* h) {
   if (h->d_res) cudaFree(h->d_res);
   if (h->h_res) cudaFreeHost(h->h_res);
   if (h->h_stage) cudaFreeHost(h->h_stage);
+  if (h->h_rows) cudaFreeHost(h->h_rows);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
 }
@@ -475,7 +546,7 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
     if (dalloc(h, &d_nodes, n_nodes) || dalloc(h, &d_cells, n_cells * 8)) { set_err(err, errlen, h->err); ssppcu_destroy(h); return SSPPCU_ECUDA; }
     g.nodes = d_nodes; g.cells = d_cells;
     h->view.grid = g;
-    ce = launch_sdf_bake(h->view, d_nodes, d_cells, h->stream);
+    ce = launch_sdf_bake(h->view, d_nodes, d_cells, h->n_sm, h->stream);
     if (ce == cudaSuccess) ce = cudaStreamSynchronize(h->stream);
     if (ce != cudaSuccess) { set_err(err, errlen, std::string("SDF bake: ") + cudaGetErrorString(ce)); ssppcu_destroy(h); return SSPPCU_ECUDA; }
   }
@@ -493,7 +564,7 @@ namespace {
 
 int check(ssppcu_t* h) {
   if (!h) return SSPPCU_EINVAL;
-  h->best_fresh = false; h->res_fresh = false;
+  h->best_fresh = false; h->res_fresh = false; h->rows_fresh = false;
   cudaError_t e = cudaSetDevice(h->cfg.device);
   if (e != cudaSuccess) return cuda_fail(h, e, "cudaSetDevice");
   return 0;
@@ -555,9 +626,29 @@ int ssppcu_set_stream(ssppcu_t* h, void* s) {
   return SSPPCU_OK;
 }
 
+}  // extern "C"
+
+namespace {
+// host FP64 set-up of a query (sspp.h:82-97 initializePath / tsp_path_model.h:11-19 setupLinear): fills h->base_host
+void fill_base(ssppcu_t* h, const double* start, const double* end);
+// initial sampling state of the planners: mean | sigma [Q][nfd] each
+void fill_state_task(const ssppcu_t* h, double sigma0, float* mean, float* sigma);                       // Planner::reset, tsp_planner.h:54-69
+void fill_state_joint(const ssppcu_t* h, double sg, const double* limits, float* mean, float* sigma);   // sspp.h:114-130 noise scale
+}  // namespace
+
+extern "C" {
+
 int ssppcu_set_queries(ssppcu_t* h, const double* start, const double* end) {
   if (int rc = check(h)) return rc;
   if (!start || !end) return fail(h, SSPPCU_EINVAL, "null start/end");
+  fill_base(h, start, end);
+  return h2d(h, const_cast<float*>(h->P.base), h->base_host.data(), h->base_host.size());
+}
+
+}  // extern "C"
+
+namespace {
+void fill_base(ssppcu_t* h, const double* start, const double* end) {
   const ScoreConfig& s = h->P.cfg;
   const int Q = h->P.n_query, K = s.K, D = s.D;
   std::vector<double> V((size_t)K * D);
@@ -578,15 +669,10 @@ int ssppcu_set_queries(ssppcu_t* h, const double* start, const double* end) {
         }
     }
   }
-  return h2d(h, const_cast<float*>(h->P.base), h->base_host.data(), h->base_host.size());
 }
-
-int ssppcu_reset_distribution(ssppcu_t* h, double sigma0) {
-  if (int rc = check(h)) return rc;
+void fill_state_task(const ssppcu_t* h, double sigma0, float* mean, float* sigma) {
   const ScoreConfig& s = h->P.cfg;
   const int Q = h->P.n_query, D = s.D, nfd = s.n_free * D;
-  std::vector<float> ms((size_t)2 * Q * nfd);               // mean | sigma are neighbours in the live state block: one copy
-  float* mean = ms.data(); float* sigma = mean + (size_t)Q * nfd;
   for (int q = 0; q < Q; ++q)
     for (int r = 0; r < s.n_free; ++r)
       for (int d = 0; d < D; ++d) {
@@ -597,6 +683,27 @@ int ssppcu_reset_distribution(ssppcu_t* h, double sigma0) {
         double sg = std::max(std::min(std::max(sigma0, h->cfg.stddev_min), h->cfg.stddev_max), h->cfg.sigma_floor);
         sigma[(size_t)q * nfd + r * D + d] = (float)sg;
       }
+}
+void fill_state_joint(const ssppcu_t* h, double sg, const double* limits, float* mean, float* sigma) {
+  const ScoreConfig& s = h->P.cfg;
+  const int Q = h->P.n_query, D = s.D, nfd = s.n_free * D;
+  for (int q = 0; q < Q; ++q)
+    for (int r = 0; r < s.n_free; ++r)
+      for (int d = 0; d < D; ++d) {
+        mean[(size_t)q * nfd + r * D + d] = h->base_host[((size_t)q * s.K + s.free_begin + r) * D + d];
+        sigma[(size_t)q * nfd + r * D + d] = (float)(sg * limits[d]);
+      }
+}
+}  // namespace
+
+extern "C" {
+
+int ssppcu_reset_distribution(ssppcu_t* h, double sigma0) {
+  if (int rc = check(h)) return rc;
+  const size_t n = (size_t)h->P.n_query * h->P.cfg.n_free * h->P.cfg.D;
+  const int Q = h->P.n_query;
+  std::vector<float> ms(2 * n);                             // mean | sigma are neighbours in the live state block: one copy
+  fill_state_task(h, sigma0, ms.data(), ms.data() + n);
   if (int rc = h2d(h, h->P.mean, ms.data(), ms.size())) return rc;
   CU(h, cudaMemsetAsync(h->P.best_valid, 0, 2 * Q * sizeof(int), h->stream));   // best_valid | any_success
   return SSPPCU_OK;
@@ -629,17 +736,12 @@ int ssppcu_get_distribution(ssppcu_t* h, double* mean, double* sigma) {
 int ssppcu_set_joint_noise(ssppcu_t* h, double sg, const double* limits) {
   if (int rc = check(h)) return rc;
   if (!limits) return fail(h, SSPPCU_EINVAL, "null limits");
-  const ScoreConfig& s = h->P.cfg;
-  const int Q = h->P.n_query, D = s.D, nfd = s.n_free * D;
-  std::vector<double> mean((size_t)Q * nfd), sigma((size_t)Q * nfd);
-  for (int q = 0; q < Q; ++q)
-    for (int r = 0; r < s.n_free; ++r)
-      for (int d = 0; d < D; ++d) {
-        mean[(size_t)q * nfd + r * D + d] = h->base_host[((size_t)q * s.K + s.free_begin + r) * D + d];
-        sigma[(size_t)q * nfd + r * D + d] = sg * limits[d];
-      }
+  const size_t n = (size_t)h->P.n_query * h->P.cfg.n_free * h->P.cfg.D;
+  const int Q = h->P.n_query;
+  std::vector<float> ms(2 * n);
+  fill_state_joint(h, sg, limits, ms.data(), ms.data() + n);
   CU(h, cudaMemsetAsync(h->P.best_valid, 0, 2 * Q * sizeof(int), h->stream));   // best_valid | any_success
-  return ssppcu_set_distribution(h, mean.data(), sigma.data());
+  return h2d(h, h->P.mean, ms.data(), ms.size());
 }
 
 int ssppcu_save_state(ssppcu_t* h) {
@@ -682,13 +784,22 @@ int ssppcu_fp32_peak(int device, double* tflops, double* sm_clock_mhz) {
   return SSPPCU_OK;
 }
 
-static int iterate_impl(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters, bool restored) {
+// inline_state: NULL, or mean | sigma [Q][nfd] each of a cold start - carried with h->base_host in the parameter block
+static int iterate_impl(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters, bool restored, const float* inline_state = nullptr) {
   if (int rc = check(h)) return rc;
   if (n_iters < 1) return fail(h, SSPPCU_EINVAL, "n_iters must be positive");
   if (restored && !h->state_saved) return fail(h, SSPPCU_EINVAL, "no saved state");
   IterParams P = h->P;
   P.seed = seed; P.iter0 = iter0; P.n_inner = n_iters;
   P.state_in = restored ? h->d_state : nullptr;
+  if (inline_state) {
+    const size_t nb = h->base_host.size(), n = (size_t)P.n_query * P.cfg.n_free * P.cfg.D;
+    std::memcpy(P.inline_blk, h->base_host.data(), nb * sizeof(float));
+    float* st = P.inline_blk + nb;                           // mean | sigma | best (zeros) | best_valid | any_success (zeros)
+    std::memcpy(st, inline_state, 2 * n * sizeof(float));
+    std::memset(st + 2 * n, 0, (n + 2 * (size_t)P.n_query) * sizeof(float));
+    P.inline_words = (int)(nb + 3 * n + 2 * (size_t)P.n_query);
+  }
   const bool mirror = h->mirror_on && P.coop && !P.sort_only && h->h_res_dev;
   if (mirror) {
     P.host_out = h->h_res_dev; P.res_dev = h->d_res;
@@ -697,7 +808,29 @@ static int iterate_impl(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters,
   }
   CU(h, launch_iterate(h->view, P, h->variant, h->threads, h->smem + h->smem_model, h->grid, h->stream));
   h->res_fresh = mirror;
+  if (h->rows_on) {
+    CU(h, launch_success_rows(h->P, reinterpret_cast<float*>(h->h_rows_dev), reinterpret_cast<int32_t*>(h->h_rows_dev + h->o_ridx),
+                              reinterpret_cast<int32_t*>(h->h_rows_dev + h->o_rcount), h->stream));
+    h->rows_fresh = true;
+  }
   return SSPPCU_OK;
+}
+
+static_assert((int)SSPPCU_WC_COUNT == (int)ssppm::WC_COUNT, "include/sspp_cuda.h mirrors ssppm::WorkCounter");
+int ssppcu_work_counters(ssppcu_t* h, uint64_t* out, int cap) {
+  if (int rc = check(h)) return rc;
+  if (!out || cap < 0) return fail(h, SSPPCU_EINVAL, "bad arguments");
+  unsigned long long* d_tot = nullptr;
+  CU(h, cudaMalloc(&d_tot, ssppm::WC_COUNT * sizeof(unsigned long long)));
+  cudaError_t e = cudaMemsetAsync(d_tot, 0, ssppm::WC_COUNT * sizeof(unsigned long long), h->stream);
+  if (e == cudaSuccess) e = launch_count(h->view, h->P, d_tot, h->n_sm, h->stream);
+  unsigned long long tot[ssppm::WC_COUNT];
+  if (e == cudaSuccess) e = cudaMemcpyAsync(tot, d_tot, sizeof(tot), cudaMemcpyDeviceToHost, h->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+  cudaFree(d_tot);
+  if (e != cudaSuccess) return cuda_fail(h, e, "ssppcu_work_counters");
+  for (int i = 0; i < cap && i < ssppm::WC_COUNT; ++i) out[i] = tot[i];
+  return ssppm::WC_COUNT;
 }
 
 int ssppcu_phase_probe(ssppcu_t* h, int enable, unsigned long long* stamps, int cap_ctas) {
@@ -717,6 +850,66 @@ int ssppcu_phase_probe(ssppcu_t* h, int enable, unsigned long long* stamps, int 
 
 int ssppcu_iterate(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters) { return iterate_impl(h, seed, iter0, n_iters, false); }
 int ssppcu_iterate_restored(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters) { return iterate_impl(h, seed, iter0, n_iters, true); }
+
+int ssppcu_plan_step(ssppcu_t* h, const double* start, const double* end, double sigma, const double* limits, uint64_t seed,
+                     uint32_t iter0, int n_iters) {
+  if (!h) return SSPPCU_EINVAL;
+  if (!start || !end) return fail(h, SSPPCU_EINVAL, "null start/end");
+  const bool joint = h->P.cfg.mode == ssppm::MODE_JOINT;
+  if (joint && !limits) return fail(h, SSPPCU_EINVAL, "null limits");
+  const size_t n = (size_t)h->P.n_query * h->P.cfg.n_free * h->P.cfg.D;
+  const size_t words = (size_t)h->P.n_query * h->P.cfg.K * h->P.cfg.D + 3 * n + 2 * (size_t)h->P.n_query;
+  if (words > (size_t)kInlineWords) {                        // too many queries for the parameter block: the three-call path
+    if (int rc = ssppcu_set_queries(h, start, end)) return rc;
+    if (int rc = joint ? ssppcu_set_joint_noise(h, sigma, limits) : ssppcu_reset_distribution(h, sigma)) return rc;
+    return iterate_impl(h, seed, iter0, n_iters, false);
+  }
+  fill_base(h, start, end);
+  float st[kInlineWords];
+  if (joint) fill_state_joint(h, sigma, limits, st, st + n); else fill_state_task(h, sigma, st, st + n);
+  return iterate_impl(h, seed, iter0, n_iters, false, st);
+}
+
+int ssppcu_set_success_rows(ssppcu_t* h, int on) {
+  if (int rc = check(h)) return rc;
+  if (on && !h->h_rows) {
+    const size_t Q = h->P.n_query, N = h->P.cfg.n_cand, nfd = (size_t)h->P.cfg.n_free * h->P.cfg.D;
+    h->o_ridx = (Q * N * nfd * 4 + 15) & ~(size_t)15;
+    h->o_rcount = h->o_ridx + ((Q * N * 4 + 15) & ~(size_t)15);
+    CU(h, cudaHostAlloc(&h->h_rows, h->o_rcount + Q * 4, cudaHostAllocMapped));
+    CU(h, cudaHostGetDevicePointer(reinterpret_cast<void**>(&h->h_rows_dev), h->h_rows, 0));
+    std::memset(h->h_rows + h->o_rcount, 0, Q * 4);
+  }
+  h->rows_on = on != 0;
+  return SSPPCU_OK;
+}
+
+int ssppcu_get_success_rows(ssppcu_t* h, int query, const float** rows, const int32_t** idx, int32_t* n) {
+  const bool fresh = h && h->rows_fresh;
+  if (int rc = check(h)) return rc;
+  if (!h->rows_on || !h->h_rows) return fail(h, SSPPCU_EINVAL, "success rows are off (ssppcu_set_success_rows)");
+  if (query < 0 || query >= h->P.n_query) return fail(h, SSPPCU_EINVAL, "query out of range");
+  if (!fresh) return fail(h, SSPPCU_EINVAL, "no iteration since the last read-back: the rows belong to an older launch");
+  CU(h, cudaStreamSynchronize(h->stream));
+  h->rows_fresh = true;                                        // reading another query of the same launch is fine
+  const size_t N = h->P.cfg.n_cand, nfd = (size_t)h->P.cfg.n_free * h->P.cfg.D;
+  if (rows) *rows = reinterpret_cast<const float*>(h->h_rows) + (size_t)query * N * nfd;
+  if (idx) *idx = reinterpret_cast<const int32_t*>(h->h_rows + h->o_ridx) + (size_t)query * N;
+  if (n) *n = reinterpret_cast<const int32_t*>(h->h_rows + h->o_rcount)[query];
+  return SSPPCU_OK;
+}
+
+int ssppcu_candidate_ctrl(ssppcu_t* h, int query, uint32_t idx, float* out) {
+  if (int rc = check(h)) return rc;
+  const ScoreConfig& s = h->P.cfg;
+  if (!out || query < 0 || query >= h->P.n_query || idx >= (uint32_t)s.n_cand) return fail(h, SSPPCU_EINVAL, "bad arguments");
+  const int D = s.D, nfd = s.n_free * D;
+  std::memcpy(out, &h->base_host[(size_t)query * s.K * D], (size_t)s.K * D * sizeof(float));
+  CU(h, cudaMemcpyAsync(out + (size_t)s.free_begin * D, h->P.params + ((size_t)query * s.n_cand + idx) * nfd, (size_t)nfd * sizeof(float),
+                        cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));
+  return SSPPCU_OK;
+}
 
 int ssppcu_set_result_mirror(ssppcu_t* h, int on) {
   if (int rc = check(h)) return rc;

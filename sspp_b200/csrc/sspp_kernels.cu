@@ -195,6 +195,12 @@ __device__ __forceinline__ bool spline_point_any(int W, int NV, unsigned a_rows,
   return false;
 }
 
+// the snapshot a restoring launch starts from: device memory (ssppcu_iterate_restored) or the parameter block (ssppcu_plan_step)
+__device__ __forceinline__ const float* snapshot_of(const IterParams& P) {
+  return P.inline_words ? P.inline_blk + (size_t)P.n_query * P.cfg.K * P.cfg.D : P.state_in;
+}
+__device__ __forceinline__ bool has_snapshot(const IterParams& P) { return P.state_in != nullptr || P.inline_words != 0; }
+
 // Phase A for one tile: candidates [c0, c0 + nc) of `query`.  Ends with the per-candidate outputs
 // and raw keys in global memory; no trailing barrier.
 __device__ __forceinline__ void score_tile(const SmemModel& M, const IterParams& P, const Smem& s, int query, int c0, int nc,
@@ -208,12 +214,12 @@ __device__ __forceinline__ void score_tile(const SmemModel& M, const IterParams&
   const bool fast_col = NV <= 2 && (P.w_col == 3 || P.w_col == 4);   // shapes spline_point_any covers
   const bool fast_arc = NV <= 2 && (P.w_arc == 3 || P.w_arc == 4);
   // sampling state: the live block, or (first iteration of a restoring launch) the snapshot it is being re-armed from
-  const float* st_base = from_saved ? P.state_in : P.mean;
+  const float* st_base = from_saved ? snapshot_of(P) : P.mean;
   const size_t st_q = (size_t)P.n_query * nfd;
   const float* mean = st_base + (size_t)query * nfd;
   const float* sigma = st_base + st_q + (size_t)query * nfd;
   const float* best = st_base + 2 * st_q + (size_t)query * nfd;
-  const float* base = P.base + (size_t)query * K * D;
+  const float* base = ((from_saved && P.inline_words) ? P.inline_blk : P.base) + (size_t)query * K * D;
   const size_t qn = (size_t)query * c.n_cand;
   SmemXF xf{s.xf, T, tid};
   SmemQ qa{s.qs, T, tid};
@@ -786,16 +792,19 @@ sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant_
     const int query = blockIdx.x;
     load_basis(s, c, P, tid, T);
     for (int it = 0; it < P.n_inner; ++it) {
-      const bool from_saved = P.state_in != nullptr && it == 0;
+      const bool from_saved = has_snapshot(P) && it == 0;
       score_tile(M, P, s, query, 0, c.n_cand, P.iter0 + (uint32_t)it, from_saved);
       if (from_saved) {               // re-arm this query's live state from the snapshot (nobody else touches it)
+        const float* snap = snapshot_of(P);
         const size_t sq = (size_t)P.n_query * nfd;
         for (int t = tid; t < nfd; t += T)
-          for (int b = 0; b < 3; ++b) P.mean[b * sq + (size_t)query * nfd + t] = P.state_in[b * sq + (size_t)query * nfd + t];
+          for (int b = 0; b < 3; ++b) P.mean[b * sq + (size_t)query * nfd + t] = snap[b * sq + (size_t)query * nfd + t];
         if (tid == 0) {
-          const int* si = reinterpret_cast<const int*>(P.state_in + 3 * sq);
+          const int* si = reinterpret_cast<const int*>(snap + 3 * sq);
           P.best_valid[query] = si[query]; P.any_success[query] = si[P.n_query + query];
         }
+        if (P.inline_words)
+          for (int e = tid; e < c.K * c.D; e += T) const_cast<float*>(P.base)[(size_t)query * c.K * c.D + e] = P.inline_blk[(size_t)query * c.K * c.D + e];
       }
       __syncthreads();                                   // raw keys were written by this CTA: visible after the barrier
       unsigned long long* keys = s.keys;
@@ -828,10 +837,15 @@ sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant_
   };
   for (int it = 0; it < P.n_inner; ++it) {
     stamp(it, 0);
-    const bool from_saved = P.state_in != nullptr && it == 0;
+    const bool from_saved = has_snapshot(P) && it == 0;
     if (from_saved) {                 // re-arm the live state from the snapshot; phase A reads the snapshot itself
+      const float* snap = snapshot_of(P);
       const size_t words = (size_t)P.n_query * (3 * nfd + 2);
-      for (size_t e = (size_t)blockIdx.x * T + tid; e < words; e += (size_t)gridDim.x * T) P.mean[e] = P.state_in[e];
+      for (size_t e = (size_t)blockIdx.x * T + tid; e < words; e += (size_t)gridDim.x * T) P.mean[e] = snap[e];
+      if (P.inline_words) {           // the point matrices too: later iterations of this launch and the read-back calls use them
+        const size_t bw = (size_t)P.n_query * c.K * c.D;
+        for (size_t e = (size_t)blockIdx.x * T + tid; e < bw; e += (size_t)gridDim.x * T) const_cast<float*>(P.base)[e] = P.inline_blk[e];
+      }
     }
     load_basis(s, c, P, tid, T);                         // phase B reuses this shared memory
     // ---- phase A: score the tiles ----
@@ -1029,6 +1043,116 @@ sspp_eval_points_kernel(const __grid_constant__ ModelView M, int D, const float*
   out[i] = point_collision_cost(M, qa, xf);
 }
 
+// Success rows for the host (sspp.h:215-216 hands every collision-free spline back to the caller): compacts the sampled rows
+// of the converged candidates of every query, in candidate order, into `rows` [Q][N][nfd] / `idx` [Q][N] / `count` [Q] -
+// pointers into the handle's mapped pinned block, so the rows cross PCIe as posted stores straight from this kernel and
+// only the successful ones do.  One CTA per 256 candidates: its base slot is the number of successes in front of its first
+// candidate (a count over at most N status bytes), the slots inside by ballot prefix.
+__global__ void __launch_bounds__(256)
+sspp_success_rows_kernel(const uint8_t* __restrict__ status, const float* __restrict__ params, int n_cand, int nfd,
+                         float* __restrict__ rows, int32_t* __restrict__ idx, int32_t* __restrict__ count) {
+  __shared__ int s_base, s_warp[8];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int query = blockIdx.y, c0 = blockIdx.x * 256;
+  const uint8_t* st = status + (size_t)query * n_cand;
+  if (tid == 0) s_base = 0;
+  __syncthreads();
+  int before = 0;
+  for (int i = tid; i < c0; i += 256) before += st[i] == ST_CONVERGED;
+  before = __reduce_add_sync(0xFFFFFFFFu, before);
+  if (lane == 0 && before) atomicAdd(&s_base, before);
+  const int cand = c0 + tid;
+  const bool ok = cand < n_cand && st[cand] == ST_CONVERGED;
+  const unsigned b = __ballot_sync(0xFFFFFFFFu, ok);
+  if (lane == 0) s_warp[warp] = __popc(b);
+  __syncthreads();
+  int slot = s_base + __popc(b & ((1u << lane) - 1u));
+  for (int w = 0; w < warp; ++w) slot += s_warp[w];
+  if (ok) idx[(size_t)query * n_cand + slot] = cand;
+  if (blockIdx.x == gridDim.x - 1 && tid == 255) {                    // the last CTA knows the total
+    int tot = s_base;
+    for (int w = 0; w < 8; ++w) tot += s_warp[w];
+    count[query] = tot;
+  }
+  // rows: a warp copies the rows of its successes one after another, lanes across the row (coalesced posted stores)
+  unsigned todo = b;
+  while (todo) {
+    const int l = __ffs((int)todo) - 1;
+    todo &= todo - 1u;
+    const int src_cand = c0 + warp * 32 + l;
+    const int dst_slot = __shfl_sync(0xFFFFFFFFu, slot, l);
+    const float* src = params + ((size_t)query * n_cand + src_cand) * nfd;
+    float* dst = rows + ((size_t)query * n_cand + dst_slot) * nfd;
+    for (int t = lane; t < nfd; t += 32) dst[t] = __ldcg(src + t);
+  }
+}
+
+// Batched B-spline evaluation (sspp/BSplines.py:44-51 over many curves at once): out[b][t][:] = sum_i rows[t][i] ctrl[b][i][:],
+// i ascending from +0 with explicit fmaf (the numpy twin restates the same sum).  rows = curve_row() of every parameter
+// (banded: at most order + 1 non-zeros, zeros skipped by value); one thread per (curve, parameter), rows staged in shared memory.
+__global__ void __launch_bounds__(256)
+sspp_bspline_eval_kernel(const float* __restrict__ rows, int T_, int n, const float* __restrict__ ctrl, int B_, int d, float* __restrict__ out) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float* s_rows = reinterpret_cast<float*>(smem_raw);
+  for (int e = threadIdx.x; e < T_ * n; e += blockDim.x) s_rows[e] = rows[e];
+  __syncthreads();
+  const long long total = (long long)B_ * T_;
+  for (long long item = (long long)blockIdx.x * blockDim.x + threadIdx.x; item < total; item += (long long)gridDim.x * blockDim.x) {
+    const int b = (int)(item / T_), t = (int)(item - (long long)b * T_);
+    const float* c = ctrl + (size_t)b * n * d;
+    const float* r = s_rows + (size_t)t * n;
+    for (int e = 0; e < d; ++e) {
+      float acc = 0.0f;
+      for (int i = 0; i < n; ++i) { const float w = r[i]; if (w != 0.0f) acc = fmaf(w, c[(size_t)i * d + e], acc); }
+      out[((size_t)b * T_ + t) * d + e] = acc;
+    }
+  }
+}
+
+// Diagnostics: the EXECUTED work of the last scored iteration (roofline: flop_per_point_executed).  Re-scores the stored
+// candidates of query 0 .. n_query-1 (sampled rows P.params, point matrix P.base) on the collision grid with the work
+// counters of sspp_math.h switched on; one thread per (candidate, collision row), totals by warp reduction + atomics.
+// Never part of a timed step.
+__global__ void __launch_bounds__(128)
+sspp_count_kernel(const __grid_constant__ ModelView M, const __grid_constant__ IterParams P, unsigned long long* __restrict__ totals) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const ScoreConfig& c = P.cfg;
+  const int tid = threadIdx.x, T = blockDim.x, D = c.D, K = c.K, nfd = c.n_free * D;
+  float* s_qs = reinterpret_cast<float*>(smem_raw);
+  float* s_xf = s_qs + D * T;
+  uint32_t wc[WC_COUNT];
+#pragma unroll
+  for (int e = 0; e < WC_COUNT; ++e) wc[e] = 0u;
+  const long long total = (long long)P.n_query * c.n_cand * c.Mc;
+  for (long long item = (long long)blockIdx.x * T + tid; item < total; item += (long long)gridDim.x * T) {
+    const int m = (int)(item % c.Mc);
+    const long long qc = item / c.Mc;                      // query * n_cand + candidate
+    const int query = (int)(qc / c.n_cand);
+    if (m < c.col_first || P.status[qc] == ST_ABSENT) continue;
+    const float* base = P.base + (size_t)query * K * D;
+    const float* par = P.params + (size_t)qc * nfd;
+    const float* row = P.psi_col + (size_t)m * P.w_col;
+    const int first = P.first_col[m];
+    for (int d = 0; d < D; ++d) {
+      float acc = 0.0f;
+      for (int k = 0; k < P.w_col; ++k) {
+        const int r = first + k, fr = r - c.free_begin;
+        const float x = (fr >= 0 && fr < c.n_free) ? par[fr * D + d] : base[r * D + d];
+        acc = fmaf(row[k], x, acc);
+      }
+      s_qs[d * T + tid] = acc;
+    }
+    SmemXF xf{s_xf, T, tid};
+    SmemQ qa{s_qs, T, tid};
+    (void)point_collision_cost(M, qa, xf, wc);
+  }
+#pragma unroll
+  for (int e = 0; e < WC_COUNT; ++e) {
+    const unsigned tot = __reduce_add_sync(0xFFFFFFFFu, wc[e]);
+    if ((tid & 31) == 0 && tot) atomicAdd(totals + e, (unsigned long long)tot);
+  }
+}
+
 // SDF refinement step: per collocation row m the configuration q_m = sum_j W[m][j] pts[j], the closest
 // sample sphere and g_m = -clearance * grad / |grad| (clearance times the unit direction towards the obstacle, the
 // `grad` of scripts/sdf_gradient/main.py:60-61); then G_j = (1/rows) sum_m g_m W[m][j] (main.py:66-81) by one thread
@@ -1111,11 +1235,11 @@ sspp_fma_probe_kernel(float* sink, int iters) {
 
 }  // namespace
 
-cudaError_t launch_sdf_bake(const ModelView& M, float* nodes, float* cells, cudaStream_t stream) {
-  sspp_sdf_bake_kernel<<<148 * 8, 256, 0, stream>>>(M, nodes);
+cudaError_t launch_sdf_bake(const ModelView& M, float* nodes, float* cells, int n_sm, cudaStream_t stream) {
+  sspp_sdf_bake_kernel<<<n_sm * 8, 256, 0, stream>>>(M, nodes);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
-  sspp_sdf_pack_kernel<<<148 * 8, 256, 0, stream>>>(M, nodes, cells);
+  sspp_sdf_pack_kernel<<<n_sm * 8, 256, 0, stream>>>(M, nodes, cells);
   return cudaGetLastError();
 }
 
@@ -1211,6 +1335,37 @@ cudaError_t launch_sdf_gradient(const ModelView& M, int D, int K, int rows, cons
     if (e != cudaSuccess) return e;
   }
   sspp_sdf_gradient_kernel<<<1, T, smem, stream>>>(M, D, K, rows, W, pts, dist, dirs, G);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_bspline_eval(const float* rows, int T, int n, const float* ctrl, int B, int d, float* out, int n_sm, cudaStream_t stream) {
+  const size_t smem = (size_t)T * n * sizeof(float);
+  if (smem > 200 * 1024) return cudaErrorInvalidValue;
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(sspp_bspline_eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  const long long total = (long long)B * T;
+  const int blocks = (int)std::max<long long>(1, std::min<long long>((total + 255) / 256, (long long)n_sm * 8));
+  sspp_bspline_eval_kernel<<<blocks, 256, smem, stream>>>(rows, T, n, ctrl, B, d, out);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_success_rows(const IterParams& P, float* rows, int32_t* idx, int32_t* count, cudaStream_t stream) {
+  const int nfd = P.cfg.n_free * P.cfg.D;
+  sspp_success_rows_kernel<<<dim3((unsigned)((P.cfg.n_cand + 255) / 256), (unsigned)P.n_query), 256, 0, stream>>>(
+      P.status, P.params, P.cfg.n_cand, nfd, rows, idx, count);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_count(const ModelView& M, const IterParams& P, unsigned long long* totals, int n_sm, cudaStream_t stream) {
+  const int T = 128;
+  const size_t smem = (size_t)(P.cfg.D + (M.chain ? 0 : M.n_mbody * 12)) * T * sizeof(float);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(sspp_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  sspp_count_kernel<<<n_sm * 4, T, smem, stream>>>(M, P, totals);
   return cudaGetLastError();
 }
 

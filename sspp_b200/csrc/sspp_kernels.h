@@ -53,7 +53,13 @@ struct IterParams {
   unsigned char* host_out; const unsigned char* res_dev;
   unsigned mir_bytes, mir_nsucc, mir_nelite, mir_bidx, mir_extra;   // byte offsets (multiples of 16): block end, n_success, n_elite, best_idx
   unsigned long long* probe; // diagnostics, NULL = off: [grid][kProbeSlots] %globaltimer stamps at the phase boundaries (coop kernel)
+  // Query inputs carried in the kernel's parameter block (ssppcu_plan_step; inline_words = 0: off): the point matrices
+  // [Q][K][D] followed by a state snapshot laid out like state_in.  The launch's first iteration samples from it, re-arms
+  // the live state with it and stores the point matrices to `base` - no host-to-device copy precedes the launch.
+  int inline_words;
+  float inline_blk[256];
 };
+constexpr int kInlineWords = 256;
 
 // Fused key exchange of the population-sharded path (sort_only handles, cooperative kernel).  Every rank owns an
 // exchange block of 16-byte lines [2 halves][world][shard_len] that its peers map (CUDA IPC across processes, plain
@@ -119,12 +125,22 @@ cudaError_t launch_eval_points(const ssppm::ModelView& M, int D, const float* pt
 
 // SDF mode: bake the node grid from the handle's static primitives (M.sg[0..n_sgeom)) and pack the
 // 8 corners of every cell contiguously for the kernel's two 16-byte loads per sample
-cudaError_t launch_sdf_bake(const ssppm::ModelView& M, float* nodes, float* cells, cudaStream_t stream);
+cudaError_t launch_sdf_bake(const ssppm::ModelView& M, float* nodes, float* cells, int n_sm, cudaStream_t stream);
 
 // SDF mode, refinement step: per collocation row the closest sample sphere's clearance and -clearance * unit field
 // gradient, and their projection on the point-matrix rows G[K][3] = (1/rows) sum_m dirs[m] W[m][.]  (device pointers)
 cudaError_t launch_sdf_gradient(const ssppm::ModelView& M, int D, int K, int rows, const float* W, const float* pts, float* dist,
                                 float* dirs, float* G, cudaStream_t stream);
+
+// batched B-spline evaluation out[B][T][d] = rows[T][n] . ctrl[B][n][d] (device pointers)
+cudaError_t launch_bspline_eval(const float* rows, int T, int n, const float* ctrl, int B, int d, float* out, int n_sm, cudaStream_t stream);
+
+// sampled rows of the converged candidates, compacted in candidate order: rows [Q][N][nfd], idx [Q][N], count [Q] (device-visible
+// addresses, normally mapped pinned host memory)
+cudaError_t launch_success_rows(const IterParams& P, float* rows, int32_t* idx, int32_t* count, cudaStream_t stream);
+
+// diagnostics: executed-work counters (ssppm::WorkCounter) of the stored candidates of the last iteration, added to totals[WC_COUNT]
+cudaError_t launch_count(const ssppm::ModelView& M, const IterParams& P, unsigned long long* totals, int n_sm, cudaStream_t stream);
 
 // FP32 FMA peak probe: every thread runs `iters` rounds of 8 independent FMA chains
 cudaError_t launch_fma_probe(float* sink, int blocks, int threads, int iters, cudaStream_t stream);

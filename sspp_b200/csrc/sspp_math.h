@@ -40,6 +40,29 @@ enum ContactRule { CR_COUNT = 0,   // planner A: every contact with dist < margi
                    CR_CENTER = 1,  // planner B: dist < -1e-3 adds -1/(centre distance + 1e-4)   (Collision.h:93-96)
                    CR_DEPTH = 2 }; // planner B, use_center_dist = false: dist < -1e-3 adds -dist (Collision.h:97-98)
 
+// Work counters (diagnostics: ssppcu_work_counters / sspp_count_kernel).  Every function below that takes a
+// `uint32_t* wc` adds to wc[WC_*] when the pointer is non-null; the scoring kernels pass nullptr and the
+// inlined code disappears.  They give the EXECUTED work of a launch (roofline: flop_per_point_executed).
+enum WorkCounter { WC_POINTS = 0,      // configurations scored (kinematics + collision)
+                   WC_FK_HINGE_AXIS,   // hinge about a coordinate axis of the body frame
+                   WC_FK_HINGE_GEN,    // hinge about a general axis (Rodrigues)
+                   WC_FK_SLIDE, WC_FK_FREE4,
+                   WC_FK_R0,           // bodies under a moving parent with a non-identity rest orientation (one 3x3 product more)
+                   WC_FK_ANCHOR,       // hinges with an anchor off the frame origin
+                   WC_GEOM_POS,        // moving geoms placed (centre only)
+                   WC_GEOM_ROT_BOX, WC_GEOM_ROT_AXIS,   // orientations placed on demand: full matrix / axis column only
+                   WC_BROAD,           // broad-phase pair tests (one affine form each)
+                   WC_NP_PLANE,        // narrow phase: any moving geom against a plane
+                   WC_NP_SPHERE_BOX,
+                   WC_NP_CAPS_BOX_EARLY, WC_NP_CAPS_BOX, WC_NP_CAPS_NEWTON,   // centre-distance exit / full segment-box / gradient evaluations inside it
+                   WC_NP_BOX_BOX_FACE, WC_NP_BOX_BOX,     // 6 face axes only (separated beyond thr) / all 15 axes
+                   WC_NP_CYL_BOX_FACE, WC_NP_CYL_BOX,
+                   WC_NP_OTHER,        // pairings served by prim_sd
+                   WC_CONTACTS,        // pairs that ended in a contact (cost != 0)
+                   WC_MM_TESTS, WC_MM_NARROW,             // moving-moving pairs: bounding-sphere tests / narrow phases
+                   WC_SDF_SAMPLES,     // SDF mode: sphere samples read from the grid
+                   WC_COUNT };
+
 // Every record is a whole number of 16-byte words with its hot fields grouped four by four: the kernels stage
 // the tables into shared memory and read them with warp-uniform (broadcast) 128-bit loads.
 struct alignas(16) DevBody {
@@ -391,7 +414,7 @@ SSPP_HD void rot_axis(m3& R, float s, float c) {
 
 // parent frame (Rp,pp) -> this body's frame (R,p) given planned coordinates q
 template <class TAB, class QA>
-SSPP_HD void fk_body(const TAB& bodies, int b, i4 jt, bool has_parent, const m3& Rp, v3 pp, QA& q, m3* R, v3* p) {
+SSPP_HD void fk_body(const TAB& bodies, int b, i4 jt, bool has_parent, const m3& Rp, v3 pp, QA& q, m3* R, v3* p, uint32_t* wc = nullptr) {
   const int jtype = jt.y, qidx = jt.z, axis_kind = jt.w;     // jt = (parent, jtype, qidx, axis_kind)
   if (jtype == JT_FREE4) {  // (x,y,z,yaw) -> pose; quaternion (cos y/2,0,0,sin y/2) == Rz(yaw)
     float s, c;
@@ -400,6 +423,7 @@ SSPP_HD void fk_body(const TAB& bodies, int b, i4 jt, bool has_parent, const m3&
     R->a[3] = s; R->a[4] = c;  R->a[5] = 0.0f;
     R->a[6] = 0.0f; R->a[7] = 0.0f; R->a[8] = 1.0f;
     *p = mk(q.get(qidx), q.get(qidx + 1), q.get(qidx + 2));
+    if (wc) ++wc[WC_FK_FREE4];
     return;
   }
   const f4 ps = rec_f4(bodies, b, BW_POS);             // pos, axis_sign
@@ -412,6 +436,11 @@ SSPP_HD void fk_body(const TAB& bodies, int b, i4 jt, bool has_parent, const m3&
     else { const m3t ra = rec_rot12(bodies, b, BW_R0); axis = ra.t; Rw = r0_identity ? Rp : mulm(Rp, ra.R.a); }
     pw = add(pp, mulv(Rp, mk(ps.x, ps.y, ps.z)));
   } else { const m3t ra = rec_rot12(bodies, b, BW_R0); axis = ra.t; Rw = ra.R; pw = mk(ps.x, ps.y, ps.z); }
+  if (wc) {
+    if (has_parent && !r0_identity) ++wc[WC_FK_R0];
+    if (jtype == JT_HINGE) { ++wc[axis_kind < 3 ? WC_FK_HINGE_AXIS : WC_FK_HINGE_GEN]; if (has_anchor) ++wc[WC_FK_ANCHOR]; }
+    else if (jtype == JT_SLIDE) ++wc[WC_FK_SLIDE];
+  }
   if (jtype == JT_HINGE) {
     m3 Rn;
     if (axis_kind < 3) {
@@ -492,7 +521,7 @@ SSPP_HD void seg_box_grad(float t, v3 p0, v3 d, v3 h, float* g, float* hs) {
   const float hz = (ez != 0.0f) ? d.z * d.z : 0.0f;
   *hs = hx + hy + hz;
 }
-SSPP_HD float seg_box_dist(v3 p0, v3 d, v3 h) {
+SSPP_HD float seg_box_dist(v3 p0, v3 d, v3 h, uint32_t* wc = nullptr) {
   float g0, g1, hs;
   seg_box_grad(0.0f, p0, d, h, &g0, &hs);
   seg_box_grad(1.0f, p0, d, h, &g1, &hs);
@@ -502,6 +531,7 @@ SSPP_HD float seg_box_dist(v3 p0, v3 d, v3 h) {
     for (int it = 0; it < 6; ++it) {
       float g;
       seg_box_grad(t, p0, d, h, &g, &hs);
+      if (wc) ++wc[WC_NP_CAPS_NEWTON];
       if (g > 0.0f) hi = t; else if (g < 0.0f) lo = t;
       float tn = (hs > 0.0f && g != 0.0f) ? t - g / hs : t;
       if (g != 0.0f && !(tn > lo && tn < hi)) tn = 0.5f * (lo + hi);
@@ -524,7 +554,7 @@ SSPP_HD void sat_max(float s, float l2, float* bs, float* bl2) {
 // the distance), < 0 the smallest penetration depth
 // thr: once the face axes alone separate the boxes by more than thr the 9 edge axes are skipped (the
 // result only has to stay above thr: callers compare it with a margin below thr)
-SSPP_HD float box_box_sd(const Prim& A, const Prim& B, float thr = 3.0e38f) {
+SSPP_HD float box_box_sd(const Prim& A, const Prim& B, float thr = 3.0e38f, uint32_t* wc = nullptr) {
   float Rm[9], Ab[9];
   const v3 dlt = sub(B.p, A.p);
   const v3 t = multv(A.R, dlt);
@@ -553,6 +583,7 @@ SSPP_HD float box_box_sd(const Prim& A, const Prim& B, float thr = 3.0e38f) {
     const float s = fabsf(pr) - (ra + rb);
     if (s > bs) bs = s;
   }
+  if (wc) ++wc[bs > thr ? WC_NP_BOX_BOX_FACE : WC_NP_BOX_BOX];
   if (bs > thr) return bs;
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
@@ -577,7 +608,7 @@ SSPP_HD float cyl_support(v3 a, float r, float h, v3 L, float l2) {  // support 
   const float la = dot(L, a);
   return fmaf(h, fabsf(la), r * sqrtf(fmaxf(fmaf(-la, la, l2), 0.0f)));
 }
-SSPP_HD float cyl_box_sd(const Prim& C, const Prim& B, float thr = 3.0e38f) {
+SSPP_HD float cyl_box_sd(const Prim& C, const Prim& B, float thr = 3.0e38f, uint32_t* wc = nullptr) {
   const v3 a = col(C.R, 2);
   const float r = C.s.x, h = C.s.y;
   const v3 dlt = sub(C.p, B.p);
@@ -594,6 +625,7 @@ SSPP_HD float cyl_box_sd(const Prim& C, const Prim& B, float thr = 3.0e38f) {
     const float s = fabsf(dot(dlt, a)) - rb - h;
     if (s > bs) bs = s;
   }
+  if (wc) ++wc[bs > thr ? WC_NP_CYL_BOX_FACE : WC_NP_CYL_BOX];
   if (bs > thr) return bs;
 #pragma unroll
   for (int i = 0; i < 3; ++i) {   // axis x box normal
@@ -756,8 +788,9 @@ SSPP_HD float prim_sd(const Prim& A, const Prim& B, bool* ok) {
 // the by-value operand swap of prim_sd, and with conservative early exits: as soon as a cheap lower
 // bound of the distance exceeds thr (> the pair's margin) that bound is returned instead of the exact
 // distance — the contact rule maps both to "no contact".  Other pairings fall back to prim_sd.
-SSPP_HD float moving_static_sd(const Prim& P, const Prim& S, float thr) {
+SSPP_HD float moving_static_sd(const Prim& P, const Prim& S, float thr, uint32_t* wc = nullptr) {
   if (S.type == GT_PLANE) {
+    if (wc && (P.type == GT_SPHERE || P.type == GT_CAPSULE || P.type == GT_CYLINDER || P.type == GT_BOX)) ++wc[WC_NP_PLANE];
     const v3 n = col(S.R, 2);
     const float d0 = dot(n, sub(P.p, S.p));
     if (P.type == GT_SPHERE) return d0 - P.s.x;
@@ -774,14 +807,16 @@ SSPP_HD float moving_static_sd(const Prim& P, const Prim& S, float thr) {
     if (P.type == GT_CAPSULE) {
       const v3 c = multv(S.R, sub(P.p, S.p));
       const float lb = point_box_sd(c, S.s) - P.s.y - P.s.x;     // centre distance minus half length minus radius
+      if (wc) ++wc[lb > thr ? WC_NP_CAPS_BOX_EARLY : WC_NP_CAPS_BOX];
       if (lb > thr) return lb;
       const v3 al = multv(S.R, col(P.R, 2));
-      return seg_box_dist(madd(al, -P.s.y, c), scale(al, 2.0f * P.s.y), S.s) - P.s.x;
+      return seg_box_dist(madd(al, -P.s.y, c), scale(al, 2.0f * P.s.y), S.s, wc) - P.s.x;
     }
-    if (P.type == GT_BOX) return box_box_sd(P, S, thr);
-    if (P.type == GT_CYLINDER) return cyl_box_sd(P, S, thr);
-    if (P.type == GT_SPHERE) return point_box_sd(multv(S.R, sub(P.p, S.p)), S.s) - P.s.x;
+    if (P.type == GT_BOX) return box_box_sd(P, S, thr, wc);
+    if (P.type == GT_CYLINDER) return cyl_box_sd(P, S, thr, wc);
+    if (P.type == GT_SPHERE) { if (wc) ++wc[WC_NP_SPHERE_BOX]; return point_box_sd(multv(S.R, sub(P.p, S.p)), S.s) - P.s.x; }
   }
+  if (wc && S.type != GT_PLANE) ++wc[WC_NP_OTHER];
   bool ok;
   return prim_sd(P, S, &ok);
 }
@@ -841,8 +876,9 @@ SSPP_HD Prim static_prim(const DevSGeom& g) { return static_prim(&g, 0); }
 // partners first, then bounded ones); the narrow phase then visits the set bits in ascending order, so the
 // contact costs are summed in pair-table order.
 template <class MT, class XF, class QA>
-SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf) {
+SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf, uint32_t* wc = nullptr) {
   float cost = M.static_cost;
+  if (wc) ++wc[WC_POINTS];
   m3 R; v3 p = mk(0.f, 0.f, 0.f);
 #pragma unroll
   for (int k = 0; k < 9; ++k) R.a[k] = 0.0f;
@@ -859,7 +895,7 @@ SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf) {
         pp = mk(xf.get(jt.x, 9), xf.get(jt.x, 10), xf.get(jt.x, 11));
       }
     } else { pp = mk(0.f, 0.f, 0.f); Rp = R; }
-    fk_body(M.body, b, jt, hp, Rp, pp, q, &R, &p);
+    fk_body(M.body, b, jt, hp, Rp, pp, q, &R, &p, wc);
     if (!M.chain) {
 #pragma unroll
       for (int k = 0; k < 9; ++k) xf.put(b, k, R.a[k]);
@@ -867,6 +903,7 @@ SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf) {
     }
     if (M.sdf_mode) {                                        // sphere samples of this body against the grid
       const i4 sp = rec_i4(M.body, b, BW_SPH);          // sph_begin, sph_end
+      if (wc) wc[WC_SDF_SAMPLES] += (uint32_t)(sp.y - sp.x);
 #if defined(__CUDA_ARCH__) && SDF_BATCH > 1
 #pragma unroll 1
       for (int k0 = sp.x; k0 < sp.y; k0 += SDF_BATCH) {
@@ -909,6 +946,7 @@ SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf) {
       P.p = add(p, mulv(R, mk(gp.x, gp.y, gp.z)));
       P.type = gi.x;
       bool rotated = false;
+      if (wc) { ++wc[WC_GEOM_POS]; wc[WC_BROAD] += (uint32_t)(gi.w - gi.y); }
       {
         const int k0 = gi.y;
         uint32_t near_mask = 0u;
@@ -928,10 +966,12 @@ SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf) {
           near_mask &= near_mask - 1u;
           const i4 t4 = rec_i4(M.pair, k0 + j, PW_S);        // s, margin, thr, plane (floats as raw words)
           const float margin = word_as_float(t4.y), thr = word_as_float(t4.z);
-          if (!rotated) { place_rotation(M.mg, g, gi.x, R, &P); rotated = true; }
+          if (!rotated) { place_rotation(M.mg, g, gi.x, R, &P); rotated = true; if (wc && gi.x != GT_SPHERE) ++wc[gi.x == GT_BOX ? WC_GEOM_ROT_BOX : WC_GEOM_ROT_AXIS]; }
           const Prim Q = static_prim(M.sg, t4.x);
-          const float d = moving_static_sd(P, Q, thr);
-          cost += contact_cost(M.rule, d, margin, P.p, Q.p);
+          const float d = moving_static_sd(P, Q, thr, wc);
+          const float cc = contact_cost(M.rule, d, margin, P.p, Q.p);
+          if (wc && cc != 0.0f) ++wc[WC_CONTACTS];
+          cost += cc;
         }
       }
     }
@@ -950,7 +990,9 @@ SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf) {
     const Prim P = place(M.mg, mp.x, Ra, pa), Q = place(M.mg, mp.y, Rb, pb);
     const v3 w = sub(P.p, Q.p);
     const float rr = ra + rb + fmaxf(margin, 0.0f) + 1e-4f;
+    if (wc) ++wc[WC_MM_TESTS];
     if (dot(w, w) > rr * rr) continue;
+    if (wc) ++wc[WC_MM_NARROW];
     bool ok;
     const float d = prim_sd(P, Q, &ok);
     cost += contact_cost(M.rule, d, margin, P.p, Q.p);

@@ -37,4 +37,16 @@ SplineSetup make_setup(int K, int p);
 //   via-point form     (planner B): Psi = Basis(grid) * Ainv    [M x K]
 std::vector<double> collocation_matrix(const SplineSetup& s, const std::vector<double>& grid, bool via_form);
 
+// ---- the reference's Python spline twins (sspp/BSplines.py, sspp/CubicPath.py), host FP64 ----
+// clamped UNIFORM knot vector of BSplines.py:58-62: k zeros, linspace(0, 1, n - k + 1), k ones  (n + k + 1 values)
+std::vector<double> uniform_knots(int n_ctrl, int k);
+// Cox-de Boor basis with HALF-OPEN spans as BSplines.py:11-29 defines it (B_{i,0} = 1 iff t[i] <= theta < t[i+1], so every
+// value is 0 at theta = t.back()); deriv: BSplines.py:31-42.  Full row of n = knots.size() - k - 1 values.
+std::vector<double> half_open_basis_row(double theta, int k, const std::vector<double>& knots, bool deriv);
+// row that gives bspline(theta, t, c, k) = row . c with the end rules of BSplines.py:44-51 (theta < 0: c[0] B_0(0);
+// theta >= 1: c[n-1]); deriv: bspline_derivative, BSplines.py:53-55 (no end rules)
+std::vector<double> curve_row(double theta, int k, const std::vector<double>& knots, bool deriv);
+// compute_control_points, BSplines.py:65-106: via [n][d] row-major at theta_i = i/(n-1) on uniform knots -> ctrl [n][d]
+std::vector<double> fit_uniform(const std::vector<double>& via, int n, int d, int k, std::vector<double>* knots_out);
+
 }  // namespace sspp

@@ -1,11 +1,16 @@
 """Algorithmic work per scored collocation point (constants frozen here).
 
 The scoring path moves ~16 B per CANDIDATE (L, Cnf, Cwf, cost, status, key) and reads a few KiB
-of constants, so HBM is not the bound; FP32 issue is.  `flop_per_point` is the NOMINAL model the
-roofline fraction is quoted on: every filtered geom pair is charged its full narrow phase, although
-the kernel's bounding-sphere cull skips most of them (so nominal FLOP/s can exceed what the FP32
-pipe physically executed; the ncu pipe utilisation in profiles/ is the physical measure).
-FMA = 2 FLOP.
+of constants, so HBM is not the bound; FP32 issue is.  Two figures (SURVEY 8d asks for both):
+
+  executed_flop()  F_executed: the floating-point operations the kernel's arithmetic performs for the work it
+                   actually did, from the counters of ssppcu_work_counters (pairs that reached the narrow phase by
+                   type, early exits, Newton steps, placements, broad-phase tests) times the operation count of the
+                   corresponding code in sspp_b200/csrc/sspp_math.h.  `roofline.frac` is quoted on THIS figure.
+  work_model()     F_nominal: every filtered geom pair charged its full narrow phase, before the compile-time pruning
+                   and the per-point broad phase - the work the reference's semantics define (MuJoCo tests every
+                   pair it keeps).  Reported as `frac_nominal`; it can exceed what the FP32 pipe executed.
+FMA = 2 FLOP; add, mul, sqrt, div = 1; compare / min / max / abs / integer = 0.
 """
 from __future__ import annotations
 
@@ -80,3 +85,57 @@ def work_model(model, mode: int, dof: int, n_points: int, body: str = "") -> dic
     return dict(flop_per_point=float(total), spline=spline, fk=fk, placement=place, narrow_phase=narrow, cost_terms=cost,
                 sfu_sincos=sfu, n_pairs=int(sum(pair_hist.values())), n_moving_geoms=len(touched),
                 pair_hist={f"{k[0]}-{k[1]}": n for k, n in sorted(pair_hist.items())})
+
+
+# ---- F_executed: operation counts of the code paths of sspp_b200/csrc/sspp_math.h (FMA = 2) ----
+SINCOS = 24                 # sincos_poly: range reduction 1 mul + 3 FMA, two minimax kernels
+EXEC_FLOP = dict(
+    fk_hinge_axis=18 + SINCOS + 1 + 18,      # frame origin (R p + p), sincos, sign, rot_axis (two columns mix)
+    fk_hinge_gen=18 + SINCOS + 28 + 45,      # Rodrigues matrix + 3x3 product
+    fk_slide=18 + 15 + 6,
+    fk_free4=SINCOS,
+    fk_r0=45,                                # rest orientation: one more 3x3 product
+    fk_anchor=36,
+    geom_pos=18 + 5,                         # centre + |p|^2 for the bounded partners' test
+    geom_rot_box=45, geom_rot_axis=15,
+    broad=6,                                 # one affine form: 3 FMA
+    np_plane=29,                             # box against a plane (the costliest of the plane forms)
+    np_sphere_box=28,
+    np_caps_box_early=29,                    # centre into the box frame + point-box distance + bound
+    np_caps_box=29 + 25 + 2 * 19 + 15 + 1,   # ... + segment into the box frame, two bracket gradients, end evaluation
+    np_caps_newton=23,                       # one gradient evaluation + Newton / bisection step
+    np_box_box_face=120, np_box_box=275,     # 6 face axes / all 15 axes + depth
+    np_cyl_box_face=84, np_cyl_box=292,
+    np_other=60,
+    contacts=11,                             # centre-distance cost (Collision.h:96); the count rule adds 1.0
+    mm_tests=138, mm_narrow=126,
+    sdf_samples=49,                          # sphere centre, cell + fractions, trilinear blend, radius
+)
+SAMPLE_FLOP = 64            # one sampled element: Box-Muller (log, sqrt, sincos) + mean + sigma z
+
+
+def executed_flop(counters: dict, *, n_cand_total: int, check_points: int, dof: int, n_points: int, degree: int, mode: int,
+                  limit_penalty: bool = False) -> dict:
+    """F_executed per scored collocation point (N * M points) from the work counters of one iteration.
+    n_cand_total: candidates scored (all queries); returns the per-term breakdown too."""
+    M = check_points
+    pts = float(n_cand_total * M)
+    task = mode == 1
+    dp = (dof + 3) // 4 * 4
+    W = degree + 1
+    evals = (M + 1) + (M if task else M)             # collision grid + (TASK: the segment's start point again | JOINT: the arc grid)
+    n_seg = M if task else M - 1
+    spline = n_cand_total * (evals * 2 * W * dp + n_seg * (3 * dof + 1))
+    n_free = n_points - 2 if task else n_points - 2 * degree
+    sampling = n_cand_total * n_free * dof * SAMPLE_FLOP
+    penalty = counters["points"] * (4 if task else (4 * dof if limit_penalty else 0))
+    terms = {k: counters[k] * f for k, f in EXEC_FLOP.items()}
+    fk = sum(terms[k] for k in terms if k.startswith("fk_"))
+    place = terms["geom_pos"] + terms["geom_rot_box"] + terms["geom_rot_axis"]
+    narrow = sum(terms[k] for k in terms if k.startswith("np_") or k.startswith("mm_")) + terms["contacts"]
+    total = spline + sampling + penalty + fk + place + terms["broad"] + narrow + terms["sdf_samples"]
+    return dict(flop_per_point_executed=total / pts, spline=spline / pts, sampling=sampling / pts, fk=fk / pts, placement=place / pts,
+                broad_phase=terms["broad"] / pts, narrow_phase=narrow / pts, sdf=terms["sdf_samples"] / pts, penalty=penalty / pts,
+                pairs_tested_per_point=counters["broad"] / pts,
+                pairs_in_narrow_phase_per_point=sum(counters[k] for k in counters if k.startswith("np_") and k != "np_caps_newton") / pts,
+                contacts_per_point=counters["contacts"] / pts)

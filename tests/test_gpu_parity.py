@@ -382,3 +382,80 @@ def test_set_distribution_round_trips_mean_sigma_and_either_alone():
     h.iterate(SEED, 0, 1)
     r = h.results()
     assert r["any_success"].shape == (d.n_queries,)
+
+
+@pytest.mark.parametrize("kind", ["joint", "joint_multi", "task", "task_batch"])
+def test_plan_step_equals_the_three_calls(kind):
+    """ssppcu_plan_step (query + initial state in the kernel's parameter block, one launch) == ssppcu_set_queries +
+    ssppcu_set_joint_noise / ssppcu_reset_distribution + ssppcu_iterate, bit for bit; success rows and candidate_ctrl read back
+    what the kernel sampled"""
+    from sspp_b200 import capi
+    if kind == "joint":
+        case = joint_case(n_samples=1000, check_points=32, do_update=True)
+    elif kind == "joint_multi":
+        case = joint_case(n_samples=300, check_points=24, do_update=True, n_queries=2)       # two queries still fit the parameter block
+    elif kind == "task":
+        case = task_case(n_samples=62, n_points=5)
+    else:
+        rng = np.random.default_rng(5)
+        Q = 300                                                                               # too many for the block: the three-call path inside
+        s = np.column_stack([rng.uniform(0.2, 0.6, Q), rng.uniform(-0.4, 0.4, Q), rng.uniform(0.14, 0.4, Q), rng.uniform(-1.5, 1.5, Q)])
+        e = np.column_stack([rng.uniform(0.2, 0.6, Q), rng.uniform(-0.4, 0.4, Q), rng.uniform(0.14, 0.4, Q), rng.uniform(-1.5, 1.5, Q)])
+        case = task_case(n_queries=Q, start=s, end=e)
+    a = capi.Handle(case.model, case.cfg); b = capi.Handle(case.model, case.cfg)
+    b.set_success_rows(True)
+    joint = case.cfg.mode == 0
+    for rep in range(2):                                       # the second round starts from a used handle (state must be re-armed)
+        case.prepare(a)
+        a.iterate(SEED, 10 * rep, 3)
+        b.plan_step(case.start, case.end, case.joint_sigma if joint else case.sigma0, case.limits if joint else None, SEED, 10 * rep, 3)
+        ra, rb = a.results(), b.results()
+        for k in ("L", "Cnf", "Cwf", "cost"):
+            assert np.array_equal(ra[k].view(np.uint32), rb[k].view(np.uint32)), k
+        for k in ("status", "n_success", "n_elite", "best_idx"):
+            assert np.array_equal(ra[k], rb[k]), k
+        assert np.array_equal(a.params(), b.params()) and np.array_equal(a.base(), b.base())
+        for x, y in zip(a.get_distribution() + a.best(), b.get_distribution() + b.best()):
+            assert np.array_equal(x, y)
+        P = b.params()
+        for q in range(min(case.cfg.n_queries, 3)):
+            rows, idx = b.success_rows(q)
+            ok = np.flatnonzero(rb["status"][q] == 0)
+            assert np.array_equal(idx, ok) and np.array_equal(rows, P[q].reshape(len(P[q]), -1)[ok])
+            if len(ok):
+                c = b.candidate_ctrl(int(ok[-1]), q)
+                fb = 1 if not joint else case.cfg.degree
+                assert np.array_equal(c[fb:fb + P.shape[2]], P[q, ok[-1]]) and np.array_equal(np.delete(c, np.s_[fb:fb + P.shape[2]], 0),
+                                                                                             np.delete(b.base()[q], np.s_[fb:fb + P.shape[2]], 0))
+    with pytest.raises(capi.SsppError):
+        a.success_rows(0)                                      # never switched on for this handle
+    a.close(); b.close()
+
+
+def test_work_counters_describe_the_scored_iteration():
+    from sspp_b200 import capi, roofline
+    case = joint_case(n_samples=512, check_points=64, do_update=True)
+    h = _handle(case)
+    h.iterate(SEED, 0, 1)
+    wc = h.work_counters()
+    r = h.results()
+    d = h.dims
+    assert wc["points"] == 512 * 65 and wc["fk_hinge_axis"] == 7 * wc["points"] and wc["broad"] == d.n_pair * wc["points"]
+    assert wc["np_caps_box"] <= wc["np_caps_box_early"] + wc["np_caps_box"] <= wc["broad"]
+    assert wc["contacts"] == int(round(float(r["Cnf"].sum())))              # planner A: every contact adds exactly 1 (sspp.h:144)
+    # the same counters from the replica oracle's host build of the same header
+    o2 = o2_for(case)
+    import ctypes as C
+    o2.lib.o2_work.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+    psi_col, psi_arc = h.collocation()
+    case.prepare(h)
+    mean, sigma = h.get_distribution()
+    o2.lib.o2_work(o2.h, 1, None, 0)
+    o2.iterate(psi_col, psi_arc, h.base()[0], mean[0], sigma[0], np.zeros_like(mean[0]), 0, SEED, 0)
+    out = np.zeros(len(capi.WORK_COUNTERS), np.uint64)
+    o2.lib.o2_work(o2.h, 0, out.ctypes.data_as(C.c_void_p), len(out))
+    assert {k: int(v) for k, v in zip(capi.WORK_COUNTERS, out)} == wc
+    ex = roofline.executed_flop(wc, n_cand_total=512, check_points=64, dof=7, n_points=10, degree=3, mode=0)
+    nom = roofline.work_model(case.model, 0, 7, 10)
+    assert 500 < ex["flop_per_point_executed"] < nom["flop_per_point"]
+    h.close()

@@ -108,10 +108,13 @@ def test_plan_device_buffers(sp):
     import torch
     p = sp.SamplingPathPlanner7(XML)
     p.set_verbose(False)
-    d = p.plan_device(Q_START, Q_END, 0.08, np.full(7, np.pi), 512, 64, 10)
+    d = p.plan_device(Q_START, Q_END, 0.08, np.full(7, np.pi), 512, 64, 10, fetch_ctrl=True)
     assert d["n_candidates"] == 512 and d["ctrl"].shape == (512, 4, 7)
     assert (d["status"] == 0).sum() == d["n_success"]
     ok = d["status"] == 0
+    # the collision-free candidates' rows travel with the results, compacted in candidate order; all rows only on request
+    assert np.array_equal(d["success_idx"], np.flatnonzero(ok)) and np.array_equal(d["ctrl_success"], d["ctrl"][ok])
+    assert "ctrl" not in p.plan_device(Q_START, Q_END, 0.08, np.full(7, np.pi), 512, 64, 10)
     assert d["best_idx"] == int(np.flatnonzero(ok)[np.argmin(d["arc_length"][ok])])
 
     class Dev:
