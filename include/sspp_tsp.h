@@ -225,13 +225,16 @@ class TaskSpacePlanner {
     mean_.assign(nv, Point{}); sigma_.assign(nv, Point{});
     for (int r = 0; r < nv; ++r)
       for (int d = 0; d < kDOF; ++d) { mean_[r][d] = m[(size_t)r * kDOF + d]; sigma_[r][d] = s[(size_t)r * kDOF + d]; }
-    // path_ follows the forwarded best (tsp_planner.h:131-138); before any success it is the straight line
+    // path_: every plan() call starts from the straight start-end line (tsp_planner.h:74-76) and replaces it with the best
+    // path only when THIS iteration had successes (tsp_planner.h:122, 131-138) - a best forwarded from an earlier query that
+    // fails now (iterate = true with a moved start / end) must not leak into path_
     std::vector<float> best((size_t)dims_.nfd);
     int32_t valid = 0;
     check(h_, ssppcu_get_best(h_, best.data(), &valid));
+    const bool use_best = valid && ns > 0;
     ViaSet v(nv);
     for (int r = 0; r < nv; ++r)
-      for (int d = 0; d < kDOF; ++d) v[r][d] = valid ? (double)best[(size_t)r * kDOF + d] : initial_via_[1 + r][d];
+      for (int d = 0; d < kDOF; ++d) v[r][d] = use_best ? (double)best[(size_t)r * kDOF + d] : initial_via_[1 + r][d];
     path_ = spline_from_vias(v);
   }
 

@@ -1,7 +1,9 @@
 """torchrun check on N GPUs: a population sharded over the ranks reaches the state of the unsharded population,
 bit for bit, with both transports (all-gather + merge kernels; key exchange fused into the iteration kernel), and what
 an iteration costs either way.  POP_CASE=sdf runs the cfg 3 scene (cluttered stacking scene, SDF grid 128^3) instead
-of the robocrane task scene; POP_PER_RANK (default 8192) candidates per rank."""
+of the robocrane task scene; POP_PER_RANK (default 8192) candidates per rank.
+POP_SOAK=<iterations> (default 0) appends a soak of the fused exchange: that many iterations back to back, the state re-armed
+every 50 iterations, bit identity with the unsharded handle verified every 1000 iterations (flag protocol / epoch wrap / halves)."""
 import os, sys
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
@@ -76,6 +78,27 @@ names = {1: "scored", 3: "ranked", 8: "shard_ordered", 9: "published", 10: "flag
 if rank == 0:
     print("fused-exchange phases on rank 0 (us since launch start, min/median/max over CTAs): " +
           ", ".join(f"{n} {A[:, :, i].min(axis=1).mean():.1f}/{np.median(A[:, :, i], axis=1).mean():.1f}/{A[:, :, i].max(axis=1).mean():.1f}" for i, n in names.items()), flush=True)
+SOAK = int(os.environ.get("POP_SOAK", "0"))
+if SOAK:
+    import time
+    c0 = sdf_case(n_samples=8, check_points=64, n_points=5, dims=(128, 128, 128)) if SDF else task_case(n_samples=8, check_points=64, n_points=5)
+    ok3, checked, t_s = True, 0, time.perf_counter()
+    for it in range(SOAK):
+        if it % 50 == 0:
+            c0.prepare(px.h); c0.prepare(full2)
+        px.iterate(SEED, 1000 + it); full2.iterate(SEED, 1000 + it, 1)
+        if it % 1000 == 999 or it == SOAK - 1:
+            px.check(); torch.cuda.synchronize()
+            fi, fc, fw = full2.elites(0); mi, mc, mw = px.h.merged(N)
+            m0, s0 = full2.get_distribution(); m1, s1 = px.h.get_distribution()
+            ok3 &= bool(np.array_equal(mi[:len(fi)], fi) and np.array_equal(mw[:len(fw)], fw) and np.array_equal(m0, m1) and np.array_equal(s0, s1))
+            checked += 1
+    px.check(); torch.cuda.synchronize()
+    rows = [None] * world
+    dist.all_gather_object(rows, bool(ok3))
+    if rank == 0:
+        print(f"soak: {'OK' if all(rows) else 'FAIL ' + str([i for i, r in enumerate(rows) if not r])} on {world} ranks, {SOAK} fused-exchange iterations, "
+              f"{checked} bit-identity checks against the unsharded handle, {time.perf_counter() - t_s:.1f} s, protocol {os.environ.get('SSPPCU_XCHG_PROTOCOL', '1')}", flush=True)
 t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
 with torch.cuda.stream(px.stream):
     t0.record()

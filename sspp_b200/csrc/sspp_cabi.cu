@@ -60,7 +60,8 @@ struct ssppcu_planner {
   bool res_fresh = false;    // the last call was a launch that mirrors its results (cleared by any other call)
   // success rows (ssppcu_set_success_rows): mapped pinned block rows [Q][N][nfd] | idx [Q][N] | count [Q], filled by a
   // compaction kernel enqueued behind every iteration launch
-  bool rows_on = false, rows_fresh = false;
+  bool rows_on = false;
+  unsigned long long launch_epoch = 0, rows_epoch = ~0ull;   // the rows in the pinned block belong to launch rows_epoch
   unsigned char* h_rows = nullptr; unsigned char* h_rows_dev = nullptr; size_t o_ridx = 0, o_rcount = 0;
   // fused key exchange of a population shard (ssppcu_exchange_*): this rank's block, the peers' mappings
   struct Exchange {
@@ -457,6 +458,21 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
       if (got == per_sm || round == 2) break;
       per_sm = got;
     }
+    {   // whatever round the loop left on: the ranking scratch of the FINAL grid must fit, and a chunk must hold keys
+      const long long total = (long long)c.n_queries * s.n_cand;
+      const size_t fixed = (size_t)((total + h->grid - 1) / h->grid) * 16 + 64;
+      if (fixed + 256 * 8 > h->smem) {
+        h->smem = std::min<size_t>(fixed + std::min<size_t>((size_t)s.n_cand + 1, 8192) * 8, smem_cap);
+        if (fixed + 256 * 8 > h->smem) { set_err(err, errlen, "population too large for the ranking scratch of the final grid"); delete h; return SSPPCU_ELIMIT; }
+        int got = 0;
+        if ((ce = iterate_occupancy(h->variant, h->threads, h->smem + h->smem_model, &got)) != cudaSuccess || got < 1 ||
+            (long long)got * h->n_sm < h->grid) {
+          set_err(err, errlen, "the grid does not stay co-resident with the ranking scratch it needs"); delete h; return SSPPCU_ELIMIT;
+        }
+      }
+      P.rank_chunk = (int)std::min<size_t>((size_t)s.n_cand + 1, (h->smem - fixed) / 8) & ~1;
+      if (P.rank_chunk < 2) { set_err(err, errlen, "ranking chunk too small"); delete h; return SSPPCU_ELIMIT; }
+    }
   } else {
     if (h->smem > smem_cap) { set_err(err, errlen, "problem shape needs more shared memory than a CTA has"); delete h; return SSPPCU_ELIMIT; }
     P.n_tiles = c.n_queries;
@@ -564,7 +580,7 @@ namespace {
 
 int check(ssppcu_t* h) {
   if (!h) return SSPPCU_EINVAL;
-  h->best_fresh = false; h->res_fresh = false; h->rows_fresh = false;
+  h->best_fresh = false; h->res_fresh = false;
   cudaError_t e = cudaSetDevice(h->cfg.device);
   if (e != cudaSuccess) return cuda_fail(h, e, "cudaSetDevice");
   return 0;
@@ -808,10 +824,11 @@ static int iterate_impl(ssppcu_t* h, uint64_t seed, uint32_t iter0, int n_iters,
   }
   CU(h, launch_iterate(h->view, P, h->variant, h->threads, h->smem + h->smem_model, h->grid, h->stream));
   h->res_fresh = mirror;
+  ++h->launch_epoch;
   if (h->rows_on) {
     CU(h, launch_success_rows(h->P, reinterpret_cast<float*>(h->h_rows_dev), reinterpret_cast<int32_t*>(h->h_rows_dev + h->o_ridx),
                               reinterpret_cast<int32_t*>(h->h_rows_dev + h->o_rcount), h->stream));
-    h->rows_fresh = true;
+    h->rows_epoch = h->launch_epoch;
   }
   return SSPPCU_OK;
 }
@@ -885,13 +902,11 @@ int ssppcu_set_success_rows(ssppcu_t* h, int on) {
 }
 
 int ssppcu_get_success_rows(ssppcu_t* h, int query, const float** rows, const int32_t** idx, int32_t* n) {
-  const bool fresh = h && h->rows_fresh;
   if (int rc = check(h)) return rc;
   if (!h->rows_on || !h->h_rows) return fail(h, SSPPCU_EINVAL, "success rows are off (ssppcu_set_success_rows)");
   if (query < 0 || query >= h->P.n_query) return fail(h, SSPPCU_EINVAL, "query out of range");
-  if (!fresh) return fail(h, SSPPCU_EINVAL, "no iteration since the last read-back: the rows belong to an older launch");
+  if (h->rows_epoch != h->launch_epoch) return fail(h, SSPPCU_EINVAL, "no iteration was launched since success rows were switched on");
   CU(h, cudaStreamSynchronize(h->stream));
-  h->rows_fresh = true;                                        // reading another query of the same launch is fine
   const size_t N = h->P.cfg.n_cand, nfd = (size_t)h->P.cfg.n_free * h->P.cfg.D;
   if (rows) *rows = reinterpret_cast<const float*>(h->h_rows) + (size_t)query * N * nfd;
   if (idx) *idx = reinterpret_cast<const int32_t*>(h->h_rows + h->o_ridx) + (size_t)query * N;
@@ -1172,6 +1187,8 @@ static int exchange_finish_attach(ssppcu_t* h, void* const* bases) {
   ExchangeParams E;
   std::memset(&E, 0, sizeof(E));
   E.world = x.world; E.rank = x.rank; E.shard_len = h->P.cfg.n_cand;
+  E.protocol = 1;
+  if (const char* pr = std::getenv("SSPPCU_XCHG_PROTOCOL")) E.protocol = std::atoi(pr) != 0;
   E.n_global = h->cfg.shard_global; E.n_pad = h->merge_cap;
   for (int r = 0; r < x.world; ++r) E.peer_lines[r] = reinterpret_cast<uint4*>(bases[r]);
   E.lines_local = reinterpret_cast<const uint4*>(x.block);
@@ -1223,6 +1240,7 @@ int ssppcu_iterate_exchange(ssppcu_t* h, uint64_t seed, uint32_t iter) {
   P.seed = seed; P.iter0 = iter; P.n_inner = 1; P.state_in = nullptr;
   P.xchg = x.d_params; P.xchg_epoch = ++x.epoch;
   CU(h, launch_iterate(h->view, P, h->variant, h->threads, h->smem + h->smem_model, h->grid, h->stream));
+  ++h->launch_epoch;
   h->merged_n = x.world * h->P.cfg.n_cand;
   return SSPPCU_OK;
 }

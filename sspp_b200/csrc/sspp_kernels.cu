@@ -323,6 +323,9 @@ __device__ __forceinline__ void score_tile(const SmemModel& M, const IterParams&
       P.L[qn + cand] = L; P.Cnf[qn + cand] = Cnf; P.Cwf[qn + cand] = Cwf; P.cost[qn + cand] = cost;
       P.status[qn + cand] = (uint8_t)st;
       P.keys_raw[(size_t)query * P.n_pad + cand] = sort_key(cost, st, (uint32_t)(P.cand_offset + cand));
+      // the ranking phase of OTHER CTAs reads these keys with a bulk asynchronous copy (async proxy): order this generic-proxy
+      // store before it across the proxies; the grid barrier then orders it across the CTAs
+      asm volatile("fence.proxy.async.global;" ::: "memory");
     }
   }
 }
@@ -684,13 +687,34 @@ struct RegenParams {
 };
 __device__ __forceinline__ void merge_finish_body(const MergeParams& P, float* s_part, int block, int n_blocks, const float* vals = nullptr, int vals_pitch = 0);
 
-__device__ __forceinline__ void st_line(uint4* p, unsigned long long key, unsigned epoch) {
-  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};"
-               :: "l"(p), "r"((unsigned)key), "r"(epoch), "r"((unsigned)(key >> 32)), "r"(epoch) : "memory");
+// One exchange line = 16 bytes = two 8-byte halves {key word, epoch}.  A reader accepts a line when BOTH halves carry the
+// epoch, so data and flag travel together and no fence or separate signal is needed - provided each 8-byte half becomes
+// visible as a whole.  PTX promises that for a naturally aligned 8-byte SCALAR access (single-copy atomicity), not for a vector
+// access.  protocol 1 (default) therefore writes / reads a line as two 8-byte scalar accesses, relaxed at system scope (a
+// strong operation: not torn, not cached stale); protocol 0 is the first implementation - one 16-byte volatile vector access per
+// line - which relies on the hardware never tearing an aligned 8-byte half of a vector store over NVLink.  Both were measured
+// (profiles/r02_popshard_*): SSPPCU_XCHG_PROTOCOL selects.
+__device__ __forceinline__ void st_line(uint4* p, unsigned long long key, unsigned epoch, int protocol) {
+  if (protocol == 0) {
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};"
+                 :: "l"(p), "r"((unsigned)key), "r"(epoch), "r"((unsigned)(key >> 32)), "r"(epoch) : "memory");
+    return;
+  }
+  const unsigned long long lo = (unsigned long long)(unsigned)key | ((unsigned long long)epoch << 32);
+  const unsigned long long hi = (key >> 32) | ((unsigned long long)epoch << 32);
+  asm volatile("st.relaxed.sys.global.b64 [%0], %1;" :: "l"(p), "l"(lo) : "memory");
+  asm volatile("st.relaxed.sys.global.b64 [%0 + 8], %1;" :: "l"(p), "l"(hi) : "memory");
 }
-__device__ __forceinline__ uint4 ld_line(const uint4* p) {
+__device__ __forceinline__ uint4 ld_line(const uint4* p, int protocol) {
   uint4 v;
-  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  if (protocol == 0) {
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+  }
+  unsigned long long lo, hi;
+  asm volatile("ld.relaxed.sys.global.b64 %0, [%1];" : "=l"(lo) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.sys.global.b64 %0, [%1 + 8];" : "=l"(hi) : "l"(p) : "memory");
+  v.x = (unsigned)lo; v.y = (unsigned)(lo >> 32); v.z = (unsigned)hi; v.w = (unsigned)(hi >> 32);
   return v;
 }
 
@@ -710,7 +734,7 @@ __device__ void exchange_and_merge(const IterParams& P, cg::grid_group& grid, fl
   const long long total = (long long)W * len;
   for (long long e = (long long)blockIdx.x * T + tid; e < total; e += (long long)gridDim.x * T) {
     const int j = (int)(e / W), r = (int)(e - (long long)j * W);      // neighbouring threads feed different links
-    st_line(X.peer_lines[r] + slot + j, __ldcg(P.keys + j), epoch);
+    st_line(X.peer_lines[r] + slot + j, __ldcg(P.keys + j), epoch, X.protocol);
   }
   stamp(9);
   // receive: poll every line of this epoch's half until both flag words carry the epoch; keys go to a compact array
@@ -718,13 +742,13 @@ __device__ void exchange_and_merge(const IterParams& P, cg::grid_group& grid, fl
   unsigned long long t0;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
   for (long long e = (long long)blockIdx.x * T + tid; e < total; e += (long long)gridDim.x * T) {
-    uint4 v = ld_line(lines + e);
+    uint4 v = ld_line(lines + e, X.protocol);
     while (v.y != epoch || v.w != epoch) {
       unsigned long long t1;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
       if (t1 - t0 > X.timeout_ns) { *reinterpret_cast<volatile int*>(X.status) = 1; break; }
       __nanosleep(100);
-      v = ld_line(lines + e);
+      v = ld_line(lines + e, X.protocol);
     }
     X.gathered[e] = (unsigned long long)v.x | ((unsigned long long)v.z << 32);
   }

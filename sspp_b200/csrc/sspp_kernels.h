@@ -71,6 +71,7 @@ constexpr int kInlineWords = 256;
 constexpr int kMaxExchangeRanks = 16;
 struct ExchangeParams {
   int world, rank, shard_len;
+  int protocol;                                          // 1: two 8-byte relaxed.sys scalar accesses per line (default); 0: one 16-byte volatile vector access
   int n_global, n_pad;                                   // merged population, pitch of the merged key array
   uint4* peer_lines[kMaxExchangeRanks];                  // base of rank r's block
   const uint4* lines_local;                              // this rank's own block

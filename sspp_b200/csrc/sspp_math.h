@@ -942,6 +942,7 @@ SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf, uint32_t* wc = nu
     for (int g = fl.z; g < fl.w; ++g) {
       const f4 gp = rec_f4(M.mg, g, GW_POS);                 // pos, rbound
       const i4 gi = rec_i4(M.mg, g, GW_TYPE);                // type, pair_begin, pair_mid, pair_end (<= 32 pairs)
+      if (gi.w == gi.y) continue;                            // every partner was pruned when the scene was compiled: nothing to place
       Prim P;
       P.p = add(p, mulv(R, mk(gp.x, gp.y, gp.z)));
       P.type = gi.x;

@@ -720,8 +720,7 @@ ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const 
     return sg_of[g] = D.n_sgeom++;
   };
   // Workspace bound of every moving body: its frame origin stays within reach[b] of the world point centre[b]
-  // whatever the planned coordinates are (hinges turn about their own anchor, slides move by at most their
-  // range, a free body is unbounded).  A pair whose static partner lies beyond that bound can never generate a
+  // whatever the planned coordinates are (hinges turn about their own anchor; slides and free bodies are unbounded).  A pair whose static partner lies beyond that bound can never generate a
   // contact and is dropped here, once, instead of being culled per collocation point.
   const double kInf = 1e30;
   std::vector<double> reach(D.n_mbody, kInf);
@@ -732,12 +731,9 @@ ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const 
     const double alen = std::sqrt((double)B.anchor[0] * B.anchor[0] + (double)B.anchor[1] * B.anchor[1] + (double)B.anchor[2] * B.anchor[2]);
     double own = kInf;
     if (B.jtype == JT_HINGE) own = 2.0 * alen;
-    else if (B.jtype == JT_SLIDE) {
-      int src = -1;
-      for (int b = 1; b < m.nbody; ++b) if (mb_of[b] == mb) src = b;
-      const double lo = m.jnt_range[2 * src], hi = m.jnt_range[2 * src + 1];
-      if (lo < hi) own = std::max(std::fabs(lo), std::fabs(hi));
-    }
+    // a slide joint is UNBOUNDED here even when the MJCF gives it a range: nothing on the path clamps the planned coordinate
+    // to jnt_range (the noise is unbounded, the spline may overshoot, limit_penalty is a soft cost) and the reference writes
+    // qpos as it is (sspp.h:139-142) - so a partner beyond the range is still reachable and must stay in the pair table
     if (B.parent < 0) { centre[mb] = {B.pos[0], B.pos[1], B.pos[2]}; reach[mb] = own; }
     else { centre[mb] = centre[B.parent]; reach[mb] = std::min(kInf, reach[B.parent] + plen + own); }
   }

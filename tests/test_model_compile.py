@@ -48,3 +48,22 @@ def test_pruned_pairs_never_touch_at_the_workspace_boundary():
         if (c1 != 0.0) != (c2 != 0.0) and abs(md) > 1e-4:
             bad += 1
     assert bad == 0
+
+
+def test_coordinates_outside_jnt_range_keep_their_contacts():
+    """Nothing on the path clamps the planned coordinates to jnt_range (neither does the reference: sspp.h:139-142 writes qpos
+    as sampled), so pruning must not rely on the range: hinges far outside their range and a slide pushed well beyond its
+    range still see every obstacle the FP64 oracle (all pairs) sees"""
+    from tests.helpers import armlab_case
+    rng = np.random.default_rng(8)
+    for case, scale in ((joint_case(), np.full(7, 3.0 * np.pi)), (armlab_case(), np.array([6.0, 6.0, 6.0, 6.0, 6.0, 1.5]))):
+        o1, o2 = o1_for(case), o2_for(case)
+        Q = rng.uniform(-1, 1, (1500, case.cfg.dof)) * scale             # the armlab slide (range 0.04 m) travels +-1.5 m
+        bad = hits = 0
+        for q in Q:
+            c1, ncon, md = o1.point_cost(q)
+            c2 = o2.point_cost(q)
+            hits += c1 != 0.0
+            if (c1 != 0.0) != (c2 != 0.0) and abs(md) > 1e-4:
+                bad += 1
+        assert bad == 0 and hits > 20
