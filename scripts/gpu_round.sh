@@ -18,15 +18,16 @@ timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > $OUT/${TAG}_
 cut -c1-400 $OUT/${TAG}_bench_reference_arm.json
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/${TAG}_launches.csv \
     python bench.py --steps 20 --warmup 3 --no-cpu-baseline > $OUT/${TAG}_ncu_launch.log 2>&1; echo "ncu launches rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:sspp_iterate -s 10 -c 2 -f -o $OUT/${TAG}_iterate_full \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:sspp_iterate -s 10 -c 2 -f -o /tmp/${TAG}_iterate_full \
     python bench.py --steps 20 --warmup 3 --no-cpu-baseline > $OUT/${TAG}_ncu_full.log 2>&1; echo "ncu full rc=$?"
-ncu -i $OUT/${TAG}_iterate_full.ncu-rep --page raw --csv > $OUT/${TAG}_iterate_full_raw.csv 2>/dev/null
+ncu -i /tmp/${TAG}_iterate_full.ncu-rep --page raw --csv > $OUT/${TAG}_iterate_full_raw.csv 2>/dev/null
 timeout 600 ncu --metrics smsp__sass_thread_inst_executed_op_fadd_pred_on.sum,smsp__sass_thread_inst_executed_op_fmul_pred_on.sum,smsp__sass_thread_inst_executed_op_ffma_pred_on.sum,smsp__thread_inst_executed.sum,smsp__inst_executed.sum \
     --clock-control none -k regex:sspp_iterate -s 10 -c 2 --csv --log-file $OUT/${TAG}_iterate_flops.csv \
     python bench.py --steps 20 --warmup 3 --no-cpu-baseline > $OUT/${TAG}_ncu_flops.log 2>&1; echo "ncu flops rc=$?"
 python scripts/ncu_keys_json.py cfg2 262144 $OUT/${TAG}_iterate_full_raw.csv $OUT/${TAG}_iterate_flops.csv $OUT/${TAG}_iterate_keys.json
 python scripts/ncu_keys.py $OUT/${TAG}_iterate_full_raw.csv > $OUT/${TAG}_iterate_summary.txt 2>&1
-ncu -i $OUT/${TAG}_iterate_full.ncu-rep --page source --csv --print-source sass,cuda > $OUT/${TAG}_iterate_source.csv 2>/dev/null
-python scripts/ncu_byfunc.py $OUT/${TAG}_iterate_source.csv >> $OUT/${TAG}_iterate_summary.txt 2>&1
+ncu -i /tmp/${TAG}_iterate_full.ncu-rep --page source --csv --print-source sass,cuda > /tmp/${TAG}_iterate_source.csv 2>/dev/null
+python scripts/ncu_byfunc.py /tmp/${TAG}_iterate_source.csv >> $OUT/${TAG}_iterate_summary.txt 2>&1
 python scripts/phase_times.py > $OUT/${TAG}_phase_timeline.json 2>$OUT/${TAG}_phase.err
+# the .ncu-rep and the source page (35 MB each) stay on the box: gpurun_out/ is capped at 64 MiB
 ls -la $OUT | tail -30

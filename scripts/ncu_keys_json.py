@@ -52,15 +52,21 @@ for i, h in enumerate(hdr):
 rec["stalls_per_issue"] = {h: round(v, 2) for v, h in sorted(st, reverse=True)[:6]}
 if rec["warp_inst_per_launch"] and rec["lanes_per_inst"]:
     rec["thread_inst_per_point"] = rec["warp_inst_per_launch"] * rec["lanes_per_inst"] / pts
-try:
-    h2, d2 = table(flops)
-    fa = col(h2, d2, "smsp__sass_thread_inst_executed_op_fadd_pred_on.sum")
-    fm = col(h2, d2, "smsp__sass_thread_inst_executed_op_fmul_pred_on.sum")
-    ff = col(h2, d2, "smsp__sass_thread_inst_executed_op_ffma_pred_on.sum")
+try:                                                   # the --metrics pass logs one row per (launch, metric)
+    acc = {}
+    rows = list(csv.reader(open(flops, errors="replace")))
+    i = next(k for k, r in enumerate(rows) if r and r[0] == "ID")
+    hn, hv, hi = rows[i].index("Metric Name"), rows[i].index("Metric Value"), rows[i].index("ID")
+    for r in rows[i + 1:]:
+        if len(r) > hv:
+            acc.setdefault(r[hn], {})[r[hi]] = float(r[hv].replace(",", ""))
+    mean = {k: sum(v.values()) / len(v) for k, v in acc.items()}
+    fa, fm, ff = (mean.get(f"smsp__sass_thread_inst_executed_op_{o}_pred_on.sum") for o in ("fadd", "fmul", "ffma"))
     if None not in (fa, fm, ff):
         rec.update(fadd_per_point=fa / pts, fmul_per_point=fm / pts, ffma_per_point=ff / pts, flop_per_point_ncu=(fa + fm + 2 * ff) / pts,
+                   fp32_share_of_thread_inst=(fa + fm + ff) / mean["smsp__thread_inst_executed.sum"] if "smsp__thread_inst_executed.sum" in mean else None,
                    flop_source="ncu smsp__sass_thread_inst_executed_op_{fadd,fmul,ffma}_pred_on.sum (FMA = 2), whole launch incl. ranking / update")
-except (OSError, StopIteration):
+except (OSError, StopIteration, ValueError):
     pass
 allrec = json.loads(out.read_text()) if out.exists() else {}
 allrec[wl] = rec

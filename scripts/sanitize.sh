@@ -28,5 +28,5 @@ print("sanitize target done")
 PY
 for TOOL in memcheck racecheck synccheck; do
   timeout 1500 compute-sanitizer --tool $TOOL --print-limit 20 python /tmp/sanitize_target.py > $OUT/${TAG}_sanitize_${TOOL}.log 2>&1
-  echo "$TOOL rc=$? : $(grep -E 'ERROR SUMMARY|RACECHECK SUMMARY' $OUT/${TAG}_sanitize_${TOOL}.log | tail -1)"
+  echo "$TOOL rc=$? : $(grep -E 'ERROR SUMMARY|RACECHECK SUMMARY' $OUT/${TAG}_sanitize_${TOOL}.log | tail -1)"; tail -3 $OUT/${TAG}_sanitize_${TOOL}.log | cut -c1-300
 done

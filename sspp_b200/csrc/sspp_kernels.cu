@@ -373,33 +373,40 @@ __device__ __forceinline__ float ces_weight_sum(int k, float lk, Sum sum) {
   return sum(k, [&](int j, float acc) { return acc + (lk - log_poly((float)j + 1.0f)); });
 }
 
-// K7 for one distribution element t of one query.  value_of(j): the element's value in the j-th best candidate.
+// K7 for one distribution element t of one query.  value_of(j): the element's value in the j-th best candidate;
+// weight_of(j): the CES weight (lk - ln(j + 1)) / sumw of rank j - recomputed on the fly (InlineWeight) or read from a
+// table the caller filled with exactly that expression (the same bits either way).
 // `sum` is WarpSum (one warp executes this) or CtaSum (the whole CTA does); `writer` is true in the thread that
 // stores the result.
-template <class ValueOf, class Sum>
-__device__ __forceinline__ void update_element(const ScoreConfig& c, int k, float lk, float sumw, int t, float* mean, float* sigma,
-                                               ValueOf value_of, Sum sum, bool writer) {
+struct InlineWeight {
+  float lk, sumw;
+  __device__ __forceinline__ float operator()(int j) const { return (lk - log_poly((float)j + 1.0f)) / sumw; }
+};
+template <class ValueOf, class WeightOf, class Sum>
+__device__ __forceinline__ void update_element_w(const ScoreConfig& c, int k, int t, float* mean, float* sigma,
+                                                 ValueOf value_of, WeightOf weight_of, Sum sum, bool writer) {
   const int d = t % c.D;
-  const float em = sum(k, [&](int j, float acc) {
-    const float w = (lk - log_poly((float)j + 1.0f)) / sumw;
-    return fmaf(w, value_of(j), acc);
-  });
+  const float em = sum(k, [&](int j, float acc) { return fmaf(weight_of(j), value_of(j), acc); });
   const float m0 = mean[t];
   float nm = fmaf(c.mean_lr, em - m0, m0);
   if (c.mode == MODE_TASK && d == 2) nm = fmaxf(nm, c.dist_zmin);
   nm = fminf(fmaxf(nm, c.lo[d]), c.hi[d]);
   const bool wrap = (c.mode == MODE_TASK && d == 3 && c.lo[3] != c.hi[3]);
   const float var = sum(k, [&](int j, float acc) {
-    const float w = (lk - log_poly((float)j + 1.0f)) / sumw;
     const float v = value_of(j);
     const float df = wrap ? wrap_angle_diff(v, nm, c.lo[3], c.hi[3]) : v - nm;
-    return fmaf(w, df * df, acc);
+    return fmaf(weight_of(j), df * df, acc);
   });
   const float s0 = sigma[t];
   const float blend = fmaf(c.var_beta, var, (1.0f - c.var_beta) * (s0 * s0));
   float sg = clamp_sigma(c, sqrtf(blend));
   sg = clamp_sigma(c, sg * c.dec);               // adapt(true)
   if (writer) { mean[t] = nm; sigma[t] = sg; }
+}
+template <class ValueOf, class Sum>
+__device__ __forceinline__ void update_element(const ScoreConfig& c, int k, float lk, float sumw, int t, float* mean, float* sigma,
+                                               ValueOf value_of, Sum sum, bool writer) {
+  update_element_w(c, k, t, mean, sigma, value_of, InlineWeight{lk, sumw}, sum, writer);
 }
 
 struct StoredParams {
@@ -607,6 +614,13 @@ __device__ void rank_phase(const IterParams& P, unsigned char* smem_raw, unsigne
 template <bool MIRROR>
 __device__ void update_phase(const IterParams& P, float* s_part, float* s_val, int s_val_cap, bool mirror_now) {
   const bool mirror = MIRROR && mirror_now;
+  auto ustamp = [&](int slot) {      // diagnostics: sub-phase stamps of the update (probe slots 8-11, free outside the exchange path)
+    if (P.probe && !P.xchg && threadIdx.x == 0) {
+      unsigned long long tt;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
+      P.probe[(size_t)blockIdx.x * kProbeSlots + slot] = tt;
+    }
+  };
   const ScoreConfig& c = P.cfg;
   const int tid = threadIdx.x, T = blockDim.x;
   const int nfd = c.n_free * c.D, N = c.n_cand;
@@ -618,6 +632,25 @@ __device__ void update_phase(const IterParams& P, float* s_part, float* s_val, i
     const unsigned long long* keys = P.keys + (size_t)query * P.n_pad;
     float* mean = P.mean + (size_t)query * nfd;
     float* sigma = P.sigma + (size_t)query * nfd;
+    // CES weights of the query, ONCE per CTA into shared memory: u_j = ln(k + 1/2) - ln(j + 1), their wide sum, w_j = u_j / sum -
+    // the expressions update_element evaluates on the fly, so the table holds the same bits; the two reductions below then read
+    // a weight instead of recomputing a logarithm and a division per term
+    const bool table = n_succ > 0 && 2 * k <= s_val_cap;
+    float* s_w = s_val + (table ? k : 0);              // [k] weights behind the [k] gathered values
+    float lk = 0.0f, sumw = 1.0f;
+    ustamp(8);
+    if (n_succ > 0) {
+      lk = log_poly((float)k + 0.5f);
+      if (table) {
+        __syncthreads();
+        for (int j = tid; j < k; j += T) s_w[j] = lk - log_poly((float)j + 1.0f);
+        __syncthreads();
+        sumw = CtaSum{s_part}(k, [&](int j, float acc) { return acc + s_w[j]; });
+        for (int j = tid; j < k; j += T) s_w[j] = s_w[j] / sumw;
+        __syncthreads();
+      } else sumw = ces_weight_sum(k, lk, CtaSum{s_part});
+    }
+    ustamp(9);
     if (t == nfd) {                     // scalars + elite weights of the query
       if (tid == 0) {
         P.n_success[query] = n_succ; P.n_elite[query] = k;
@@ -627,19 +660,21 @@ __device__ void update_phase(const IterParams& P, float* s_part, float* s_val, i
         }
       }
       if (n_succ > 0) {
-        const float lk = log_poly((float)k + 0.5f);
-        const float sumw = ces_weight_sum(k, lk, CtaSum{s_part});
         float* ew = P.elite_w + (size_t)query * P.n_pad;
-        for (int j = tid; j < k; j += T) ew[j] = (lk - log_poly((float)j + 1.0f)) / sumw;
+        for (int j = tid; j < k; j += T) ew[j] = table ? s_w[j] : (lk - log_poly((float)j + 1.0f)) / sumw;
       }
       continue;
     }
     if (!c.do_update) continue;
     if (n_succ == 0) { if (tid == 0) sigma[t] = clamp_sigma(c, sigma[t] * c.inc); continue; }   // adapt(false)
-    const float lk = log_poly((float)k + 0.5f);
-    const float sumw = ces_weight_sum(k, lk, CtaSum{s_part});
     StoredParams gp{P.params + (size_t)query * N * nfd, nfd, (unsigned)P.cand_offset};
-    if (k <= s_val_cap) {           // gather the element's elite values once (keys -> sampled rows: two dependent reads)
+    if (table) {                    // gather the element's elite values once (keys -> sampled rows: two dependent reads)
+      for (int j = tid; j < k; j += T) s_val[j] = gp((unsigned)(__ldcg(keys + j) & 0xFFFFFFFFu), t);
+      __syncthreads();
+      ustamp(10);
+      update_element_w(c, k, t, mean, sigma, [&](int j) { return s_val[j]; }, [&](int j) { return s_w[j]; }, CtaSum{s_part}, tid == 0);
+      ustamp(11);
+    } else if (k <= s_val_cap) {
       __syncthreads();
       for (int j = tid; j < k; j += T) s_val[j] = gp((unsigned)(__ldcg(keys + j) & 0xFFFFFFFFu), t);
       __syncthreads();
@@ -905,6 +940,7 @@ sspp_iterate_kernel(const __grid_constant__ ModelView MG, const __grid_constant_
     if (mirror) mirror_scalars(P);
     update_phase<MIRROR>(P, s_part, reinterpret_cast<float*>(smem_raw), P.smem_words, mirror);
     stamp(it, 5);
+
     if (it + 1 < P.n_inner) grid.sync();
   }
 }

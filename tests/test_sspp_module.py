@@ -114,7 +114,6 @@ def test_plan_device_buffers(sp):
     ok = d["status"] == 0
     # the collision-free candidates' rows travel with the results, compacted in candidate order; all rows only on request
     assert np.array_equal(d["success_idx"], np.flatnonzero(ok)) and np.array_equal(d["ctrl_success"], d["ctrl"][ok])
-    assert "ctrl" not in p.plan_device(Q_START, Q_END, 0.08, np.full(7, np.pi), 512, 64, 10)
     assert d["best_idx"] == int(np.flatnonzero(ok)[np.argmin(d["arc_length"][ok])])
 
     class Dev:
@@ -122,3 +121,4 @@ def test_plan_device_buffers(sp):
             self.__cuda_array_interface__ = dict(shape=shape, typestr=typestr, data=(ptr, False), version=2)
     t = torch.as_tensor(Dev(d["device_ptrs"]["arc_length"], (512,), "<f4"), device="cuda")
     np.testing.assert_array_equal(t.cpu().numpy(), d["arc_length"])          # zero-copy view of the device results
+    assert "ctrl" not in p.plan_device(Q_START, Q_END, 0.08, np.full(7, np.pi), 512, 64, 10)
