@@ -345,7 +345,7 @@ class Dist:
     def max_over_ranks(self, x: float) -> float:
         if self.world == 1:
             return x
-        t = self.torch.tensor([x], dtype=self.torch.float64, device="cuda")
+        t = self.torch.tensor([x], dtype=self.torch.float64, device=self.torch.device("cuda", self.local))
         self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
         return float(t.item())
 
@@ -492,7 +492,7 @@ def run_handle_workload(args, D: Dist, workload: str) -> dict | None:
     e2e_plan = None
     if joint and case.cfg.dof in (3, 6, 7, 9):
         from sspp_b200 import _sspp
-        planner = getattr(_sspp, f"SamplingPathPlanner{case.cfg.dof}")(str(case.mjcf))
+        planner = getattr(_sspp, f"SamplingPathPlanner{case.cfg.dof}")(str(case.mjcf), device=D.local)
         planner.set_verbose(False)
         planner.set_seed(SEED)
         st, en, lim = case.start[0], case.end[0], case.limits

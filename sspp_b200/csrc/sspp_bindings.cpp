@@ -51,7 +51,8 @@ void bind_SamplingPathPlanner(py::module& m, const std::string& class_name, cons
       .def("__call__", [](const Spline& s, double u) { return from_point<kDOF>(s(u)); }, py::arg("u"));
 
   py::class_<Planner>(m, class_name.c_str())
-      .def(py::init([](const std::string& xml_string) { return new Planner(xml_string); }), py::arg("xml_string"))
+      .def(py::init([](const std::string& xml_string, int device) { return new Planner(xml_string, device); }), py::arg("xml_string"),
+           py::arg("device") = 0)   // `device` is additive: the CUDA ordinal this planner lives on (one process per GPU)
       .def("initializePath",
            [](Planner& self, const py::object& start, const py::object& end, Spline& init_spline, int num_points) {
              return self.initializePath(to_point<kDOF>(start, "start"), to_point<kDOF>(end, "end"), init_spline, num_points);
