@@ -54,6 +54,7 @@ enum WorkCounter { WC_POINTS = 0,      // configurations scored (kinematics + co
                    WC_BROAD,           // broad-phase pair tests (one affine form each)
                    WC_NP_PLANE,        // narrow phase: any moving geom against a plane
                    WC_NP_SPHERE_BOX,
+                   WC_NP_BOX_CULL,     // second-level cull: the geom's bounding sphere against the partner BOX itself (not its sphere)
                    WC_NP_CAPS_BOX_EARLY, WC_NP_CAPS_BOX, WC_NP_CAPS_NEWTON,   // centre-distance exit / full segment-box / gradient evaluations inside it
                    WC_NP_BOX_BOX_FACE, WC_NP_BOX_BOX,     // 6 face axes only (separated beyond thr) / all 15 axes
                    WC_NP_CYL_BOX_FACE, WC_NP_CYL_BOX,
@@ -967,8 +968,15 @@ SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf, uint32_t* wc = nu
           near_mask &= near_mask - 1u;
           const i4 t4 = rec_i4(M.pair, k0 + j, PW_S);        // s, margin, thr, plane (floats as raw words)
           const float margin = word_as_float(t4.y), thr = word_as_float(t4.z);
-          if (!rotated) { place_rotation(M.mg, g, gi.x, R, &P); rotated = true; if (wc && gi.x != GT_SPHERE) ++wc[gi.x == GT_BOX ? WC_GEOM_ROT_BOX : WC_GEOM_ROT_AXIS]; }
           const Prim Q = static_prim(M.sg, t4.x);
+          if (Q.type == GT_BOX) {
+            // second-level cull before anything of the moving geom is oriented: a long thin box (a wall) has a bounding sphere
+            // that most of the workspace lies inside, so its pairs pass the sphere test at every point; the geom lies inside the
+            // sphere (P.p, rbound), hence its distance to the box is at least dist(P.p, box) - rbound
+            if (wc) ++wc[WC_NP_BOX_CULL];
+            if (point_box_sd(multv(Q.R, sub(P.p, Q.p)), Q.s) - gp.w > thr) continue;
+          }
+          if (!rotated) { place_rotation(M.mg, g, gi.x, R, &P); rotated = true; if (wc && gi.x != GT_SPHERE) ++wc[gi.x == GT_BOX ? WC_GEOM_ROT_BOX : WC_GEOM_ROT_AXIS]; }
           const float d = moving_static_sd(P, Q, thr, wc);
           const float cc = contact_cost(M.rule, d, margin, P.p, Q.p);
           if (wc && cc != 0.0f) ++wc[WC_CONTACTS];

@@ -753,6 +753,19 @@ ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const 
     const double need = r + glen + G.rbound + margin + 2e-3;      // 2 mm of slack over every FP32 rounding in the kernel
     const double dx = centre[G.body][0] - pw[0], dy = centre[G.body][1] - pw[1], dz = centre[G.body][2] - pw[2];
     if (m.geom_type[h] == GT_PLANE) return Rw[2] * dx + Rw[5] * dy + Rw[8] * dz > need;
+    if (m.geom_type[h] == GT_BOX) {
+      // exact distance from the workspace centre to the box, not to its bounding sphere: a long thin box (a wall) has a
+      // bounding sphere that swallows the whole workspace, which kept every link's pair with it alive - and sent each of
+      // them through the narrow phase's early exit at every collocation point
+      const double d3[3] = {dx, dy, dz};
+      double out2 = 0.0;
+      for (int a = 0; a < 3; ++a) {
+        const double l = Rw[a] * d3[0] + Rw[3 + a] * d3[1] + Rw[6 + a] * d3[2];          // Rw^T (centre - box centre)
+        const double e = std::max(std::fabs(l) - m.geom_size[3 * h + a], 0.0);
+        out2 += e * e;
+      }
+      return std::sqrt(out2) > need;
+    }
     const double rb = bound_radius(m.geom_type[h], &m.geom_size[3 * h]);
     return rb >= 0 && std::sqrt(dx * dx + dy * dy + dz * dz) > need + rb;
   };

@@ -101,6 +101,7 @@ EXEC_FLOP = dict(
     broad=6,                                 # one affine form: 3 FMA
     np_plane=29,                             # box against a plane (the costliest of the plane forms)
     np_sphere_box=28,
+    np_box_cull=28,                          # geom centre into the box frame + point-box distance + bound (before any orientation work)
     np_caps_box_early=29,                    # centre into the box frame + point-box distance + bound
     np_caps_box=29 + 25 + 2 * 19 + 15 + 1,   # ... + segment into the box frame, two bracket gradients, end evaluation
     np_caps_newton=23,                       # one gradient evaluation + Newton / bisection step
@@ -137,5 +138,5 @@ def executed_flop(counters: dict, *, n_cand_total: int, check_points: int, dof: 
     return dict(flop_per_point_executed=total / pts, spline=spline / pts, sampling=sampling / pts, fk=fk / pts, placement=place / pts,
                 broad_phase=terms["broad"] / pts, narrow_phase=narrow / pts, sdf=terms["sdf_samples"] / pts, penalty=penalty / pts,
                 pairs_tested_per_point=counters["broad"] / pts,
-                pairs_in_narrow_phase_per_point=sum(counters[k] for k in counters if k.startswith("np_") and k != "np_caps_newton") / pts,
+                pairs_in_narrow_phase_per_point=sum(counters[k] for k in counters if k.startswith("np_") and k not in ("np_caps_newton", "np_box_cull")) / pts,
                 contacts_per_point=counters["contacts"] / pts)
