@@ -201,7 +201,7 @@ int ssppcu_phase_probe(ssppcu_t* h, int enable, unsigned long long* stamps, int 
  * Returns the number of counters or a negative error.  (The reference has no counterpart: it cannot see inside
  * mj_forward.) */
 enum { SSPPCU_WC_POINTS = 0, SSPPCU_WC_FK_HINGE_AXIS, SSPPCU_WC_FK_HINGE_GEN, SSPPCU_WC_FK_SLIDE, SSPPCU_WC_FK_FREE4, SSPPCU_WC_FK_R0,
-       SSPPCU_WC_FK_ANCHOR, SSPPCU_WC_GEOM_POS, SSPPCU_WC_GEOM_ROT_BOX, SSPPCU_WC_GEOM_ROT_AXIS, SSPPCU_WC_BROAD, SSPPCU_WC_NP_PLANE,
+       SSPPCU_WC_FK_ANCHOR, SSPPCU_WC_GEOM_POS, SSPPCU_WC_GEOM_ROT_BOX, SSPPCU_WC_GEOM_ROT_AXIS, SSPPCU_WC_BROAD, SSPPCU_WC_BODY_BROAD, SSPPCU_WC_NP_PLANE,
        SSPPCU_WC_NP_SPHERE_BOX, SSPPCU_WC_NP_BOX_CULL, SSPPCU_WC_NP_CAPS_BOX_EARLY, SSPPCU_WC_NP_CAPS_BOX, SSPPCU_WC_NP_CAPS_NEWTON, SSPPCU_WC_NP_BOX_BOX_FACE,
        SSPPCU_WC_NP_BOX_BOX, SSPPCU_WC_NP_CYL_BOX_FACE, SSPPCU_WC_NP_CYL_BOX, SSPPCU_WC_NP_OTHER, SSPPCU_WC_CONTACTS, SSPPCU_WC_MM_TESTS,
        SSPPCU_WC_MM_NARROW, SSPPCU_WC_SDF_SAMPLES, SSPPCU_WC_COUNT };

@@ -97,7 +97,7 @@ SYMBOLS = [
     "ssppcu_bspline_knot_vector", "ssppcu_bspline_rows", "ssppcu_bspline_fit", "ssppcu_cubic_path", "ssppcu_bspline_eval_batch",
 ]
 WORK_COUNTERS = ("points", "fk_hinge_axis", "fk_hinge_gen", "fk_slide", "fk_free4", "fk_r0", "fk_anchor", "geom_pos", "geom_rot_box",
-                 "geom_rot_axis", "broad", "np_plane", "np_sphere_box", "np_box_cull", "np_caps_box_early", "np_caps_box", "np_caps_newton",
+                 "geom_rot_axis", "broad", "body_broad", "np_plane", "np_sphere_box", "np_box_cull", "np_caps_box_early", "np_caps_box", "np_caps_newton",
                  "np_box_box_face", "np_box_box", "np_cyl_box_face", "np_cyl_box", "np_other", "contacts", "mm_tests", "mm_narrow",
                  "sdf_samples")
 

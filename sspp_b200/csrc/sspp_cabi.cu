@@ -543,12 +543,12 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
     ssppm::DevPair* d_pair = nullptr; ssppm::DevMMPair* d_mm = nullptr; ssppm::DevSphere* d_sph = nullptr;
     int rt = 0;
     rt |= dalloc(h, &d_body, D.n_mbody); rt |= dalloc(h, &d_mg, D.n_mgeom); rt |= dalloc(h, &d_sg, D.n_sgeom);
-    rt |= dalloc(h, &d_pair, D.n_pair); rt |= dalloc(h, &d_mm, D.n_mmpair); rt |= dalloc(h, &d_sph, D.n_sphere);
+    rt |= dalloc(h, &d_pair, D.n_pair + D.n_bpair); rt |= dalloc(h, &d_mm, D.n_mmpair); rt |= dalloc(h, &d_sph, D.n_sphere);
     if (rt) { set_err(err, errlen, h->err); ssppcu_destroy(h); return SSPPCU_ECUDA; }
     ce = cudaMemcpy(d_body, D.body, D.n_mbody * sizeof(ssppm::DevBody), cudaMemcpyHostToDevice);
     if (ce == cudaSuccess) ce = cudaMemcpy(d_mg, D.mg, D.n_mgeom * sizeof(ssppm::DevMGeom), cudaMemcpyHostToDevice);
     if (ce == cudaSuccess) ce = cudaMemcpy(d_sg, D.sg, D.n_sgeom * sizeof(ssppm::DevSGeom), cudaMemcpyHostToDevice);
-    if (ce == cudaSuccess) ce = cudaMemcpy(d_pair, D.pair, D.n_pair * sizeof(ssppm::DevPair), cudaMemcpyHostToDevice);
+    if (ce == cudaSuccess) ce = cudaMemcpy(d_pair, D.pair, (D.n_pair + D.n_bpair) * sizeof(ssppm::DevPair), cudaMemcpyHostToDevice);
     if (ce == cudaSuccess) ce = cudaMemcpy(d_mm, D.mm, D.n_mmpair * sizeof(ssppm::DevMMPair), cudaMemcpyHostToDevice);
     if (ce == cudaSuccess) ce = cudaMemcpy(d_sph, D.sph, D.n_sphere * sizeof(ssppm::DevSphere), cudaMemcpyHostToDevice);
     if (ce != cudaSuccess) { set_err(err, errlen, std::string("cudaMemcpy (scene tables): ") + cudaGetErrorString(ce)); ssppcu_destroy(h); return SSPPCU_ECUDA; }

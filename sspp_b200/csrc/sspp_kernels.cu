@@ -147,7 +147,7 @@ __device__ __forceinline__ SmemModel stage_model(const ModelView& G, int tid, in
   } else {
     S.mg.addr = base + stage_table(G.mg, G.n_mgeom * (unsigned)sizeof(DevMGeom), at, tid, T);
     S.sg.addr = base + stage_table(G.sg, G.n_sgeom * (unsigned)sizeof(DevSGeom), at, tid, T);
-    S.pair.addr = base + stage_table(G.pair, G.n_pair * (unsigned)sizeof(DevPair), at, tid, T);
+    S.pair.addr = base + stage_table(G.pair, (G.n_pair + G.n_bpair) * (unsigned)sizeof(DevPair), at, tid, T);
     S.mm.addr = base + stage_table(G.mm, G.n_mmpair * (unsigned)sizeof(DevMMPair), at, tid, T);
   }
   return S;
@@ -1311,7 +1311,7 @@ cudaError_t launch_fma_probe(float* sink, int blocks, int threads, int iters, cu
 size_t model_smem_bytes(const ssppm::DevModelHead& M) {
   size_t b = (size_t)M.n_mbody * sizeof(DevBody);
   if (M.sdf_mode) return b + (size_t)M.n_sphere * sizeof(DevSphere);
-  return b + (size_t)M.n_mgeom * sizeof(DevMGeom) + (size_t)M.n_sgeom * sizeof(DevSGeom) + (size_t)M.n_pair * sizeof(DevPair) +
+  return b + (size_t)M.n_mgeom * sizeof(DevMGeom) + (size_t)M.n_sgeom * sizeof(DevSGeom) + (size_t)(M.n_pair + M.n_bpair) * sizeof(DevPair) +
          (size_t)M.n_mmpair * sizeof(DevMMPair);
 }
 

@@ -52,6 +52,7 @@ enum WorkCounter { WC_POINTS = 0,      // configurations scored (kinematics + co
                    WC_GEOM_POS,        // moving geoms placed (centre only)
                    WC_GEOM_ROT_BOX, WC_GEOM_ROT_AXIS,   // orientations placed on demand: full matrix / axis column only
                    WC_BROAD,           // broad-phase pair tests (one affine form each)
+                   WC_BODY_BROAD,      // body-level broad-phase tests (the same affine form, per body and static partner)
                    WC_NP_PLANE,        // narrow phase: any moving geom against a plane
                    WC_NP_SPHERE_BOX,
                    WC_NP_BOX_CULL,     // second-level cull: the geom's bounding sphere against the partner BOX itself (not its sphere)
@@ -82,6 +83,11 @@ struct alignas(16) DevBody {
   int geom_begin, geom_end;  // moving geoms attached to this body
   int sph_begin, sph_end;    // SDF mode: sphere samples attached to this body
   int pad_[2];
+  // body-level broad phase (bodies that carry several geoms): a sphere (centre in the body frame, radius) around all of the
+  // body's geoms and one affine record (DevPair form, in the pair table at [bpair_begin, bpair_end), planes first) per static
+  // partner of any of them; when the sphere is clear of every partner the body's geoms are not even placed
+  float bound[4];
+  int bpair_begin, bpair_mid, bpair_end, pad2_;
 };
 struct alignas(16) DevMGeom {
   float pos[3];     // in the body frame
@@ -122,6 +128,7 @@ struct alignas(16) DevMMPair { int a, b; float margin; int pad_; };
 // scalars of the flattened scene (kernel-parameter resident)
 struct DevModelHead {
   int n_mbody, n_mgeom, n_sgeom, n_pair, n_mmpair;
+  int n_bpair;       // body-level broad-phase records, stored behind the n_pair geom pairs in the pair table
   int rule;          // ContactRule
   int chain;         // 1: parent[b] == b-1 for every b and no moving-moving pairs (no transform store)
   float static_cost; // contribution of pairs that never move (added to every point)
@@ -148,7 +155,7 @@ struct ModelView : DevModelHead {
   const DevSphere* sph;
 };
 
-static_assert(sizeof(DevBody) == 128 && sizeof(DevMGeom) == 96 && sizeof(DevSGeom) == 80 && sizeof(DevPair) == 32 &&
+static_assert(sizeof(DevBody) == 160 && sizeof(DevMGeom) == 96 && sizeof(DevSGeom) == 80 && sizeof(DevPair) == 32 &&
               sizeof(DevSphere) == 32 && sizeof(DevMMPair) == 16, "table records are whole 16-byte words");
 
 // ----------------------------------------------------------------------------------------
@@ -223,7 +230,7 @@ SSPP_HD float word_as_float(int w) {
 // Record access.  Tables are arrays of 16-byte aligned records; rec_f4 / rec_i4(tab, i, w) read words
 // [w, w + 4) of record i (w a multiple of 4).  These overloads serve plain arrays (host container, global
 // memory); the kernels add overloads for their shared-memory staged tables.  Word offsets of the groups:
-enum { BW_POS = 0, BW_R0 = 4, BW_ANCHOR = 16, BW_JOINT = 20, BW_FLAGS = 24, BW_SPH = 28,     // DevBody
+enum { BW_POS = 0, BW_R0 = 4, BW_ANCHOR = 16, BW_JOINT = 20, BW_FLAGS = 24, BW_SPH = 28, BW_BOUND = 32, BW_BPAIR = 36,   // DevBody
        GW_POS = 0, GW_R = 4, GW_TYPE = 16, GW_BODY = 20,                                   // DevMGeom / DevSGeom
        PW_C = 0, PW_S = 4,                                                               // DevPair
        SW_C = 0, SW_MARGIN = 4 };                                                        // DevSphere
@@ -939,6 +946,27 @@ SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf, uint32_t* wc = nu
       continue;
     }
     const i4 fl = rec_i4(M.body, b, BW_FLAGS);               // has_anchor, r0_identity, geom_begin, geom_end
+    {
+      const i4 bp = rec_i4(M.body, b, BW_BPAIR);             // bpair_begin, bpair_mid, bpair_end
+      if (bp.z > bp.x) {                                     // body-level broad phase: is the whole body clear of all its partners?
+        const f4 bb = rec_f4(M.body, b, BW_BOUND);
+        const v3 bc = add(p, mulv(R, mk(bb.x, bb.y, bb.z)));
+        const float nbb = -dot(bc, bc);
+        bool near = false;
+#pragma unroll 1
+        for (int k = bp.x; k < bp.y; ++k) {
+          const f4 c4 = rec_f4(M.pair, k, PW_C);
+          near = near || !(fmaf(c4.z, bc.z, fmaf(c4.y, bc.y, fmaf(c4.x, bc.x, c4.w))) > 0.0f);
+        }
+#pragma unroll 1
+        for (int k = bp.y; k < bp.z; ++k) {
+          const f4 c4 = rec_f4(M.pair, k, PW_C);
+          near = near || !(fmaf(c4.z, bc.z, fmaf(c4.y, bc.y, fmaf(c4.x, bc.x, c4.w))) > nbb);
+        }
+        if (wc) wc[WC_BODY_BROAD] += (uint32_t)(bp.z - bp.x);
+        if (!near) continue;
+      }
+    }
 #pragma unroll 1
     for (int g = fl.z; g < fl.w; ++g) {
       const f4 gp = rec_f4(M.mg, g, GW_POS);                 // pos, rbound

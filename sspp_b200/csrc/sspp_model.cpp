@@ -862,6 +862,61 @@ ssppm::DevModel compile_model(const FlatModel& m, PlanMode mode, int dof, const 
       mgeom_src = src_out;
     }
   }
+  // Body-level broad phase.  A body that carries several geoms (a tool with its fingers, pads and couplers) gets one bounding
+  // sphere around all of them and one affine record per static partner of any of them, stored behind the geom pairs; the
+  // kernel tests those first and skips the body's geoms - their placement and their own pair tests - when the sphere is clear
+  // of every partner.  Exact: every geom lies inside the body sphere.  Not for the planned free body (it is what the planner
+  // steers among the obstacles: the test would rarely cull) and not worth it below three geoms.
+  D.n_bpair = 0;
+  for (int mb = 0; mb < D.n_mbody; ++mb) D.body[mb].bpair_begin = D.body[mb].bpair_mid = D.body[mb].bpair_end = 0;
+  if (!opt.sdf)
+    for (int mb = 0; mb < D.n_mbody; ++mb) {
+      DevBody& B = D.body[mb];
+      const int ng = B.geom_end - B.geom_begin;
+      if (ng < 3 || B.jtype == JT_FREE4) continue;
+      double cb[3] = {0, 0, 0};
+      for (int ig = B.geom_begin; ig < B.geom_end; ++ig) for (int a = 0; a < 3; ++a) cb[a] += D.mg[ig].pos[a] / ng;
+      double rb = 0.0;
+      for (int ig = B.geom_begin; ig < B.geom_end; ++ig) {
+        const DevMGeom& G = D.mg[ig];
+        const double dx = G.pos[0] - cb[0], dy = G.pos[1] - cb[1], dz = G.pos[2] - cb[2];
+        rb = std::max(rb, std::sqrt(dx * dx + dy * dy + dz * dz) + G.rbound);
+      }
+      rb *= 1.0 + 1e-6;
+      std::map<int, float> partner;                       // static geom -> largest cull threshold among this body's pairs with it
+      for (int ig = B.geom_begin; ig < B.geom_end; ++ig)
+        for (int k = D.mg[ig].pair_begin; k < D.mg[ig].pair_end; ++k) {
+          auto it = partner.find(D.pair[k].s);
+          if (it == partner.end()) partner[D.pair[k].s] = D.pair[k].thr; else it->second = std::max(it->second, D.pair[k].thr);
+        }
+      if (partner.empty() || D.n_pair + D.n_bpair + (int)partner.size() > MAX_PAIR) continue;
+      for (int a = 0; a < 3; ++a) B.bound[a] = (float)cb[a];
+      B.bound[3] = (float)rb;
+      B.bpair_begin = D.n_pair + D.n_bpair;
+      const double cen = std::sqrt(centre[mb][0] * centre[mb][0] + centre[mb][1] * centre[mb][1] + centre[mb][2] * centre[mb][2]);
+      const double blen = std::sqrt(cb[0] * cb[0] + cb[1] * cb[1] + cb[2] * cb[2]);
+      for (int pass = 0; pass < 2; ++pass) {              // planes first, as in the geom tables
+        for (const auto& kv : partner) {
+          const DevSGeom& S = D.sg[kv.first];
+          if ((S.rbound < 0.0f) != (pass == 0)) continue;
+          DevPair& pr = D.pair[D.n_pair + D.n_bpair++];
+          pr.s = kv.first; pr.margin = 0.0f; pr.thr = kv.second;
+          if (S.rbound >= 0.0f) {
+            const double rr = rb + S.rbound + pr.thr;
+            const double c2 = (double)S.pos[0] * S.pos[0] + (double)S.pos[1] * S.pos[1] + (double)S.pos[2] * S.pos[2];
+            const double pmax = reach[mb] < kInf ? cen + reach[mb] + blen : 4.0;
+            const double widen = 16.0 * 1.1920929e-7 * (pmax * pmax + c2);
+            pr.plane = 0; pr.c[0] = -2.0f * S.pos[0]; pr.c[1] = -2.0f * S.pos[1]; pr.c[2] = -2.0f * S.pos[2];
+            pr.c[3] = (float)(c2 - (rr * rr + widen));
+          } else {
+            const v3 n = mk(S.R[2], S.R[5], S.R[8]);
+            pr.plane = 1; pr.c[0] = n.x; pr.c[1] = n.y; pr.c[2] = n.z; pr.c[3] = -(dot(n, ld3(S.pos)) + (float)rb + pr.thr);
+          }
+        }
+        if (pass == 0) B.bpair_mid = D.n_pair + D.n_bpair;
+      }
+      B.bpair_end = D.n_pair + D.n_bpair;
+    }
   if (opt.sdf) {
     // The grid is the union of the static partners; it cannot express a per-geom collision mask, so every
     // sampled moving geom must see exactly the same static geoms, and nothing may collide moving-vs-moving.

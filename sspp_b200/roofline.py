@@ -99,6 +99,7 @@ EXEC_FLOP = dict(
     geom_pos=18 + 5,                         # centre + |p|^2 for the bounded partners' test
     geom_rot_box=45, geom_rot_axis=15,
     broad=6,                                 # one affine form: 3 FMA
+    body_broad=6,
     np_plane=29,                             # box against a plane (the costliest of the plane forms)
     np_sphere_box=28,
     np_box_cull=28,                          # geom centre into the box frame + point-box distance + bound (before any orientation work)
@@ -134,9 +135,9 @@ def executed_flop(counters: dict, *, n_cand_total: int, check_points: int, dof: 
     fk = sum(terms[k] for k in terms if k.startswith("fk_"))
     place = terms["geom_pos"] + terms["geom_rot_box"] + terms["geom_rot_axis"]
     narrow = sum(terms[k] for k in terms if k.startswith("np_") or k.startswith("mm_")) + terms["contacts"]
-    total = spline + sampling + penalty + fk + place + terms["broad"] + narrow + terms["sdf_samples"]
+    total = spline + sampling + penalty + fk + place + terms["broad"] + terms["body_broad"] + narrow + terms["sdf_samples"]
     return dict(flop_per_point_executed=total / pts, spline=spline / pts, sampling=sampling / pts, fk=fk / pts, placement=place / pts,
-                broad_phase=terms["broad"] / pts, narrow_phase=narrow / pts, sdf=terms["sdf_samples"] / pts, penalty=penalty / pts,
+                broad_phase=(terms["broad"] + terms["body_broad"]) / pts, narrow_phase=narrow / pts, sdf=terms["sdf_samples"] / pts, penalty=penalty / pts,
                 pairs_tested_per_point=counters["broad"] / pts,
                 pairs_in_narrow_phase_per_point=sum(counters[k] for k in counters if k.startswith("np_") and k not in ("np_caps_newton", "np_box_cull")) / pts,
                 contacts_per_point=counters["contacts"] / pts)

@@ -440,7 +440,8 @@ def test_work_counters_describe_the_scored_iteration():
     wc = h.work_counters()
     r = h.results()
     d = h.dims
-    assert wc["points"] == 512 * 65 and wc["fk_hinge_axis"] == 7 * wc["points"] and wc["broad"] == d.n_pair * wc["points"]
+    assert wc["points"] == 512 * 65 and wc["fk_hinge_axis"] == 7 * wc["points"]
+    assert 0 < wc["broad"] <= d.n_pair * wc["points"] and wc["body_broad"] > 0      # the tool body's geoms are skipped while it is clear of everything
     assert wc["np_caps_box"] <= wc["np_caps_box_early"] + wc["np_caps_box"] <= wc["broad"]
     assert wc["contacts"] == int(round(float(r["Cnf"].sum())))              # planner A: every contact adds exactly 1 (sspp.h:144)
     # the same counters from the replica oracle's host build of the same header
