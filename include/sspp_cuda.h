@@ -149,6 +149,20 @@ int ssppcu_cubic_path(const double* start, const double* via, const double* end,
 int ssppcu_bspline_eval_batch(int device, const float* rows, int n_theta, int n_ctrl, const float* ctrl, int n_curves, int d, float* out,
                               char* err, size_t errlen);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, same arithmetic and
+ * bit-identical output as ssppcu_bspline_eval_batch, but this entry point allocates nothing: no cudaMalloc, cudaFree or
+ * allocating library routine.  The device staging (rows | control points | output, each region rounded up to 64 floats)
+ * lives in a file-scope `static __device__` array of SSPPCU_NOALLOC_MAX_FLOATS floats (4 MiB) that every GPU loading the
+ * library holds until the process exits.  A call needing more returns SSPPCU_ELIMIT with the figures in `err` before any
+ * CUDA call is made (also: n_theta * n_ctrl * 4 bytes <= 200 KiB, the kernel's shared-memory row table).  Host pointers;
+ * synchronous.  All calls on a device share the array, which keeps the previous call's contents (nothing in it has to
+ * start at zero: inputs are overwritten, every output element is stored before the read-back); calls overlapping on
+ * the same GPU would race on it - inside one process a per-device mutex serialises them. */
+#define SSPPCU_NOALLOC_MAX_FLOATS (1 << 20)
+int ssppcu_bspline_eval_batch_noalloc(int device, const float* rows, int n_theta, int n_ctrl, const float* ctrl, int n_curves, int d,
+                                      float* out, char* err, size_t errlen);
+
 /* ---- planner handle ---- */
 void ssppcu_default_config(int mode, SsppPlannerConfig* cfg);
 int ssppcu_create(const ssppcu_model_t* m, const SsppPlannerConfig* cfg, ssppcu_t** out, char* err, size_t errlen);

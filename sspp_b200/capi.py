@@ -95,6 +95,7 @@ SYMBOLS = [
     "ssppcu_exchange_status", "ssppcu_sdf_gradient", "ssppcu_set_result_mirror", "ssppcu_work_counters",
     "ssppcu_plan_step", "ssppcu_set_success_rows", "ssppcu_get_success_rows", "ssppcu_candidate_ctrl",
     "ssppcu_bspline_knot_vector", "ssppcu_bspline_rows", "ssppcu_bspline_fit", "ssppcu_cubic_path", "ssppcu_bspline_eval_batch",
+    "ssppcu_bspline_eval_batch_noalloc",
 ]
 WORK_COUNTERS = ("points", "fk_hinge_axis", "fk_hinge_gen", "fk_slide", "fk_free4", "fk_r0", "fk_anchor", "geom_pos", "geom_rot_box",
                  "geom_rot_axis", "broad", "body_broad", "np_plane", "np_sphere_box", "np_box_cull", "np_caps_box_early", "np_caps_box", "np_caps_newton",

@@ -194,6 +194,33 @@ int ssppcu_bspline_eval_batch(int device, const float* rows, int n_theta, int n_
   return SSPPCU_OK;
 }
 
+// No counterpart in the reference.  ssppcu_bspline_eval_batch without any
+// allocation: the device staging is the file-scope 4 MiB array of sspp_kernels.cu (sspp::bspline_eval_static).  No
+// cudaMalloc / cudaFree / allocating library call on this path; sizes beyond the array are refused before any CUDA call.
+static_assert(SSPPCU_NOALLOC_MAX_FLOATS == sspp::kStaticScratchFloats, "include/sspp_cuda.h and sspp_kernels.h disagree on the static scratch size");
+int ssppcu_bspline_eval_batch_noalloc(int device, const float* rows, int n_theta, int n_ctrl, const float* ctrl, int n_curves, int d, float* out,
+                                      char* err, size_t errlen) {
+  if (!rows || !ctrl || !out || n_theta < 1 || n_ctrl < 1 || n_curves < 1 || d < 1) { set_err(err, errlen, "bad arguments"); return SSPPCU_EINVAL; }
+  const size_t need = sspp::static_scratch_floats_needed(n_theta, n_ctrl, n_curves, d);
+  if (need > (size_t)SSPPCU_NOALLOC_MAX_FLOATS) {
+    set_err(err, errlen, "ssppcu_bspline_eval_batch_noalloc: rows + control points + output need " + std::to_string(need) +
+                             " floats (each region rounded up to 64), the static device scratch holds " +
+                             std::to_string(SSPPCU_NOALLOC_MAX_FLOATS) + " (4 MiB); use ssppcu_bspline_eval_batch or split the batch");
+    return SSPPCU_ELIMIT;
+  }
+  if ((size_t)n_theta * n_ctrl * sizeof(float) > 200 * 1024) {
+    set_err(err, errlen, "ssppcu_bspline_eval_batch_noalloc: the row table n_theta x n_ctrl exceeds 200 KiB of shared memory");
+    return SSPPCU_ELIMIT;
+  }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) { set_err(err, errlen, "no CUDA device (this library has no CPU path)"); return SSPPCU_ECUDA; }
+  if (device < 0 || device >= ndev) { set_err(err, errlen, "device ordinal out of range"); return SSPPCU_EINVAL; }
+  e = sspp::bspline_eval_static(device, rows, n_theta, n_ctrl, ctrl, n_curves, d, out);
+  if (e != cudaSuccess) { set_err(err, errlen, std::string("ssppcu_bspline_eval_batch_noalloc: ") + cudaGetErrorString(e)); return SSPPCU_ECUDA; }
+  return SSPPCU_OK;
+}
+
 int ssppcu_model_load(const char* path, ssppcu_model_t** out, char* err, size_t errlen) {
   if (!path || !out) { set_err(err, errlen, "null argument"); return SSPPCU_EINVAL; }
   try { auto* m = new ssppcu_model; m->m = load_mjcf(path); *out = m; return SSPPCU_OK; }

@@ -28,6 +28,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <mutex>
 
 namespace cg = cooperative_groups;
 
@@ -1436,6 +1437,69 @@ cudaError_t launch_merge_update(const MergeParams& P, cudaStream_t stream) {
   if (e != cudaSuccess) return e;
   sspp_merge_finish_kernel<<<nfd + 1, 256, 0, stream>>>(P);
   return cudaGetLastError();
+}
+
+}  // namespace sspp
+
+// ------------------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of the batched B-spline evaluation (ssppcu_bspline_eval_batch_noalloc).  No counterpart in the
+// reference; added for callers that cannot call cudaMalloc (CUDA graph capture,
+// tight serving loops, harnesses that forbid it).  The device staging that ssppcu_bspline_eval_batch cudaMallocs per
+// call (rows | control points | output) lives in this file-scope array instead: kStaticScratchFloats * 4 = 4 MiB, held by
+// every GPU that loads the library until the process exits.
+//   * In HOST code `g_static_scratch` is only a stand-in for the symbol, not a device address: the address is looked
+//     up once per device, with that device current, by cudaGetSymbolAddress and cached in g_static_ptr[].
+//   * Every call on a device shares the one array and finds the previous call's contents in it.  Nothing has to start
+//     at zero: the two input regions are overwritten by the copies and the kernel stores every output element before
+//     the read-back.  Calls that overlap on the same GPU would race on it; inside one process a per-device mutex
+//     serialises them (the call is synchronous), across processes each has its own copy of the array.
+// ------------------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_static_scratch[sspp::kStaticScratchFloats];
+
+namespace sspp {
+namespace {
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mu[kStaticMaxDevices];
+float* g_static_ptr[kStaticMaxDevices];          // device address of g_static_scratch on device i; nullptr = not looked up yet
+int g_static_sms[kStaticMaxDevices];
+}  // namespace
+
+size_t static_scratch_floats_needed(int T, int n, int B, int d) {
+  auto up = [](size_t x) { return (x + 63) / 64 * 64; };                    // every region starts on a 256-byte boundary
+  return up((size_t)T * n) + up((size_t)B * n * d) + up((size_t)B * T * d);
+}
+
+cudaError_t bspline_eval_static(int device, const float* h_rows, int T, int n, const float* h_ctrl, int B, int d, float* h_out) {
+  if (device < 0 || device >= kStaticMaxDevices) return cudaErrorInvalidDevice;
+  if (static_scratch_floats_needed(T, n, B, d) > (size_t)kStaticScratchFloats) return cudaErrorInvalidValue;
+  int prev = -1;
+  cudaError_t e = cudaGetDevice(&prev);
+  if (e != cudaSuccess) return e;
+  e = cudaSetDevice(device);
+  if (e != cudaSuccess) return e;
+  {
+    std::lock_guard<std::mutex> lock(g_static_mu[device]);
+    if (!g_static_ptr[device]) {                                             // set-up, once per device, that device current
+      float* p = nullptr;
+      e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_static_scratch);
+      if (e == cudaSuccess && !p) e = cudaErrorInvalidSymbol;
+      if (e == cudaSuccess) e = cudaDeviceGetAttribute(&g_static_sms[device], cudaDevAttrMultiProcessorCount, device);
+      if (e == cudaSuccess) g_static_ptr[device] = p;
+    }
+    if (e == cudaSuccess) {
+      auto up = [](size_t x) { return (x + 63) / 64 * 64; };
+      const size_t nr = (size_t)T * n, nc = (size_t)B * n * d, no = (size_t)B * T * d;
+      float* d_rows = g_static_ptr[device];
+      float* d_ctrl = d_rows + up(nr);
+      float* d_out = d_ctrl + up(nc);
+      e = cudaMemcpy(d_rows, h_rows, nr * sizeof(float), cudaMemcpyHostToDevice);
+      if (e == cudaSuccess) e = cudaMemcpy(d_ctrl, h_ctrl, nc * sizeof(float), cudaMemcpyHostToDevice);
+      if (e == cudaSuccess) e = launch_bspline_eval(d_rows, T, n, d_ctrl, B, d, d_out, g_static_sms[device], 0);
+      if (e == cudaSuccess) e = cudaMemcpy(h_out, d_out, no * sizeof(float), cudaMemcpyDeviceToHost);
+    }
+  }
+  if (prev >= 0 && prev != device) cudaSetDevice(prev);
+  return e;
 }
 
 }  // namespace sspp

@@ -60,6 +60,7 @@ struct IterParams {
   float inline_blk[256];
 };
 constexpr int kInlineWords = 256;
+constexpr int kStaticScratchFloats = 1 << 20;   // file-scope device scratch of the allocation-free entry point: 4 MiB per GPU
 
 // Fused key exchange of the population-sharded path (sort_only handles, cooperative kernel).  Every rank owns an
 // exchange block of 16-byte lines [2 halves][world][shard_len] that its peers map (CUDA IPC across processes, plain
@@ -135,6 +136,11 @@ cudaError_t launch_sdf_gradient(const ssppm::ModelView& M, int D, int K, int row
 
 // batched B-spline evaluation out[B][T][d] = rows[T][n] . ctrl[B][n][d] (device pointers)
 cudaError_t launch_bspline_eval(const float* rows, int T, int n, const float* ctrl, int B, int d, float* out, int n_sm, cudaStream_t stream);
+
+// the same evaluation with HOST pointers and no allocation: staging in the file-scope device array of sspp_kernels.cu
+// (kStaticScratchFloats); cudaErrorInvalidValue when static_scratch_floats_needed() exceeds it.  Synchronous.
+size_t static_scratch_floats_needed(int T, int n, int B, int d);
+cudaError_t bspline_eval_static(int device, const float* h_rows, int T, int n, const float* h_ctrl, int B, int d, float* h_out);
 
 // sampled rows of the converged candidates, compacted in candidate order: rows [Q][N][nfd], idx [Q][N], count [Q] (device-visible
 // addresses, normally mapped pinned host memory)

@@ -102,6 +102,25 @@ def bspline_batch(theta, t, c_batch, k: int, derivative: bool = False, device: i
     return out
 
 
+def bspline_batch_noalloc(theta, t, c_batch, k: int, derivative: bool = False, device: int = 0) -> np.ndarray:
+    """bspline_batch through ssppcu_bspline_eval_batch_noalloc: same output bit for bit, no device allocation (the staging is
+    a 4 MiB file-scope device array; larger batches raise SsppError with code ELIMIT).  No counterpart in the reference."""
+    cb = np.ascontiguousarray(c_batch, np.float32)
+    if cb.ndim != 3:
+        raise ValueError("c_batch must be [n_curves][n][d]")
+    n = len(t) - k - 1
+    rows = np.ascontiguousarray(_rows(theta, t, k, 3 if derivative else 2), np.float32)
+    cb = np.ascontiguousarray(cb[:, :n])
+    out = np.zeros((cb.shape[0], rows.shape[0], cb.shape[2]), np.float32)
+    err = C.create_string_buffer(512)
+    f = C.POINTER(C.c_float)
+    rc = _lib.ssppcu_bspline_eval_batch_noalloc(device, rows.ctypes.data_as(f), rows.shape[0], n, cb.ctypes.data_as(f), cb.shape[0],
+                                                cb.shape[2], out.ctypes.data_as(f), err, len(err))
+    if rc != capi.OK:
+        raise capi.SsppError(rc, err.value.decode())
+    return out
+
+
 class CubicPath:
     """closed-form cubic through start, via (at u = 1/2) and end with zero start velocity (CubicPath.py:8-60)"""
 
