@@ -468,9 +468,15 @@ def run_handle_workload(args, D: Dist, workload: str) -> dict | None:
     res, best = h.results(), h.best()                # caller-owned host buffers, refilled by every step
     sig = case.joint_sigma if joint else case.sigma0
 
+    # caller-owned host input buffers; their addresses are taken once, as a C caller keeps its pointers (every call reads their
+    # current contents: nothing about the inputs is cached on the device or in the library between steps)
+    in_start = np.ascontiguousarray(case.start, np.float64); in_end = np.ascontiguousarray(case.end, np.float64)
+    in_lim = np.ascontiguousarray(case.limits, np.float64) if joint else None
+    bound_step = h.bind_plan_step(in_start, in_end, in_lim)
+
     def e2e_step(i: int):
         nonlocal res, best
-        h.plan_step(case.start, case.end, sig, case.limits if joint else None, SEED, i * inner, inner)   # host start/end (+ noise scale) in
+        bound_step(sig, SEED, i * inner, inner)      # host start/end (+ noise scale) in
         res = h.results(res)                         # L, Cnf, Cwf, cost, status per candidate + per-query scalars out
         best = h.best(best)
     for i in range(max(args.warmup, 3)):             # untimed: the mirroring instantiation of the kernel is loaded by its first launch

@@ -136,6 +136,7 @@ lib.ssppcu_sync.argtypes = [C.c_void_p]
 lib.ssppcu_get_results.argtypes = [C.c_void_p] + [C.c_void_p] * 10
 lib.ssppcu_get_params.argtypes = [C.c_void_p, C.c_void_p]
 lib.ssppcu_get_best.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+lib.ssppcu_plan_step.argtypes = [C.c_void_p, _dp, _dp, C.c_double, _dp, C.c_uint64, C.c_uint32, C.c_int]
 lib.ssppcu_get_elites.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
 lib.ssppcu_device_view.argtypes = [C.c_void_p, C.POINTER(DeviceView)]
 lib.ssppcu_eval_points.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
@@ -300,6 +301,11 @@ class _Results(dict):
     ptrs: list
 
 
+class _Best(tuple):
+    """the (best, best_valid) pair Handle.best returns; keeps the ctypes pointers of its arrays like _Results"""
+    ptrs: tuple
+
+
 class Handle:
     """One ssppcu_t: a scene specialised for one planner shape, resident on one GPU."""
 
@@ -367,8 +373,22 @@ class Handle:
         """set_queries + set_joint_noise / reset_distribution + iterate in one call and one launch (ssppcu_plan_step)"""
         s = np.ascontiguousarray(start, np.float64); e = np.ascontiguousarray(end, np.float64)
         lim = None if limits is None else np.ascontiguousarray(limits, np.float64)
-        lib.ssppcu_plan_step.argtypes = [C.c_void_p, _dp, _dp, C.c_double, _dp, C.c_uint64, C.c_uint32, C.c_int]
         self._ck(lib.ssppcu_plan_step(self._h, _dptr(s), _dptr(e), float(sigma), None if lim is None else _dptr(lim), seed, iter0, n_iters))
+
+    def bind_plan_step(self, start, end, limits=None):
+        """plan_step over caller-owned host buffers whose addresses are taken ONCE, the way a C caller keeps its pointers (the
+        ndarray -> ctypes pointer conversion costs microseconds per argument in Python).  start / end / limits must be C-contiguous
+        float64 arrays; the returned callable (sigma, seed, iter0, n_iters) reads their CURRENT contents on every call."""
+        for a in (start, end) + (() if limits is None else (limits,)):
+            if not (isinstance(a, np.ndarray) and a.dtype == np.float64 and a.flags.c_contiguous):
+                raise ValueError("bind_plan_step needs C-contiguous float64 ndarrays")
+        ps, pe, pl = _dptr(start), _dptr(end), (None if limits is None else _dptr(limits))
+        keep = (start, end, limits)
+        fn, hh, ck = lib.ssppcu_plan_step, self._h, self._ck
+
+        def step(sigma: float, seed: int = 0, iter0: int = 0, n_iters: int = 1, _keep=keep):
+            ck(fn(hh, ps, pe, sigma, pl, seed, iter0, n_iters))
+        return step
 
     def set_success_rows(self, on: bool):
         lib.ssppcu_set_success_rows.argtypes = [C.c_void_p, C.c_int]
@@ -465,7 +485,10 @@ class Handle:
         if out is None:
             d = self.dims
             out = (np.zeros((d.n_queries, d.n_free, d.dof), np.float32), np.zeros(d.n_queries, np.int32))
-        self._ck(lib.ssppcu_get_best(self._h, _ptr(out[0]), _ptr(out[1])))
+        if not isinstance(out, _Best):
+            out = _Best(out)
+            out.ptrs = (_ptr(out[0]), _ptr(out[1]))
+        self._ck(lib.ssppcu_get_best(self._h, *out.ptrs))
         return out
 
     def elites(self, query: int = 0, cap: int | None = None):

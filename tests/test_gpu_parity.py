@@ -460,3 +460,29 @@ def test_work_counters_describe_the_scored_iteration():
     nom = roofline.work_model(case.model, 0, 7, 10)
     assert 500 < ex["flop_per_point_executed"] < nom["flop_per_point"]
     h.close()
+
+
+def test_bound_plan_step_reads_the_callers_buffers_every_call():
+    """Handle.bind_plan_step (addresses of the caller's host arrays taken once, like a C caller's pointers) == plan_step, and an
+    in-place edit of a bound array changes the next call's result the way passing the edited array would"""
+    from sspp_b200 import capi
+    case = joint_case(n_samples=500, check_points=32, do_update=True)
+    a = capi.Handle(case.model, case.cfg); b = capi.Handle(case.model, case.cfg)
+    start = np.ascontiguousarray(case.start, np.float64).copy(); end = np.ascontiguousarray(case.end, np.float64).copy()
+    lim = np.ascontiguousarray(case.limits, np.float64).copy()
+    step = b.bind_plan_step(start, end, lim)
+    best = None
+    for rep in range(3):
+        if rep == 2:
+            start[...] += 0.01; end[...] -= 0.02                       # in place: the bound addresses stay valid
+        a.plan_step(start.copy(), end.copy(), case.joint_sigma, lim.copy(), SEED, 5 * rep, 2)
+        step(case.joint_sigma, SEED, 5 * rep, 2)
+        ra, rb = a.results(), b.results()
+        for k in ("L", "Cnf", "Cwf", "cost"):
+            assert np.array_equal(ra[k].view(np.uint32), rb[k].view(np.uint32)), k
+        assert np.array_equal(ra["status"], rb["status"]) and np.array_equal(a.base(), b.base())
+        best = b.best(best)                                              # refilled in place through its cached pointers
+        for x, y in zip(a.best(), best):
+            assert np.array_equal(x, y)
+    with pytest.raises(ValueError):
+        b.bind_plan_step(np.zeros((1, 7), np.float32), end, lim)
