@@ -254,6 +254,13 @@ int ssppcu_device_view(ssppcu_t* h, SsppDeviceView* out);
 /* Score explicit spline points: pts [n][dof] host floats -> collision cost per point (the
  * contact rule of the handle's mode).  The unit check of FK + narrow phase. */
 int ssppcu_eval_points(ssppcu_t* h, const float* pts, int n, float* cost_out);
+/* include/Collision.h:51-82 check_collision_point, batched: for each of n configurations (pts [n][dof], float) the contact that
+ * penetrates by more than 1 mm (contact dist < -1e-3, the reference's test) with the smallest geom pair: geom1[i] < geom2[i] are
+ * model geom ids (names: ssppcu_model_geom_name), dist[i] its signed distance; geom1[i] = geom2[i] = -1 and dist[i] = 0 when the
+ * configuration is free of such contacts (the reference returns false).  The reference walks mjData::contact and reports the first
+ * hit; MuJoCo orders contacts by geom pair, which the smallest-pair rule restates.  dist may be NULL.  Returns the number of
+ * colliding configurations or a negative error.  Primitives collision mode only.  Diagnostic: the planner loop does not use it. */
+int ssppcu_check_points(ssppcu_t* h, const float* pts, int n, int32_t* geom1, int32_t* geom2, float* dist);
 
 /* SDF mode: the baked node grid [nz][ny][nx] (host copy) and its geometry; nodes may be NULL to query sizes */
 int ssppcu_get_sdf(ssppcu_t* h, float* nodes, int32_t dims[3], double lo[3], double cell[3]);

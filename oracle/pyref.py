@@ -67,6 +67,7 @@ def lib() -> C.CDLL:
         L.ref_floor_penalty.argtypes = [C.c_double, C.c_double, C.c_double, _dp]
         L.ref_from_vias.argtypes = [_dp, _dp, C.c_int, _dp, C.c_int, _dp, _dp, _dp, _dp]
         L.ref_point_costs.argtypes = [C.c_void_p, C.c_char_p, _dp, C.c_int, C.c_int, _dp]
+        L.ref_check_points.argtypes = [C.c_void_p, C.c_char_p, _dp, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, _dp]
         L.ref_tsp_create.restype = C.c_void_p
         L.ref_tsp_create.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(TspArgs)]
         L.ref_tsp_destroy.argtypes = [C.c_void_p]
@@ -129,6 +130,17 @@ class RefModel:
         out = np.zeros(len(pts))
         lib().ref_point_costs(self.h, body.encode(), _d(pts), len(pts), int(use_center), _d(out))
         return out
+
+
+    def check_points(self, body: str, pts):
+        """Collision<Point>::check_collision_point (Collision.h:51-82) at task-space points [n][4] -> (hit, geom1, geom2, dist):
+        the function's return value and the ids / distance it prints for the first penetrating contact"""
+        pts = np.ascontiguousarray(pts, np.float64).reshape(-1, 4)
+        n = len(pts)
+        hit = np.zeros(n, np.int32); g1 = np.zeros(n, np.int32); g2 = np.zeros(n, np.int32); dist = np.zeros(n)
+        v = C.c_void_p
+        lib().ref_check_points(self.h, body.encode(), _d(pts), n, hit.ctypes.data_as(v), g1.ctypes.data_as(v), g2.ctypes.data_as(v), _d(dist))
+        return hit.astype(bool), g1, g2, dist
 
 
 # ---- CES pieces (tsp_elites.h, tsp_distribution.h, tsp_sampler.h, tsp_evaluator.h, tsp_path_model.h) ----

@@ -22,6 +22,9 @@
 
 #include <map>
 #include <memory>
+#include <sstream>
+#include <iostream>
+#include <cstring>
 
 #include "mujoco/mujoco.h"
 #include "sspp.h"
@@ -284,6 +287,25 @@ void ref_from_vias(const double* start, const double* end, int total_points, con
 void ref_point_costs(void* model, const char* body, const double* pts, int n, int use_center, double* cost_out) {
   Collision<tsp::Point> col(body, static_cast<mjModel*>(model));
   for (int i = 0; i < n; ++i) cost_out[i] = col.collision_point_cost(P4(pts + 4 * i), use_center != 0);
+}
+
+// Collision<Point>::check_collision_point (Collision.h:51-82) at n task-space points.  The function reports through std::cout;
+// its text is captured and parsed: hit[i] = its return value, g1 / g2 / dist = the ids and distance it printed.
+void ref_check_points(void* model, const char* body, const double* pts, int n, int32_t* hit, int32_t* g1, int32_t* g2, double* dist) {
+  Collision<tsp::Point> col(body, static_cast<mjModel*>(model));
+  for (int i = 0; i < n; ++i) {
+    std::ostringstream cap;
+    std::streambuf* old = std::cout.rdbuf(cap.rdbuf());
+    const bool h = col.check_collision_point(P4(pts + 4 * i));
+    std::cout.rdbuf(old);
+    hit[i] = h ? 1 : 0; g1[i] = g2[i] = -1; dist[i] = 0.0;
+    if (!h) continue;
+    const std::string t = cap.str();
+    auto after = [&](const char* key) { const size_t p = t.find(key); return p == std::string::npos ? std::string() : t.substr(p + std::strlen(key)); };
+    dist[i] = std::atof(after("(col_dist): ").c_str());
+    g1[i] = std::atoi(after("Geom 1 ID: ").c_str());
+    g2[i] = std::atoi(after("Geom 2 ID: ").c_str());
+  }
 }
 
 // ---- Planner B whole: tsp::TaskSpacePlanner (tsp.h adapter over tsp_planner.h) ----

@@ -95,7 +95,7 @@ SYMBOLS = [
     "ssppcu_exchange_status", "ssppcu_sdf_gradient", "ssppcu_set_result_mirror", "ssppcu_work_counters",
     "ssppcu_plan_step", "ssppcu_set_success_rows", "ssppcu_get_success_rows", "ssppcu_candidate_ctrl",
     "ssppcu_bspline_knot_vector", "ssppcu_bspline_rows", "ssppcu_bspline_fit", "ssppcu_cubic_path", "ssppcu_bspline_eval_batch",
-    "ssppcu_bspline_eval_batch_noalloc",
+    "ssppcu_bspline_eval_batch_noalloc", "ssppcu_check_points",
 ]
 WORK_COUNTERS = ("points", "fk_hinge_axis", "fk_hinge_gen", "fk_slide", "fk_free4", "fk_r0", "fk_anchor", "geom_pos", "geom_rot_box",
                  "geom_rot_axis", "broad", "body_broad", "np_plane", "np_sphere_box", "np_box_cull", "np_caps_box_early", "np_caps_box", "np_caps_newton",
@@ -490,6 +490,15 @@ class Handle:
             out.ptrs = (_ptr(out[0]), _ptr(out[1]))
         self._ck(lib.ssppcu_get_best(self._h, *out.ptrs))
         return out
+
+    def check_points(self, pts):
+        """Collision.h:51-82 for a batch of configurations: (geom1, geom2, dist) per point, geom ids of the penetrating contact
+        with the smallest geom pair, -1 / -1 / 0 when free"""
+        p = np.ascontiguousarray(pts, np.float32).reshape(-1, self.dims.dof)
+        g1 = np.zeros(len(p), np.int32); g2 = np.zeros(len(p), np.int32); dist = np.zeros(len(p), np.float32)
+        lib.ssppcu_check_points.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        self._ck(lib.ssppcu_check_points(self._h, _ptr(p), len(p), _ptr(g1), _ptr(g2), _ptr(dist)))
+        return g1, g2, dist
 
     def elites(self, query: int = 0, cap: int | None = None):
         cap = self.dims.n_cand if cap is None else cap

@@ -43,6 +43,8 @@ struct ssppcu_planner {
   std::vector<float> psi_col, psi_arc, base_host;
   std::vector<void*> allocs;
   float* d_eval_pts = nullptr; float* d_eval_out = nullptr; int eval_cap = 0;
+  std::vector<int> mgeom_src, sgeom_src;   // FlatModel geom ids behind dev.mg / dev.sg (ssppcu_check_points)
+  int* d_geom_src = nullptr;               // the two maps on the device, uploaded by the first ssppcu_check_points
   unsigned long long* d_merge_keys = nullptr; int merge_cap = 0, merged_n = 0;
   float* d_live = nullptr;       // mean | sigma | best | best_valid | any_success (ints), one block
   float* d_state = nullptr;      // snapshot of d_live
@@ -355,7 +357,9 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
     opt.sdf = c.collision_mode == SSPPCU_COLLIDE_SDF;
     opt.sphere_ratio = c.sdf_sphere_ratio > 0 ? c.sdf_sphere_ratio : 0.5;
     opt.use_center_dist = c.use_center_dist != 0;
-    h->dev = compile_model(mm->m, task ? PLAN_TASK : PLAN_JOINT, c.dof, h->body_name, nullptr, opt);
+    CompileInfo info;
+    h->dev = compile_model(mm->m, task ? PLAN_TASK : PLAN_JOINT, c.dof, h->body_name, &info, opt);
+    h->mgeom_src = info.mgeom_src; h->sgeom_src = info.sgeom_src;
     h->spl = make_setup(c.n_points, c.degree);
   } catch (const std::exception& e) { set_err(err, errlen, e.what()); delete h; return SSPPCU_EMODEL; }
   if (c.collision_mode != SSPPCU_COLLIDE_PRIMITIVES && c.collision_mode != SSPPCU_COLLIDE_SDF) { set_err(err, errlen, "unknown collision_mode"); delete h; return SSPPCU_EINVAL; }
@@ -1068,6 +1072,39 @@ int ssppcu_eval_points(ssppcu_t* h, const float* pts, int n, float* out) {
   CU(h, cudaMemcpyAsync(out, h->d_eval_out, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
   CU(h, cudaStreamSynchronize(h->stream));
   return SSPPCU_OK;
+}
+
+int ssppcu_check_points(ssppcu_t* h, const float* pts, int n, int32_t* geom1, int32_t* geom2, float* dist) {
+  if (int rc = check(h)) return rc;
+  if (!pts || !geom1 || !geom2 || n < 0) return fail(h, SSPPCU_EINVAL, "bad arguments");
+  if (h->dev.sdf_mode) return fail(h, SSPPCU_EINVAL, "ssppcu_check_points needs the primitives collision mode (an SDF scene has no geom pairs)");
+  if (n == 0) return 0;
+  const int D = h->P.cfg.D;
+  const size_t nm = h->mgeom_src.size(), ns = h->sgeom_src.size();
+  if (!h->d_geom_src) {
+    std::vector<int> both(h->mgeom_src);
+    both.insert(both.end(), h->sgeom_src.begin(), h->sgeom_src.end());
+    if (int rc = dalloc(h, &h->d_geom_src, both.size())) return rc;
+    CU(h, cudaMemcpy(h->d_geom_src, both.data(), both.size() * sizeof(int), cudaMemcpyHostToDevice));
+  }
+  (void)ns;
+  float* d_pts = nullptr;
+  cudaError_t e = cudaMalloc(&d_pts, ((size_t)n * D + 3 * (size_t)n) * sizeof(float));
+  if (e != cudaSuccess) return cuda_fail(h, e, "cudaMalloc");
+  int* d_g1 = reinterpret_cast<int*>(d_pts + (size_t)n * D); int* d_g2 = d_g1 + n; float* d_dist = reinterpret_cast<float*>(d_g2 + n);
+  std::vector<float> hd((size_t)n);
+  e = cudaMemcpyAsync(d_pts, pts, (size_t)n * D * sizeof(float), cudaMemcpyHostToDevice, h->stream);
+  if (e == cudaSuccess) e = launch_check_points(h->view, D, d_pts, n, h->d_geom_src, h->d_geom_src + nm, d_g1, d_g2, d_dist, h->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(geom1, d_g1, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, h->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(geom2, d_g2, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, h->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(hd.data(), d_dist, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, h->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+  cudaFree(d_pts);
+  if (e != cudaSuccess) return cuda_fail(h, e, "ssppcu_check_points");
+  if (dist) std::copy(hd.begin(), hd.end(), dist);
+  int hits = 0;
+  for (int i = 0; i < n; ++i) hits += geom1[i] >= 0;
+  return hits;
 }
 
 int ssppcu_sdf_gradient(ssppcu_t* h, const float* pts, const float* weights, int rows, float* grad, float* dist, float* dirs) {

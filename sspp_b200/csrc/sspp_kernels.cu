@@ -1104,6 +1104,29 @@ sspp_eval_points_kernel(const __grid_constant__ ModelView M, int D, const float*
   out[i] = point_collision_cost(M, qa, xf);
 }
 
+// Collision.h:51-82 check_collision_point for n configurations: per point the penetrating contact (dist < -1e-3) with the
+// smallest geom pair, as FlatModel geom ids, and its distance; geom1 = -1 when the configuration is free.  Diagnostic path
+// (the planner loop never calls it): scene tables read from global memory, primitives mode only.
+__global__ void __launch_bounds__(128)
+sspp_check_points_kernel(const __grid_constant__ ModelView M, int D, const float* __restrict__ pts, int n, const int* __restrict__ mg_src,
+                         const int* __restrict__ sg_src, int* __restrict__ geom1, int* __restrict__ geom2, float* __restrict__ dist) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float* s_qs = reinterpret_cast<float*>(smem_raw);
+  float* s_xf = s_qs + D * blockDim.x;
+  const int tid = threadIdx.x, T = blockDim.x;
+  const int i = blockIdx.x * T + tid;
+  if (i >= n) return;
+  for (int d = 0; d < D; ++d) s_qs[d * T + tid] = pts[(size_t)i * D + d];
+  SmemXF xf{s_xf, T, tid};
+  SmemQ qa{s_qs, T, tid};
+  ContactProbe cp{mg_src, sg_src, 0xFFFFFFFFu, 0.0f};
+  (void)point_collision_cost(M, qa, xf, nullptr, &cp);
+  const bool hit = cp.key != 0xFFFFFFFFu;
+  geom1[i] = hit ? (int)(cp.key >> 16) : -1;
+  geom2[i] = hit ? (int)(cp.key & 0xFFFFu) : -1;
+  dist[i] = hit ? cp.dist : 0.0f;
+}
+
 // Success rows for the host (sspp.h:215-216 hands every collision-free spline back to the caller): compacts the sampled rows
 // of the converged candidates of every query, in candidate order, into `rows` [Q][N][nfd] / `idx` [Q][N] / `count` [Q] -
 // pointers into the handle's mapped pinned block, so the rows cross PCIe as posted stores straight from this kernel and
@@ -1384,6 +1407,18 @@ cudaError_t launch_eval_points(const ModelView& M, int D, const float* pts, int 
     configured = smem;
   }
   sspp_eval_points_kernel<<<(n + T - 1) / T, T, smem, stream>>>(M, D, pts, n, out);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_check_points(const ModelView& M, int D, const float* pts, int n, const int* mg_src, const int* sg_src, int* geom1, int* geom2,
+                                float* dist, cudaStream_t stream) {
+  const int T = 128;
+  const size_t smem = (size_t)(D + (M.chain ? 0 : M.n_mbody * 12)) * T * sizeof(float);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(sspp_check_points_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  sspp_check_points_kernel<<<(n + T - 1) / T, T, smem, stream>>>(M, D, pts, n, mg_src, sg_src, geom1, geom2, dist);
   return cudaGetLastError();
 }
 

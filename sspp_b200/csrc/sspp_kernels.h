@@ -129,6 +129,11 @@ cudaError_t launch_eval_points(const ssppm::ModelView& M, int D, const float* pt
 // 8 corners of every cell contiguously for the kernel's two 16-byte loads per sample
 cudaError_t launch_sdf_bake(const ssppm::ModelView& M, float* nodes, float* cells, int n_sm, cudaStream_t stream);
 
+// Collision.h:51-82 for n configurations (device pointers): FlatModel geom ids of the penetrating contact with the smallest
+// geom pair (-1: free) and its distance; mg_src / sg_src map the compiled geom tables back to FlatModel ids
+cudaError_t launch_check_points(const ssppm::ModelView& M, int D, const float* pts, int n, const int* mg_src, const int* sg_src, int* geom1,
+                                int* geom2, float* dist, cudaStream_t stream);
+
 // SDF mode, refinement step: per collocation row the closest sample sphere's clearance and -clearance * unit field
 // gradient, and their projection on the point-matrix rows G[K][3] = (1/rows) sum_m dirs[m] W[m][.]  (device pointers)
 cudaError_t launch_sdf_gradient(const ssppm::ModelView& M, int D, int K, int rows, const float* W, const float* pts, float* dist,

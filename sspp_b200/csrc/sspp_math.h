@@ -883,8 +883,24 @@ SSPP_HD Prim static_prim(const DevSGeom& g) { return static_prim(&g, 0); }
 // The broad phase of a geom runs branch-free over its pair records, 32 at a time, into a bit mask (plane
 // partners first, then bounded ones); the narrow phase then visits the set bits in ascending order, so the
 // contact costs are summed in pair-table order.
+// ssppcu_check_points (Collision.h:51-82 check_collision_point): of the contacts of one configuration that penetrate by more
+// than 1 mm (dist < margin and dist < -1e-3, the reference's test on mjData::contact) the one with the smallest geom pair
+// (g1 << 16 | g2, FlatModel geom ids, g1 < g2).  Only the diagnostic kernel passes a probe; the scoring paths pass none.
+struct ContactProbe {
+  const int* mg_src;   // DevModel::mg index -> FlatModel geom id
+  const int* sg_src;   // DevModel::sg index -> FlatModel geom id
+  uint32_t key;        // 0xFFFFFFFF: no such contact
+  float dist;
+};
+SSPP_HD void probe_contact(ContactProbe* cp, int ga, int gb, float d, float margin) {
+  if (!(d < margin && d < -1e-3f)) return;
+  const uint32_t lo = (uint32_t)(ga < gb ? ga : gb), hi = (uint32_t)(ga < gb ? gb : ga);
+  const uint32_t key = (lo << 16) | hi;
+  if (key < cp->key) { cp->key = key; cp->dist = d; }
+}
+
 template <class MT, class XF, class QA>
-SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf, uint32_t* wc = nullptr) {
+SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf, uint32_t* wc = nullptr, ContactProbe* cp = nullptr) {
   float cost = M.static_cost;
   if (wc) ++wc[WC_POINTS];
   m3 R; v3 p = mk(0.f, 0.f, 0.f);
@@ -1008,6 +1024,7 @@ SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf, uint32_t* wc = nu
           const float d = moving_static_sd(P, Q, thr, wc);
           const float cc = contact_cost(M.rule, d, margin, P.p, Q.p);
           if (wc && cc != 0.0f) ++wc[WC_CONTACTS];
+          if (cp) probe_contact(cp, cp->mg_src[g], cp->sg_src[t4.x], d, margin);
           cost += cc;
         }
       }
@@ -1032,6 +1049,7 @@ SSPP_HD float point_collision_cost(const MT& M, QA& q, XF& xf, uint32_t* wc = nu
     if (wc) ++wc[WC_MM_NARROW];
     bool ok;
     const float d = prim_sd(P, Q, &ok);
+    if (cp) probe_contact(cp, cp->mg_src[mp.x], cp->mg_src[mp.y], d, margin);
     cost += contact_cost(M.rule, d, margin, P.p, Q.p);
   }
   return cost;

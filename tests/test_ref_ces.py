@@ -214,3 +214,18 @@ def test_collision_point_cost_matches_reference(scene, body):
     assert 0.02 < (rc != 0).mean() < 0.98
     rd = rm.point_costs(body, Q, False)                     # use_center_dist = false: penetration depths
     assert ((rd > 0) == (rc < 0)).all()
+
+
+def test_reference_check_collision_point_is_wired():
+    """Collision<Point>::check_collision_point (Collision.h:51-82) through oracle/_ref: its verdict equals 'the depth cost is
+    positive' (same contacts, same -1e-3 test, Collision.h:84-103) and the printed pair is a filtered geom pair of the scene"""
+    fm = FlatModel.load("planner")
+    ref = pyref.RefModel(fm)
+    rng = np.random.default_rng(21)
+    n = 500
+    pts = np.column_stack([rng.uniform(0.0, 0.7, n), rng.uniform(-0.7, 0.7, n), rng.uniform(0.0, 0.6, n), rng.uniform(-1.6, 1.6, n)])
+    hit, g1, g2, dist = ref.check_points("block1", pts)
+    depth = ref.point_costs("block1", pts, use_center=False)
+    assert np.array_equal(hit, depth > 0) and 20 < hit.sum() < n - 20
+    assert (dist[hit] < -1e-3).all() and (g1[hit] < g2[hit]).all() and (g1[~hit] == -1).all()
+    assert (-dist[hit] <= depth[hit] + 1e-6).all()                       # the first contact's depth is one term of the sum (printed with 6 digits)
