@@ -39,9 +39,56 @@ py::array_t<double> ctrl_view(const sspp::ControlPoints<kDOF>& c, py::handle own
                              c.data.data(), owner);
 }
 
+// The planner as Python sees it: plus a pool of Spline objects for plan()'s result list.  The reference returns thousands of
+// fresh Spline objects per call (sspp_bindings.cpp:46-48); creating a pybind11 instance costs ~0.25 us, so 1 900 successes cost
+// more than five kernel launches.  The pool keeps the objects of the previous result list and hands them out again ONLY when
+// nothing but the pool still refers to them (reference count 1): whatever the caller kept - a list, one path, a numpy view of
+// its control points - is left alone and replaced by a fresh object, so a returned Spline never changes under its holder.
+template <int kDOF>
+struct PooledPlanner : sspp::SamplingPathPlanner<kDOF> {
+  using Base = sspp::SamplingPathPlanner<kDOF>;
+  using Spline = typename Base::Spline;
+  using Base::Base;
+  struct Entry { py::object obj; Spline* ptr; int busy = 0; };   // busy: consecutive calls that found the object still referenced
+  std::vector<Entry> pool;
+
+  py::list to_list(std::vector<Spline>& result) {
+    // `ok, paths = planner.plan(...)` in a loop still holds the previous list while the call runs, so its objects come free
+    // one call later: an entry stays in the pool while busy for up to two calls (two sets alternate, nothing is allocated in
+    // the steady state); an object referenced for longer belongs to its holder and leaves the pool
+    size_t kept = 0;
+    for (size_t i = 0; i < pool.size(); ++i) {
+      Entry& e = pool[i];
+      e.busy = (Py_REFCNT(e.obj.ptr()) == 1) ? 0 : e.busy + 1;
+      if (e.busy <= 2) { if (kept != i) pool[kept] = std::move(e); ++kept; }
+    }
+    pool.resize(kept);
+    py::list out(result.size());
+    size_t at = 0;
+    for (size_t i = 0; i < result.size(); ++i) {
+      while (at < pool.size() && pool[at].busy) ++at;
+      if (at == pool.size()) {
+        py::object o = py::cast(Spline(), py::return_value_policy::move);
+        Spline* p = o.cast<Spline*>();
+        pool.push_back(Entry{std::move(o), p, 0});
+      }
+      Entry& e = pool[at++];
+      *e.ptr = std::move(result[i]);
+      PyList_SET_ITEM(out.ptr(), (py::ssize_t)i, e.obj.inc_ref().ptr());
+    }
+    if (at < pool.size()) {                            // free objects beyond what this call used: keep a bounded reserve
+      size_t spare = 0, k2 = at;
+      for (size_t i = at; i < pool.size(); ++i)
+        if (pool[i].busy || spare++ < 4096) { if (k2 != i) pool[k2] = std::move(pool[i]); ++k2; }
+      pool.resize(k2);
+    }
+    return out;
+  }
+};
+
 template <int kDOF>
 void bind_SamplingPathPlanner(py::module& m, const std::string& class_name, const std::string& splineclass_name) {
-  using Planner = sspp::SamplingPathPlanner<kDOF>;
+  using Planner = PooledPlanner<kDOF>;
   using Spline = typename Planner::Spline;
 
   py::class_<Spline>(m, splineclass_name.c_str())
@@ -88,7 +135,7 @@ void bind_SamplingPathPlanner(py::module& m, const std::string& class_name, cons
                py::gil_scoped_release release;
                success = self.plan(s, e, sigma, lim, result, sample_count, check_points, init_points);
              }
-             return py::make_tuple(success, std::move(result));
+             return py::make_tuple(success, self.to_list(result));
            },
            py::arg("start"), py::arg("end"), py::arg("sigma"), py::arg("limits"), py::arg("sample_count") = 50,
            py::arg("check_points") = 50, py::arg("init_points") = 10)

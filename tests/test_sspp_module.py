@@ -104,6 +104,44 @@ def test_plan_semantics_on_gpu(sp, capfd):
 
 
 @pytest.mark.gpu
+def test_plan_result_objects_are_recycled_only_when_nobody_holds_them(sp):
+    """plan() hands the Spline objects of an earlier result list out again only if nothing else refers to them: a path, or a
+    numpy view of a path's control points, that the caller kept never changes under its holder"""
+    import gc
+    p = sp.SamplingPathPlanner7(XML)
+    p.set_verbose(False)
+    p.set_seed(SEED)
+    lim = np.full(7, np.pi)
+    ok, paths = p.plan(Q_START, Q_END, 0.08, lim, 200, 64, 10)
+    assert ok and len(paths) > 20
+    keep = paths[3]; keep_c = keep.ctrls().copy()
+    view = paths[5].ctrls(); view_c = view.copy()            # keeps paths[5] alive through its base
+    lazy = paths[7]                                           # never touched: its control points are still unbuilt
+    ids_before = {id(x) for x in paths}
+    first = [x.ctrls().copy() for x in paths]
+    del paths
+    gc.collect()
+    ok2, paths2 = p.plan(Q_START, Q_END, 0.08, lim, 200, 64, 10)       # the next draw of the same planner: different samples
+    assert ok2 and not any(y is keep or y is lazy for y in paths2)
+    np.testing.assert_array_equal(keep.ctrls(), keep_c)
+    np.testing.assert_array_equal(view, view_c)
+    np.testing.assert_array_equal(lazy.ctrls(), first[7])
+    assert len({id(y) for y in paths2}) == len(paths2)
+    assert ids_before & {id(y) for y in paths2}, "released objects are expected to be handed out again"
+    assert not any(np.array_equal(y.ctrls(), first[0]) for y in paths2[:5])
+    p.set_seed(SEED)
+    ok3, paths3 = p.plan(Q_START, Q_END, 0.08, lim, 200, 64, 10)       # paths2 is still held: fresh objects, same values as the first call
+    assert len(paths3) == len(first) and all(np.array_equal(a.ctrls(), b) for a, b in zip(paths3, first))
+    assert not ({id(y) for y in paths2} & {id(y) for y in paths3})
+    # the loop a caller writes: the previous list is still bound while the next call runs; two object sets alternate
+    seen = []
+    for it in range(6):
+        ok, paths = p.plan(Q_START, Q_END, 0.08, lim, 200, 64, 10)
+        seen.append({id(y) for y in paths})
+    assert seen[5] & seen[3] and not (seen[5] & seen[4])
+
+
+@pytest.mark.gpu
 def test_plan_device_buffers(sp):
     import torch
     p = sp.SamplingPathPlanner7(XML)
