@@ -62,6 +62,11 @@ class Spline {
   Spline() = default;
   Spline(std::vector<double> knots, ControlPoints<kDOF> ctrls) : knots_(std::move(knots)), ctrls_(std::move(ctrls)) {}
   Spline(std::shared_ptr<const SplineBlock<kDOF>> block, int row) : block_(std::move(block)), row_(row) {}
+  // point an existing object at row `row` of `block` (what assigning Spline(block, row) does, without the temporary)
+  void rebind(const std::shared_ptr<const SplineBlock<kDOF>>& block, int row) {
+    knots_.clear(); ctrls_.data.clear(); ctrls_.cols = 0;
+    block_ = block; row_ = row;
+  }
   const std::vector<double>& knots() const { materialise(); return knots_; }
   const ControlPoints<kDOF>& ctrls() const { materialise(); return ctrls_; }
   ControlPoints<kDOF>& ctrls() { materialise(); return ctrls_; }
@@ -216,26 +221,34 @@ class SamplingPathPlanner {
   // sspp.h:194-232.  One fused launch scores all sample_count candidates; successes come back in
   // candidate order (the reference's order is nondeterministic).  The best path = shortest arc length
   // among the collision-free candidates is stored like the reference's path_spline_.
-  bool plan(const Point& start, const Point& end, double sigma, const Point& limits, std::vector<Spline>& ret_success_paths,
-            int sample_count = 50, int check_points = 50, int init_points = 10) {
+  // plan() up to the point where the reference starts copying splines out: the successes of the scored population as ONE block
+  // (initial spline + their sampled rows, candidate order); row s of it is the s-th returned path.  `found` as plan()'s result.
+  struct PlannedBlock { std::shared_ptr<const SplineBlock<kDOF>> block; int n_success = 0; bool found = false; };
+  PlannedBlock plan_block(const Point& start, const Point& end, double sigma, const Point& limits, int sample_count = 50,
+                          int check_points = 50, int init_points = 10) {
     PlanBuffers& B = plan_device(start, end, sigma, limits, sample_count, check_points, init_points);
-    // the successes share one block (initial spline + their rows); each returned Spline is a (block, row) reference
     auto block = std::make_shared<SplineBlock<kDOF>>();
     block->knots = init_spline_.knots(); block->init = init_spline_.ctrls();
     block->first_free = kSplineDegree; block->n_free = B.n_free;
     block->rows.assign(B.succ_rows, B.succ_rows + (size_t)B.n_success * B.n_free * kDOF);
-    ret_success_paths.clear();
-    ret_success_paths.reserve(B.n_success);
     int best_row = -1;
-    for (int s = 0; s < B.n_success; ++s) {
-      ret_success_paths.emplace_back(block, s);
-      if (B.succ_idx[s] == B.best_idx) best_row = s;
-    }
-    if (verbose_)
-      std::cout << "Sampled " << sample_count << " splines. Successful paths found: " << ret_success_paths.size() << std::endl;
-    if (B.best_idx < 0 || best_row < 0) return false;
-    path_spline_ = Spline(block, best_row);
-    return true;
+    if (B.best_idx >= 0)
+      for (int s = 0; s < B.n_success; ++s) if (B.succ_idx[s] == B.best_idx) { best_row = s; break; }
+    if (verbose_) std::cout << "Sampled " << sample_count << " splines. Successful paths found: " << B.n_success << std::endl;
+    PlannedBlock r;
+    r.n_success = B.n_success; r.found = B.best_idx >= 0 && best_row >= 0;
+    r.block = std::move(block);
+    if (r.found) path_spline_ = Spline(r.block, best_row);
+    return r;
+  }
+  bool plan(const Point& start, const Point& end, double sigma, const Point& limits, std::vector<Spline>& ret_success_paths,
+            int sample_count = 50, int check_points = 50, int init_points = 10) {
+    const PlannedBlock r = plan_block(start, end, sigma, limits, sample_count, check_points, init_points);
+    // the successes share one block; each returned Spline is a (block, row) reference that builds its control points on first use
+    ret_success_paths.clear();
+    ret_success_paths.reserve(r.n_success);
+    for (int s = 0; s < r.n_success; ++s) ret_success_paths.emplace_back(r.block, s);
+    return r.found;
   }
   bool plan(const Point& start, const Point& end, double sigma, const Point& limits, int sample_count = 50, int check_points = 50,
             int init_points = 10) {

@@ -52,7 +52,7 @@ struct PooledPlanner : sspp::SamplingPathPlanner<kDOF> {
   struct Entry { py::object obj; Spline* ptr; int busy = 0; };   // busy: consecutive calls that found the object still referenced
   std::vector<Entry> pool;
 
-  py::list to_list(std::vector<Spline>& result) {
+  py::list to_list(const typename Base::PlannedBlock& result) {
     // `ok, paths = planner.plan(...)` in a loop still holds the previous list while the call runs, so its objects come free
     // one call later: an entry stays in the pool while busy for up to two calls (two sets alternate, nothing is allocated in
     // the steady state); an object referenced for longer belongs to its holder and leaves the pool
@@ -63,9 +63,10 @@ struct PooledPlanner : sspp::SamplingPathPlanner<kDOF> {
       if (e.busy <= 2) { if (kept != i) pool[kept] = std::move(e); ++kept; }
     }
     pool.resize(kept);
-    py::list out(result.size());
+    const size_t n = (size_t)result.n_success;
+    py::list out(n);
     size_t at = 0;
-    for (size_t i = 0; i < result.size(); ++i) {
+    for (size_t i = 0; i < n; ++i) {
       while (at < pool.size() && pool[at].busy) ++at;
       if (at == pool.size()) {
         py::object o = py::cast(Spline(), py::return_value_policy::move);
@@ -73,7 +74,7 @@ struct PooledPlanner : sspp::SamplingPathPlanner<kDOF> {
         pool.push_back(Entry{std::move(o), p, 0});
       }
       Entry& e = pool[at++];
-      *e.ptr = std::move(result[i]);
+      e.ptr->rebind(result.block, (int)i);
       PyList_SET_ITEM(out.ptr(), (py::ssize_t)i, e.obj.inc_ref().ptr());
     }
     if (at < pool.size()) {                            // free objects beyond what this call used: keep a bounded reserve
@@ -127,15 +128,14 @@ void bind_SamplingPathPlanner(py::module& m, const std::string& class_name, cons
       .def("plan",
            [](Planner& self, const py::object& start, const py::object& end, double sigma, const py::object& limits, int sample_count,
               int check_points, int init_points) {
-             std::vector<Spline> result;
              const auto s = to_point<kDOF>(start, "start"), e = to_point<kDOF>(end, "end"), lim = to_point<kDOF>(limits, "limits");
-             bool success;
+             typename Planner::PlannedBlock result;
              {   // the reference holds the GIL through its OpenMP loop (no call_guard, sspp_bindings.cpp:43); the launch + the
                  // wait for the device need none of Python, so other threads run meanwhile
                py::gil_scoped_release release;
-               success = self.plan(s, e, sigma, lim, result, sample_count, check_points, init_points);
+               result = self.plan_block(s, e, sigma, lim, sample_count, check_points, init_points);
              }
-             return py::make_tuple(success, self.to_list(result));
+             return py::make_tuple(result.found, self.to_list(result));
            },
            py::arg("start"), py::arg("end"), py::arg("sigma"), py::arg("limits"), py::arg("sample_count") = 50,
            py::arg("check_points") = 50, py::arg("init_points") = 10)
