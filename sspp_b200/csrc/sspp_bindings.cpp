@@ -12,6 +12,8 @@
 #include <pybind11/pybind11.h>
 #include <pybind11/stl.h>
 
+#include <mutex>
+
 #include "sspp_planner.h"
 
 namespace py = pybind11;
@@ -51,6 +53,7 @@ struct PooledPlanner : sspp::SamplingPathPlanner<kDOF> {
   using Base::Base;
   struct Entry { py::object obj; Spline* ptr; int busy = 0; };   // busy: consecutive calls that found the object still referenced
   std::vector<Entry> pool;
+  std::mutex mu;   // plan() / plan_device() run without the GIL: calls on ONE planner from several Python threads take turns here
 
   py::list to_list(const typename Base::PlannedBlock& result) {
     // `ok, paths = planner.plan(...)` in a loop still holds the previous list while the call runs, so its objects come free
@@ -133,6 +136,7 @@ void bind_SamplingPathPlanner(py::module& m, const std::string& class_name, cons
              {   // the reference holds the GIL through its OpenMP loop (no call_guard, sspp_bindings.cpp:43); the launch + the
                  // wait for the device need none of Python, so other threads run meanwhile
                py::gil_scoped_release release;
+               std::lock_guard<std::mutex> turn(self.mu);
                result = self.plan_block(s, e, sigma, lim, sample_count, check_points, init_points);
              }
              return py::make_tuple(result.found, self.to_list(result));
@@ -145,7 +149,8 @@ void bind_SamplingPathPlanner(py::module& m, const std::string& class_name, cons
               int check_points, int init_points, bool fetch_ctrl) {
              const auto s = to_point<kDOF>(start, "start"), e = to_point<kDOF>(end, "end"), lim = to_point<kDOF>(limits, "limits");
              sspp::PlanBuffers* Bp;
-             { py::gil_scoped_release release; Bp = &self.plan_device(s, e, sigma, lim, sample_count, check_points, init_points); }
+             std::unique_lock<std::mutex> turn(self.mu, std::defer_lock);   // held until the buffers have been read out below; taken without the GIL
+             { py::gil_scoped_release release; turn.lock(); Bp = &self.plan_device(s, e, sigma, lim, sample_count, check_points, init_points); }
              sspp::PlanBuffers& B = *Bp;
              py::dict d;
              d["n_candidates"] = B.n_cand;

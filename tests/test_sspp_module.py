@@ -142,6 +142,31 @@ def test_plan_result_objects_are_recycled_only_when_nobody_holds_them(sp):
 
 
 @pytest.mark.gpu
+def test_plan_from_several_python_threads(sp):
+    """plan() releases the GIL around launch + wait; calls on ONE planner from several threads take turns (a mutex in the binding)
+    and every caller gets a consistent result list"""
+    import threading
+    p = sp.SamplingPathPlanner7(XML)
+    p.set_verbose(False)
+    lim = np.full(7, np.pi)
+    out, errs = [], []
+
+    def work():
+        try:
+            for _ in range(15):
+                ok, paths = p.plan(Q_START, Q_END, 0.08, lim, 256, 32, 10)
+                d = p.plan_device(Q_START, Q_END, 0.08, lim, 256, 32, 10)
+                assert (d["status"] == 0).sum() == d["n_success"]
+                out.append((ok, len(paths), all(np.isfinite(x.ctrls()).all() and x.ctrls().shape == (7, 10) for x in paths[:5])))
+        except Exception as e:                                   # surfaces in the main thread below
+            errs.append(e)
+    ts = [threading.Thread(target=work) for _ in range(4)]
+    [t.start() for t in ts]; [t.join() for t in ts]
+    assert not errs, errs
+    assert len(out) == 60 and all(ok and n > 0 and fin for ok, n, fin in out)
+
+
+@pytest.mark.gpu
 def test_plan_device_buffers(sp):
     import torch
     p = sp.SamplingPathPlanner7(XML)
