@@ -95,3 +95,20 @@ def test_noalloc_entry_rejects_sizes_beyond_the_static_scratch():
     assert ei.value.code == capi.ELIMIT
     err = C.create_string_buffer(64)
     assert capi.lib.ssppcu_bspline_eval_batch_noalloc(0, None, 1, 1, None, 1, 1, None, err, C.c_size_t(64)) == capi.EINVAL
+
+
+@pytest.mark.gpu
+def test_noalloc_entry_on_a_second_device():
+    """every GPU holds its own copy of the static array and its address is looked up with that device current"""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    rows64, ctrl = _problem(9, 50, 40, 8, 3, 3)
+    for dev in (1, 0, 1):
+        rc, want, msg = _call("ssppcu_bspline_eval_batch", rows64, ctrl, device=dev)
+        assert rc == capi.OK, msg
+        rc, got, msg = _call("ssppcu_bspline_eval_batch_noalloc", rows64, ctrl, device=dev)
+        assert rc == capi.OK, msg
+        assert np.array_equal(got, want)
+    rc, _, msg = _call("ssppcu_bspline_eval_batch_noalloc", rows64, ctrl, device=torch.cuda.device_count())
+    assert rc == capi.EINVAL and "device ordinal" in msg
