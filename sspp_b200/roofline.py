@@ -104,8 +104,8 @@ EXEC_FLOP = dict(
     np_sphere_box=28,
     np_box_cull=28,                          # geom centre into the box frame + point-box distance + bound (before any orientation work)
     np_caps_box_early=29,                    # centre into the box frame + point-box distance + bound
-    np_caps_box=29 + 25 + 2 * 19 + 15 + 1,   # ... + segment into the box frame, two bracket gradients, end evaluation
-    np_caps_newton=23,                       # one gradient evaluation + Newton / bisection step
+    np_caps_box=29 + 25 + 2 * 19 + 12 + 5 + 15 + 1,   # ... + segment into the box frame, two bracket gradients, six kink parameters (sub + div), the secant step, end evaluation
+    np_caps_newton=19,                       # one gradient evaluation at a kink inside the bracket (the counter keeps its first name)
     np_box_box_face=120, np_box_box=275,     # 6 face axes / all 15 axes + depth
     np_cyl_box_face=84, np_cyl_box=292,
     np_other=60,

@@ -208,3 +208,42 @@ def test_sdf_mode_oracles_agree():
         ok = live & ~diff
         np.testing.assert_allclose(r["L"][ok], s1["L"][ok], rtol=REL)
         mean, sigma, best, bv = r["mean"], r["sigma"], r["best"], r["best_valid"]
+
+
+@pytest.mark.parametrize("scene", ["robocrane7", "armlab", "robocrane_task", "planner_task", "stacking_task"])
+def test_random_configurations_culled_fp32_replica_vs_cull_free_fp64_oracle(scene):
+    """Single configurations drawn far beyond where a planner samples (whole joint circle, slide joints metres out of range,
+    the free body anywhere around the scene): the replica - product arithmetic with every compile-time pruning and per-point
+    cull, FP32 - must see a contact exactly where the FP64 oracle, which tests every filtered pair and knows no cull, sees one.
+    This is the test that caught the six-step capsule-box iteration stopping millimetres short on long capsules."""
+    from tests.helpers import armlab_case
+    rng = np.random.default_rng(123)
+    n = 20000
+    box = lambda lo, hi: np.column_stack([rng.uniform(lo[i], hi[i], n) for i in range(4)])
+    if scene == "robocrane7":
+        case, pts = joint_case(), rng.uniform(-np.pi, np.pi, (n, 7))
+    elif scene == "armlab":
+        case, pts = armlab_case(), rng.uniform(-2.5, 2.5, (n, 6))
+    elif scene == "robocrane_task":
+        case, pts = task_case(), box([-0.3, -1.0, -0.05, -3.2], [1.0, 1.0, 0.9, 3.2])
+    elif scene == "planner_task":
+        case, pts = task_case("planner.xml", "block1"), box([-0.3, -1.0, -0.05, -3.2], [1.0, 1.0, 0.9, 3.2])
+    else:
+        case, pts = task_case("stacking.xml", "block1"), box([-0.8, -0.8, -0.05, -3.2], [0.8, 0.8, 0.7, 3.2])
+    o1, o2 = o1_for(case), o2_for(case)
+    pts = pts.astype(np.float32).astype(np.float64)
+    hits = bad = band = 0
+    worst = 0.0
+    for q in pts:
+        c1, ncon, md = o1.point_cost(q)
+        c2 = o2.point_cost(q)
+        hits += c1 != 0
+        if (c1 != 0) != (c2 != 0):
+            if abs(md) < 1e-4 or abs(md + 1e-3) < 1e-4:
+                band += 1
+            else:
+                bad += 1
+        elif c1 != 0:
+            worst = max(worst, abs(c2 - c1) / max(abs(c1), 1e-6))
+    assert hits > n // 20 and bad == 0 and band <= 3, (hits, bad, band)
+    assert worst < 1e-5, worst
