@@ -486,3 +486,30 @@ def test_bound_plan_step_reads_the_callers_buffers_every_call():
             assert np.array_equal(x, y)
     with pytest.raises(ValueError):
         b.bind_plan_step(np.zeros((1, 7), np.float32), end, lim)
+
+
+@pytest.mark.parametrize("scene", ["robocrane7", "armlab", "robocrane_task", "planner_task", "stacking_task"])
+def test_random_configurations_gpu_equals_replica_bitwise(scene):
+    """the configurations of tests/test_oracle_agreement.py's random sweep (far outside any planner's sampling range) through the
+    GPU: the same bits as the replica, which that sweep ties to the cull-free FP64 oracle"""
+    rng = np.random.default_rng(123)
+    n = 20000
+    box = lambda lo, hi: np.column_stack([rng.uniform(lo[i], hi[i], n) for i in range(4)])
+    if scene == "robocrane7":
+        case, pts = joint_case(), rng.uniform(-np.pi, np.pi, (n, 7))
+    elif scene == "armlab":
+        case, pts = armlab_case(), rng.uniform(-2.5, 2.5, (n, 6))
+    elif scene == "robocrane_task":
+        case, pts = task_case(), box([-0.3, -1.0, -0.05, -3.2], [1.0, 1.0, 0.9, 3.2])
+    elif scene == "planner_task":
+        case, pts = task_case("planner.xml", "block1"), box([-0.3, -1.0, -0.05, -3.2], [1.0, 1.0, 0.9, 3.2])
+    else:
+        case, pts = task_case("stacking.xml", "block1"), box([-0.8, -0.8, -0.05, -3.2], [0.8, 0.8, 0.7, 3.2])
+    h = _handle(case)
+    o2 = o2_for(case)
+    Q = pts.astype(np.float32)
+    g = h.eval_points(Q)
+    r = np.array([o2.point_cost(q) for q in Q], np.float32)
+    assert np.array_equal(g.view(np.uint32), r.view(np.uint32)), int((g.view(np.uint32) != r.view(np.uint32)).sum())
+    assert 0.02 < (g != 0).mean() < 0.98
+    h.close()
