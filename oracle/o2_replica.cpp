@@ -244,7 +244,7 @@ int o2_iterate(void* h, const float* psi_col, const float* psi_arc, const float*
   }
   *best_idx = (int)(uint32_t)(keys[0] & 0xFFFFFFFFu);
   const float lk = log_poly((float)k + 0.5f);
-  for (int j = 0; j < k; ++j) weights[j] = lk - log_poly((float)j + 1.0f);
+  for (int j = 0; j < k; ++j) weights[j] = ces_log_weight(k, lk, j);
   const float sumw = wide_sum(k, [&](int j, float acc) { return acc + weights[j]; });
   for (int j = 0; j < k; ++j) weights[j] = weights[j] / sumw;
   auto P = [&](int j, int t) { return params[(size_t)((uint32_t)(keys[j] & 0xFFFFFFFFu) - cand_offset) * nfd + t]; };
@@ -303,7 +303,7 @@ int o2_merge_update(void* h, unsigned long long* keys, int n_keys, uint64_t seed
   };
   *best_idx = (int)(uint32_t)(keys[0] & 0xFFFFFFFFu);
   const float lk = log_poly((float)k + 0.5f);
-  for (int j = 0; j < k; ++j) weights[j] = lk - log_poly((float)j + 1.0f);
+  for (int j = 0; j < k; ++j) weights[j] = ces_log_weight(k, lk, j);
   const float sumw = wide_sum(k, [&](int j, float acc) { return acc + weights[j]; });
   for (int j = 0; j < k; ++j) weights[j] = weights[j] / sumw;
   for (int t = 0; t < nfd; ++t) best[t] = P(0, t);

@@ -371,7 +371,7 @@ struct CtaSum { float* s_part; template <class Term> __device__ __forceinline__ 
 
 template <class Sum>
 __device__ __forceinline__ float ces_weight_sum(int k, float lk, Sum sum) {
-  return sum(k, [&](int j, float acc) { return acc + (lk - log_poly((float)j + 1.0f)); });
+  return sum(k, [&](int j, float acc) { return acc + ces_log_weight(k, lk, j); });
 }
 
 // K7 for one distribution element t of one query.  value_of(j): the element's value in the j-th best candidate;
@@ -380,8 +380,8 @@ __device__ __forceinline__ float ces_weight_sum(int k, float lk, Sum sum) {
 // `sum` is WarpSum (one warp executes this) or CtaSum (the whole CTA does); `writer` is true in the thread that
 // stores the result.
 struct InlineWeight {
-  float lk, sumw;
-  __device__ __forceinline__ float operator()(int j) const { return (lk - log_poly((float)j + 1.0f)) / sumw; }
+  int k; float lk, sumw;
+  __device__ __forceinline__ float operator()(int j) const { return ces_log_weight(k, lk, j) / sumw; }
 };
 template <class ValueOf, class WeightOf, class Sum>
 __device__ __forceinline__ void update_element_w(const ScoreConfig& c, int k, int t, float* mean, float* sigma,
@@ -407,7 +407,7 @@ __device__ __forceinline__ void update_element_w(const ScoreConfig& c, int k, in
 template <class ValueOf, class Sum>
 __device__ __forceinline__ void update_element(const ScoreConfig& c, int k, float lk, float sumw, int t, float* mean, float* sigma,
                                                ValueOf value_of, Sum sum, bool writer) {
-  update_element_w(c, k, t, mean, sigma, value_of, InlineWeight{lk, sumw}, sum, writer);
+  update_element_w(c, k, t, mean, sigma, value_of, InlineWeight{k, lk, sumw}, sum, writer);
 }
 
 struct StoredParams {
@@ -474,7 +474,7 @@ __device__ void cta_elites_and_update(const ScoreConfig& c, unsigned long long* 
   }
   const float lk = log_poly((float)k + 0.5f);
   const float sumw = ces_weight_sum(k, lk, WarpSum{lane});   // every warp computes the same number
-  for (int j = tid; j < k; j += T) elite_w[j] = (lk - log_poly((float)j + 1.0f)) / sumw;
+  for (int j = tid; j < k; j += T) elite_w[j] = ces_log_weight(k, lk, j) / sumw;
   // the best candidate is read before any element is updated (its rows are not state, but keep the order of v1)
   const unsigned bi = (unsigned)(keys[0] & 0xFFFFFFFFu);
   if (c.do_update)
@@ -644,7 +644,7 @@ __device__ void update_phase(const IterParams& P, float* s_part, float* s_val, i
       lk = log_poly((float)k + 0.5f);
       if (table) {
         __syncthreads();
-        for (int j = tid; j < k; j += T) s_w[j] = lk - log_poly((float)j + 1.0f);
+        for (int j = tid; j < k; j += T) s_w[j] = ces_log_weight(k, lk, j);
         __syncthreads();
         sumw = CtaSum{s_part}(k, [&](int j, float acc) { return acc + s_w[j]; });
         for (int j = tid; j < k; j += T) s_w[j] = s_w[j] / sumw;
@@ -662,7 +662,7 @@ __device__ void update_phase(const IterParams& P, float* s_part, float* s_val, i
       }
       if (n_succ > 0) {
         float* ew = P.elite_w + (size_t)query * P.n_pad;
-        for (int j = tid; j < k; j += T) ew[j] = table ? s_w[j] : (lk - log_poly((float)j + 1.0f)) / sumw;
+        for (int j = tid; j < k; j += T) ew[j] = table ? s_w[j] : ces_log_weight(k, lk, j) / sumw;
       }
       continue;
     }
@@ -1071,7 +1071,7 @@ __device__ __forceinline__ void merge_finish_body(const MergeParams& P, float* s
         for (int e = tid; e < nfd; e += T) P.best[e] = gp((unsigned)(k0 & 0xFFFFFFFFu), e);
         const float lk = log_poly((float)k + 0.5f);
         const float sumw = ces_weight_sum(k, lk, CtaSum{s_part});
-        for (int j = tid; j < k; j += T) P.elite_w[j] = (lk - log_poly((float)j + 1.0f)) / sumw;
+        for (int j = tid; j < k; j += T) P.elite_w[j] = ces_log_weight(k, lk, j) / sumw;
       } else if (tid == 0) { *P.best_idx = -1; *P.best_cost = __int_as_float(0x7F800000); }
       continue;
     }

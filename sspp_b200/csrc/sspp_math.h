@@ -308,6 +308,32 @@ SSPP_HD float log_poly(float x) {
   return fmaf(fe, 0.693359375f, f + y);
 }
 
+// ln(1 + f) for f in (-0.2929, 0.4143): log_poly's kernel without the reduction (same coefficients, exponent 0)
+SSPP_HD float log1p_poly(float f) {
+  const float z = f * f;
+  float y = 7.0376836292e-2f;
+  y = fmaf(y, f, -1.1514610310e-1f);
+  y = fmaf(y, f, 1.1676998740e-1f);
+  y = fmaf(y, f, -1.2420140846e-1f);
+  y = fmaf(y, f, 1.4249322787e-1f);
+  y = fmaf(y, f, -1.6668057665e-1f);
+  y = fmaf(y, f, 2.0000714765e-1f);
+  y = fmaf(y, f, -2.4999993993e-1f);
+  y = fmaf(y, f, 3.3333331174e-1f);
+  y = y * f * z;
+  y = fmaf(-0.5f, z, y);
+  return f + y;
+}
+// CES log-weight of rank j among k elites: ln(k + 1/2) - ln(j + 1) (tsp_elites.h:24-32); lk = log_poly(k + 1/2).  Towards the end
+// of the elite list the two logarithms nearly cancel (j = k - 1: their difference is 1 / 2k), and a difference of FP32 logarithms
+// is then off by up to 1e-4 relative at k ~ 1000.  Where the ratio (k + 1/2) / (j + 1) is below sqrt(2) the weight is ln(1 + x) of
+// x = (k - j - 1/2) / (j + 1), whose numerator and denominator are exact in FP32.
+SSPP_HD float ces_log_weight(int k, float lk, int j) {
+  const float den = (float)j + 1.0f;
+  const float x = ((float)(k - j) - 0.5f) / den;
+  return (x <= 0.41421354f) ? log1p_poly(x) : lk - log_poly(den);
+}
+
 // sin and cos for |x| < ~1e4: 3-term Cody-Waite reduction to [-pi/4, pi/4], cephes minimax kernels
 SSPP_HD void sincos_poly(float x, float* s, float* c) {
   const float k = rintf(x * 0.63661977236758134308f);
