@@ -48,18 +48,27 @@ def dB(theta, k, i, t):
     return float(r[0]) if np.ndim(theta) == 0 else r
 
 
+def _ordered_sum(rows: np.ndarray, c: np.ndarray) -> np.ndarray:
+    """sum_i rows[:, i] * c[i] accumulated in ascending i from zero - the order of the reference's `sum(c[i] * B(...) for i in
+    range(n))` (BSplines.py:51,55), so that the result carries the same bits (a BLAS product may associate differently)"""
+    acc = np.zeros((rows.shape[0],) + c.shape[1:])
+    for i in range(c.shape[0]):
+        acc = acc + rows[:, i].reshape((-1,) + (1,) * (c.ndim - 1)) * c[i]
+    return acc
+
+
 def bspline(theta, t, c, k):
     """curve value(s) at theta (BSplines.py:44-51): theta < 0 -> c[0] B_0(0), theta >= 1 -> c[n-1]"""
     c = np.asarray(c, np.float64)
     n = len(t) - k - 1
-    v = _rows(theta, t, k, 2) @ c[:n]
+    v = _ordered_sum(_rows(theta, t, k, 2), c[:n])
     return v[0] if np.ndim(theta) == 0 else v
 
 
 def bspline_derivative(theta, t, c, k):
     c = np.asarray(c, np.float64)
     n = len(t) - k - 1
-    v = _rows(theta, t, k, 3) @ c[:n]
+    v = _ordered_sum(_rows(theta, t, k, 3), c[:n])
     return v[0] if np.ndim(theta) == 0 else v
 
 

@@ -95,3 +95,50 @@ def test_batched_evaluation_fails_loudly_without_a_gpu(golden):
     from sspp_b200 import capi
     with pytest.raises(capi.SsppError, match="no CUDA device"):
         bs.bspline_batch([0.5], golden["s0_knots"], np.zeros((2, 7, 9)), 2)
+
+
+@pytest.mark.skipif(not __import__("pathlib").Path("/root/reference/sspp/BSplines.py").exists(),
+                    reason="the reference checkout is only present in the development container")
+def test_random_inputs_bit_identical_to_the_live_reference_module():
+    """sspp/BSplines.py and sspp/CubicPath.py imported from the reference checkout (casadi / matplotlib stubbed: they are only used
+    by its plotting and casadi variants) against the product functions on random orders, sizes, control points and parameters,
+    inside and outside [0, 1]: every value must carry the same bits (fit: 1e-12, it goes through a linear solve)"""
+    import importlib
+    import sys
+    import types
+    saved = {n: sys.modules.get(n) for n in ("casadi", "matplotlib", "matplotlib.pyplot", "sspp", "sspp.BSplines", "sspp.CubicPath")}
+    for name in ("casadi", "matplotlib", "matplotlib.pyplot"):
+        sys.modules.setdefault(name, types.ModuleType(name))
+    sys.path.insert(0, "/root/reference")
+    try:
+        ref = importlib.import_module("sspp.BSplines")
+        refc = importlib.import_module("sspp.CubicPath")
+        rng = np.random.default_rng(0)
+        for trial in range(150):
+            k = int(rng.integers(1, 5)); n = int(rng.integers(max(2, k + 1), 14)); d = int(rng.integers(1, 8))
+            t_ref, t = ref.knot_vector(n, k), bs.knot_vector(n, k)
+            assert np.array_equal(t_ref, t)
+            c = rng.normal(size=(n, d))
+            for theta in list(rng.uniform(-0.1, 1.1, 5)) + [0.0, 1.0, 0.5]:
+                assert np.array_equal(np.asarray(ref.bspline(theta, t_ref, c, k)), np.asarray(bs.bspline(theta, t, c, k)))
+                assert np.array_equal(np.asarray(ref.bspline_derivative(theta, t_ref, c, k)), np.asarray(bs.bspline_derivative(theta, t, c, k)))
+                i = int(rng.integers(0, n))
+                assert ref.B(theta, k, i, t_ref) == bs.B(theta, k, i, t) and ref.dB(theta, k, i, t_ref) == bs.dB(theta, k, i, t)
+            via = rng.normal(size=(n, d))
+            cr, tr = ref.compute_control_points(via, k)
+            cp, tp = bs.compute_control_points(via, k)
+            assert np.allclose(cr, cp, rtol=0, atol=1e-12) and np.array_equal(tr, tp)
+            s, v, e = rng.normal(size=(3, d))
+            pr, pp = refc.CubicPath(), bs.CubicPath()
+            pr.plan(s, v, e); pp.plan(s, v, e)
+            for u in rng.uniform(-0.2, 1.2, 4):
+                for fn in ("evaluate", "evaluate_derivative", "evaluate_second_derivative"):
+                    if hasattr(pr, fn):
+                        assert np.array_equal(np.asarray(getattr(pr, fn)(u)), np.asarray(getattr(pp, fn)(u))), fn
+    finally:
+        sys.path.remove("/root/reference")
+        for n, m in saved.items():
+            if m is None:
+                sys.modules.pop(n, None)
+            else:
+                sys.modules[n] = m
