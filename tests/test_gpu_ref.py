@@ -119,3 +119,32 @@ def test_gpu_check_points_matches_reference_check_collision_point(scene, body):
     if cost is not None:
         assert (cost[ok & hit] != 0).all()
     h.close()
+
+
+@pytest.mark.parametrize("shape", [(100, 100, 7), (50, 50, 10), (512, 64, 10)])
+def test_drop_in_plan_returns_what_the_reference_plan_returns(shape):
+    """`_sspp.SamplingPathPlanner7(xml).plan(...)` (the drop-in Python call) against the reference's own
+    sspp::SamplingPathPlanner<7>::plan (sspp.h:194-232, compiled unmodified) fed the same Philox normals: the same candidates
+    succeed, the returned splines carry the reference's control points (FP32 sampling vs FP64: 2e-6), the same path is best"""
+    from sspp_b200 import _sspp
+    from tests.helpers import Q_START, Q_END
+    n, m, k = shape
+    case = joint_case(n_samples=n, check_points=m, n_points=k)
+    rec = ref_helpers.run_reference_a(case, seed=SEED, it=0)
+    p = _sspp.SamplingPathPlanner7(str(case.mjcf))
+    p.set_verbose(False)
+    p.set_seed(SEED)
+    ok, paths = p.plan(Q_START, Q_END, case.joint_sigma, np.asarray(case.limits, float), n, m, k)
+    free = ~rec["collides"]
+    if len(paths) != int(free.sum()):                                       # only a decision inside the contact band may differ
+        assert in_band(rec["min_dist"]).any()
+        return
+    assert ok == bool(free.any())
+    ref_ctrl = rec["ctrl"][free]                                            # [n_success][K][7], candidate order (sspp.h:215-216)
+    for sp, c in zip(paths, ref_ctrl):
+        np.testing.assert_allclose(sp.ctrls().T, c, rtol=REL, atol=2e-6)
+    if free.any():
+        np.testing.assert_allclose(p.get_ctrl_pts().T, rec["ctrl"][rec["best_idx"]], rtol=REL, atol=2e-6)   # findBestPath
+        j = list(np.flatnonzero(free)).index(rec["best_idx"])
+        for u in (0.0, 0.37, 1.0):
+            np.testing.assert_array_equal(p.evaluate(u), paths[j](u))
