@@ -148,3 +148,34 @@ def test_drop_in_plan_returns_what_the_reference_plan_returns(shape):
         j = list(np.flatnonzero(free)).index(rec["best_idx"])
         for u in (0.0, 0.37, 1.0):
             np.testing.assert_array_equal(p.evaluate(u), paths[j](u))
+
+
+def test_drop_in_task_space_planner_follows_the_reference_planner():
+    """`_tsp.TaskSpacePlanner` (the drop-in Python class, src/main_icra_benchmark.cpp:152-160 arguments) against the reference's
+    own tsp::TaskSpacePlanner run on the same Philox normals, call by call (cold plan, then iterate = true): the same seed sets
+    are sampled, the same candidates succeed, mean and standard deviation of the via distribution follow the reference's.  The
+    GPU continues from its own FP32 state here (no re-synchronisation between calls), hence the looser 1e-4."""
+    from sspp_b200 import _tsp
+    from tests.helpers import FIX, ICRA_BODY, ICRA_START, ICRA_END
+    from tests.test_tsp_module import ICRA_KW
+    case = task_case()
+    iters = 8
+    recs = ref_helpers.run_reference_b(case, iters)
+    p = _tsp.TaskSpacePlanner(str(FIX / "robocrane.xml"), ICRA_BODY, **ICRA_KW)
+    p.set_seed(SEED)
+    for it, rec in enumerate(recs):
+        succ = p.plan(ICRA_START, ICRA_END, it > 0)
+        sets = p.get_sampled_via_sets()
+        live = rec["status"] != 2
+        assert len(sets) == int(live.sum())
+        got = np.array([np.asarray(s).ravel() for s in sets])
+        np.testing.assert_allclose(got, rec["params"][live], rtol=1e-4, atol=2e-5)
+        band = in_band(rec["min_dist"][live])
+        if not band.any():
+            assert len(succ) == rec["n_success"]
+        np.testing.assert_allclose(np.asarray(p.get_current_mean()).ravel(), rec["mean_out"].ravel(), rtol=1e-4, atol=1e-5)
+        np.testing.assert_allclose(np.asarray(p.get_current_stddev()).ravel(), rec["sigma_out"].ravel(), rtol=1e-4, atol=1e-6)
+        if rec["n_success"]:
+            best = rec["params"][rec["best_idx"]].reshape(-1, 4)
+            np.testing.assert_allclose(np.asarray(p.spline()(0.5) if hasattr(p, "spline") else p.evaluate(0.5)),
+                                       np.asarray(p.spline_from_vias(best)(0.5)), atol=1e-4)
