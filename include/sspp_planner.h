@@ -226,6 +226,11 @@ class SamplingPathPlanner {
   struct PlannedBlock { std::shared_ptr<const SplineBlock<kDOF>> block; int n_success = 0; bool found = false; };
   PlannedBlock plan_block(const Point& start, const Point& end, double sigma, const Point& limits, int sample_count = 50,
                           int check_points = 50, int init_points = 10) {
+    if (sample_count <= 0) {        // sspp.h:207-221: the loop body never runs, the summary line is printed, findBestPath finds nothing
+      initializePath(start, end, init_spline_, init_points);
+      if (verbose_) std::cout << "Sampled " << sample_count << " splines. Successful paths found: 0" << std::endl;
+      return PlannedBlock{};
+    }
     PlanBuffers& B = plan_device(start, end, sigma, limits, sample_count, check_points, init_points);
     auto block = std::make_shared<SplineBlock<kDOF>>();
     block->knots = init_spline_.knots(); block->init = init_spline_.ctrls();

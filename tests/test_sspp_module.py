@@ -95,6 +95,12 @@ def test_plan_semantics_on_gpu(sp, capfd):
     np.testing.assert_allclose(best, paths[j].ctrls(), atol=0)
     np.testing.assert_allclose(p.evaluate(0.0), Q_START, atol=1e-6)
     np.testing.assert_allclose(p.evaluate(1.0), Q_END, atol=1e-6)
+    # an empty population: the reference's loop does not run, plan() prints its line and returns false (sspp.h:207-224)
+    ok0, paths0 = p.plan(Q_START, Q_END, 0.08, lim, 0, 100, 7)
+    assert ok0 is False and paths0 == [] and "Sampled 0 splines. Successful paths found: 0" in capfd.readouterr().out
+    for bad in (dict(check_points=1), dict(check_points=5000), dict(init_points=3), dict(init_points=60)):     # limits of this build, stated loudly
+        with pytest.raises(RuntimeError):
+            p.plan(Q_START, Q_END, 0.08, lim, **dict(dict(sample_count=10, check_points=20, init_points=10), **bad))
     # defaults + repeated calls draw new samples; same seed reproduces
     ok2, paths2 = p.plan(Q_START, Q_END, 0.08, lim)
     assert len(paths2) <= 50
