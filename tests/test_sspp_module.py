@@ -3,7 +3,7 @@ error behaviour on the CPU; plan() semantics against the oracles on the GPU."""
 import numpy as np
 import pytest
 
-from tests.helpers import FIX, Q_START, Q_END, SEED, joint_case, o1_for
+from tests.helpers import FIX, ROOT, Q_START, Q_END, SEED, joint_case, o1_for
 
 XML = str(FIX / "robocrane7.xml")
 
@@ -191,3 +191,21 @@ def test_plan_device_buffers(sp):
     t = torch.as_tensor(Dev(d["device_ptrs"]["arc_length"], (512,), "<f4"), device="cuda")
     np.testing.assert_array_equal(t.cpu().numpy(), d["arc_length"])          # zero-copy view of the device results
     assert "ctrl" not in p.plan_device(Q_START, Q_END, 0.08, np.full(7, np.pi), 512, 64, 10)
+
+
+def test_importable_under_the_references_name(tmp_path):
+    """the only line a maintainer adds to the reference's `sspp/__init__.py` makes
+    `from sspp import _sspp` (scripts/main.py:1) resolve to this module, with the reference's class names"""
+    import subprocess
+    import sys
+    pkg = tmp_path / "sspp"
+    pkg.mkdir()
+    (pkg / "__init__.py").write_text("from sspp_b200 import _sspp, _tsp\n")
+    code = ("from sspp import _sspp, _tsp\n"
+            "assert all(hasattr(_sspp, n) for n in ('SamplingPathPlanner3', 'SamplingPathPlanner6', 'SamplingPathPlanner7', 'SamplingPathPlanner9', "
+            "'Spline3', 'Spline6', 'Spline7', 'Spline9'))\n"
+            "assert hasattr(_tsp, 'TaskSpacePlanner')\n"
+            "print('ok')\n")
+    env = dict(__import__("os").environ, PYTHONPATH=f"{tmp_path}:{ROOT}")
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=300)
+    assert out.returncode == 0 and out.stdout.strip().endswith("ok"), out.stderr[-500:]
