@@ -460,6 +460,17 @@ int ssppcu_create(const ssppcu_model_t* mm, const SsppPlannerConfig* cfg, ssppcu
     for (int round = 0; round < 3; ++round) {
       int ctas = std::max(1, std::min(s.n_cand, (per_sm * h->n_sm + c.n_queries - 1) / c.n_queries));
       ctas = std::max(ctas, (s.n_cand + 31) / 32);     // large populations: tiles of <= 32 candidates, several rounds per CTA
+      {
+        // More tiles than resident CTAs (several large queries in one launch, or one very large population): size the tiles so
+        // that they fill a whole number of waves - 3 x 4096 candidates in 32-candidate tiles are 384 tiles on 296 CTAs, 1.3
+        // waves that cost 2; in 21-candidate tiles they are 588, 1.99 waves.  Shapes that fit one wave are left as they were.
+        const long long slots = (long long)per_sm * h->n_sm, total_cand = (long long)c.n_queries * s.n_cand;
+        if ((long long)c.n_queries * ctas > slots) {
+          const long long waves = (total_cand + slots * 32 - 1) / (slots * 32);
+          const int cpc = (int)std::min<long long>(32, std::max<long long>(1, (total_cand + waves * slots - 1) / (waves * slots)));
+          ctas = std::max(ctas, (s.n_cand + cpc - 1) / cpc);
+        }
+      }
       if (hint_cpc) ctas = (s.n_cand + hint_cpc - 1) / hint_cpc;
       for (;;) {
         P.cand_per_cta = (s.n_cand + ctas - 1) / ctas;
